@@ -1,0 +1,419 @@
+// oracle/ref_driver.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+//
+// A small command-line harness around the UNMODIFIED reference headers
+// (/root/reference/include/*.h, compiled where they lie; nothing is copied
+// into this repo).  It exists because the reference's only driver,
+// tests/main.cpp:17-117, hard-codes scene / camera / spp and writes 8-bit PPM.
+// This harness exposes the same calls with runtime arguments and dumps raw
+// float32 so the CUDA path and the C restatement (oracle/volpath_oracle.c) can
+// be checked to 1e-4 / 1e-5.
+//
+// Build: see oracle/Makefile (needs -DRECORD_PIXEL_GAUSSIANS).
+// Output binary: oracle/_ref/ref_driver (git-ignored, travels with gpurun).
+//
+// Sub-commands (key=value arguments):
+//   render   scene=F integrator=ms|ss w=W h=H spp=S cam=pinhole|ortho
+//            pos=x,y,z look=x,y,z fov=rad out=img.f32 [record=lists.bin] [repeat=K]
+//   kat      scene=F n=N seed=S out=kat.bin       known-answer vectors
+//   sfd      scene=F target=img.f32 signs=signs.i8 S=s iters=k w= h= spp= ... out=prefix
+//   spheres  scene=F w= h= step= env= cam... out=img.f32   (RayMarchingSpheres; env part is
+//            random_device-seeded in the reference -> statistical use only)
+#include "integrator.h"
+#include "test_integrators.h"
+#include "inverse_integrator.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <sstream>
+#include <string>
+
+using Args = std::map<std::string, std::string>;
+
+static Args parse_args(int argc, char** argv, int first) {
+    Args a;
+    for (int i = first; i < argc; ++i) {
+        std::string s(argv[i]);
+        auto eq = s.find('=');
+        if (eq == std::string::npos) { a[s] = "1"; continue; }
+        a[s.substr(0, eq)] = s.substr(eq + 1);
+    }
+    return a;
+}
+static std::string get(const Args& a, const std::string& k, const std::string& def = "") {
+    auto it = a.find(k);
+    return it == a.end() ? def : it->second;
+}
+static Eigen::Vector3f vec3(const std::string& s) {
+    Eigen::Vector3f v(0, 0, 0);
+    std::stringstream ss(s);
+    std::string tok;
+    for (int i = 0; i < 3 && std::getline(ss, tok, ','); ++i) v[i] = std::stof(tok);
+    return v;
+}
+static std::shared_ptr<Camera> make_camera(const Args& a) {
+    Eigen::Vector3f pos = vec3(get(a, "pos", "0,1,6"));
+    Eigen::Vector3f look = vec3(get(a, "look", "0,1,0"));
+    Eigen::Vector3f view_dir = (look - pos).normalized();   // tests/main.cpp:32
+    if (get(a, "cam", "pinhole") == "ortho")
+        return std::make_shared<Orthographic_Camera>(pos, view_dir);
+    float fov = std::stof(get(a, "fov", "0.78539816339"));  // tests/main.cpp:22
+    return std::make_shared<Pinhole_Camera>(pos, view_dir, fov);
+}
+static void dump_image(const Image& img, const std::string& path) {
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) { perror("open out"); exit(2); }
+    int W = img.get_width(), H = img.get_height();
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            Eigen::Vector3f p = img.get_pixel(x, y);
+            float rgb[3] = {p[0], p[1], p[2]};
+            fwrite(rgb, sizeof(float), 3, f);
+        }
+    fclose(f);
+}
+static Image load_image_f32(const std::string& path, int W, int H) {
+    Image img(W, H);
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) { perror("open target"); exit(2); }
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            float rgb[3];
+            if (fread(rgb, sizeof(float), 3, f) != 3) { fprintf(stderr, "short target\n"); exit(2); }
+            img.set_pixel(x, y, Eigen::Vector3f(rgb[0], rgb[1], rgb[2]));
+        }
+    fclose(f);
+    return img;
+}
+
+// ---------------------------------------------------------------------------
+static int cmd_render(const Args& a) {
+    Scene scene = Scene::load_GMM(get(a, "scene"));
+    int W = std::stoi(get(a, "w", "64")), H = std::stoi(get(a, "h", "64"));
+    int spp = std::stoi(get(a, "spp", "16"));
+    int repeat = std::stoi(get(a, "repeat", "1"));
+    auto cam = make_camera(a);
+    Image image(W, H);
+    std::string integ = get(a, "integrator", "ms");
+    std::vector<std::vector<uint32_t>> lists;
+    bool record = !get(a, "record").empty();
+    double best = 1e30;
+    std::unique_ptr<FreeFlightGaussians> ss;
+    std::unique_ptr<MultiScatterGaussians> ms;
+    if (integ == "ss") ss = std::make_unique<FreeFlightGaussians>(cam, spp);
+    else ms = std::make_unique<MultiScatterGaussians>(cam, spp, std::stoi(get(a, "min_bounces", "5")));
+    for (int r = 0; r < repeat; ++r) {
+        auto t0 = std::chrono::high_resolution_clock::now();
+        if (ss) ss->render(scene, image);
+        else if (record) ms->render(scene, image, &lists);
+        else ms->render(scene, image);
+        auto t1 = std::chrono::high_resolution_clock::now();
+        best = std::min(best, std::chrono::duration<double>(t1 - t0).count());
+    }
+    if (!get(a, "out").empty()) dump_image(image, get(a, "out"));
+    if (record) {
+        // layout: int32 npix, then per pixel: int32 count, uint32 idx[count]
+        FILE* f = fopen(get(a, "record").c_str(), "wb");
+        int32_t np = (int32_t)lists.size();
+        fwrite(&np, 4, 1, f);
+        for (auto& l : lists) {
+            int32_t c = (int32_t)l.size();
+            fwrite(&c, 4, 1, f);
+            if (c) fwrite(l.data(), 4, c, f);
+        }
+        fclose(f);
+    }
+    double nsamp = double(W) * H * spp;
+    printf("{\"cmd\": \"render\", \"integrator\": \"%s\", \"w\": %d, \"h\": %d, \"spp\": %d, "
+           "\"n_gaussians\": %zu, \"time_s\": %.6f, \"msamples_per_s\": %.6f, \"threads\": %d}\n",
+           integ.c_str(), W, H, spp, scene.get_num_primitives(), best, nsamp / best * 1e-6,
+           omp_get_max_threads());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Known-answer vectors.  All records are float32/uint32 little-endian, written
+// as sections: [uint32 tag][uint32 count][payload].
+static void wsec(FILE* f, uint32_t tag, uint32_t count, const void* p, size_t bytes) {
+    fwrite(&tag, 4, 1, f); fwrite(&count, 4, 1, f);
+    uint64_t b = bytes; fwrite(&b, 8, 1, f);
+    fwrite(p, 1, bytes, f);
+}
+static int cmd_kat(const Args& a) {
+    Scene scene = Scene::load_GMM(get(a, "scene"));
+    const GaussianMixtureModel& gmm = scene.gmm->at(0);
+    int n = std::stoi(get(a, "n", "1000"));
+    uint64_t seed = std::stoull(get(a, "seed", "1"));
+    FILE* f = fopen(get(a, "out").c_str(), "wb");
+    if (!f) { perror("open out"); return 2; }
+
+    // tag 1: PCG streams. for k<n: (x,y,si) = hashed small ints; 8 u32 + 8 uniform floats
+    {
+        std::vector<uint32_t> rec;
+        PCG32 gen(seed, 7);
+        for (int k = 0; k < n; ++k) {
+            int x = gen.next_u32() % 2048, y = gen.next_u32() % 2048, si = gen.next_u32() % 1024;
+            rec.push_back(x); rec.push_back(y); rec.push_back(si);
+            uint64_t ps = derive_path_seed(x, y, si);
+            rec.push_back(uint32_t(ps)); rec.push_back(uint32_t(ps >> 32));
+            PCG32 r(ps, 1);
+            for (int j = 0; j < 4; ++j) rec.push_back(r.next_u32());
+            for (int j = 0; j < 4; ++j) { float u = r.uniform(); uint32_t b; memcpy(&b, &u, 4); rec.push_back(b); }
+        }
+        wsec(f, 1, n, rec.data(), rec.size() * 4);
+    }
+    // tag 2: erfinv_approx on a grid in (-1,1): pairs (x, y) as double
+    {
+        std::vector<double> rec;
+        for (int k = 0; k < n; ++k) {
+            double x = -0.999999 + 1.999998 * (k + 0.5) / n;
+            rec.push_back(x); rec.push_back(erfinv_approx(x));
+        }
+        wsec(f, 2, n, rec.data(), rec.size() * 8);
+    }
+    // random rays through the scene bounding region
+    PCG32 gen(seed, 11);
+    auto rnd = [&]() { return gen.uniform(); };
+    size_t N = gmm.gaussians.size();
+    // tag 3: per (ray, gaussian): o(3) d(3) gidx hit t0 t1 tau(t0,t1) mu_t(mid) ok t_solved
+    {
+        std::vector<float> rec;
+        int made = 0, tries = 0;
+        while (made < n && tries < 200 * n) {
+            ++tries;
+            size_t gi = size_t(rnd() * N) % N;
+            const Gaussian& G = gmm.gaussians[gi];
+            // aim at a point near the gaussian so that most rays hit
+            Eigen::Vector3f c = G.centroid();
+            Eigen::Matrix3f cov = G.get_covariance();
+            float sx = std::sqrt(cov(0, 0)), sy = std::sqrt(cov(1, 1)), sz = std::sqrt(cov(2, 2));
+            Eigen::Vector3f tgt = c + Eigen::Vector3f((rnd() * 2 - 1) * 2.5f * sx, (rnd() * 2 - 1) * 2.5f * sy,
+                                                      (rnd() * 2 - 1) * 2.5f * sz);
+            Eigen::Vector3f o(rnd() * 6 - 3, rnd() * 6 - 2, rnd() * 6 - 3);
+            if (made % 5 == 0) o = c + Eigen::Vector3f((rnd() - .5f) * sx, (rnd() - .5f) * sy, (rnd() - .5f) * sz);  // origin inside
+            Ray ray(o, tgt - o);
+            float t0 = 0, t1 = 0;
+            bool hit = G.intersect_direct(ray, t0, t1);
+            float tau = 0, mu = 0, tsol = 0, okf = 0, frac = rnd();
+            if (hit) {
+                tau = G.optical_depth(ray, t0, t1);
+                mu = G.mu_t(ray(0.5f * (t0 + t1)));
+                bool ok = G.solve_for_t_given_tau(ray, t0, t1, frac * tau, tsol);
+                okf = ok ? 1.f : 0.f;
+            }
+            float gif; uint32_t giu = (uint32_t)gi; memcpy(&gif, &giu, 4);
+            float row[16] = {ray.origin[0], ray.origin[1], ray.origin[2], ray.direction[0], ray.direction[1],
+                             ray.direction[2], gif, hit ? 1.f : 0.f, t0, t1, tau, mu, frac, okf, tsol, 0.f};
+            rec.insert(rec.end(), row, row + 16);
+            ++made;
+        }
+        wsec(f, 3, made, rec.data(), rec.size() * 4);
+    }
+    // tag 4: transmittance_up_to on random rays: o(3) d(3) tmax Tr
+    {
+        std::vector<float> rec;
+        for (int k = 0; k < n; ++k) {
+            Eigen::Vector3f o(rnd() * 2 - 1, rnd() * 2, rnd() * 2 - 1);
+            if (k % 3 == 0) o = Eigen::Vector3f(rnd() * 8 - 4, rnd() * 6 - 2, rnd() * 8 - 4);
+            Eigen::Vector3f tgt(rnd() * 2 - 1, rnd() * 2, rnd() * 2 - 1);
+            Ray ray(o, tgt - o);
+            float tmax = (k % 2) ? std::numeric_limits<float>::infinity() : rnd() * 4.0f;
+            float Tr = gmm.transmittance_up_to(ray, tmax);
+            float row[8] = {ray.origin[0], ray.origin[1], ray.origin[2], ray.direction[0], ray.direction[1],
+                            ray.direction[2], tmax, Tr};
+            rec.insert(rec.end(), row, row + 8);
+        }
+        wsec(f, 4, n, rec.data(), rec.size() * 4);
+    }
+    // tag 5: event lists for a few rays: o(3) d(3) nevents then (t, enter, idx)*
+    {
+        std::vector<float> rec;
+        int nr = std::min(n, 64);
+        for (int k = 0; k < nr; ++k) {
+            Eigen::Vector3f o(rnd() * 8 - 4, rnd() * 6 - 2, rnd() * 8 - 4);
+            Eigen::Vector3f tgt(rnd() * 2 - 1, rnd() * 2, rnd() * 2 - 1);
+            Ray ray(o, tgt - o);
+            std::vector<PrimitiveHitEvent> ev;
+            gmm.intersect_events(ray, ev);
+            float hdr[7] = {ray.origin[0], ray.origin[1], ray.origin[2], ray.direction[0], ray.direction[1],
+                            ray.direction[2], float(ev.size())};
+            rec.insert(rec.end(), hdr, hdr + 7);
+            for (auto& e : ev) { rec.push_back(e.t); rec.push_back(e.entering ? 1.f : 0.f); rec.push_back(float(e.index)); }
+        }
+        wsec(f, 5, nr, rec.data(), rec.size() * 4);
+    }
+    // tag 6: camera rays: kind(0 pinhole,1 ortho) u v -> o(3) d(3), for the default cameras
+    {
+        std::vector<float> rec;
+        auto pin = make_camera(a);
+        Args b = a; b["cam"] = "ortho";
+        auto ort = make_camera(b);
+        for (int k = 0; k < n; ++k) {
+            float u = rnd(), v = rnd();
+            for (int kind = 0; kind < 2; ++kind) {
+                Ray r = (kind ? ort : pin)->sample_ray({u, v});
+                float row[9] = {float(kind), u, v, r.origin[0], r.origin[1], r.origin[2], r.direction[0],
+                                r.direction[1], r.direction[2]};
+                rec.insert(rec.end(), row, row + 9);
+            }
+        }
+        wsec(f, 6, 2 * n, rec.data(), rec.size() * 4);
+    }
+    fclose(f);
+    printf("{\"cmd\": \"kat\", \"n\": %d}\n", n);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// One or more SFD iterations with INJECTED sign vectors.  The loop glue below
+// follows include/inverse_integrator.h:114-207 step by step, but every
+// numerical routine it calls is the reference's own (MultiScatterGaussians::
+// render with recording, compute_pixel_losses, pack_parameters,
+// apply_params_to_gmm_local, make_default_eps_for_params, AdamOptimizer::step).
+// The reference draws its signs from std::random_device (inverse_integrator.h:
+// 101-103,141-143), which cannot be reproduced, hence the file.
+// Output <out>.bin sections per iteration: tag 10 params_before[D] f32,
+// tag 11 F_diff[S*N] f64, tag 12 grad[D] f32, tag 13 params_after[D] f32,
+// tag 14 {mean base loss} f64, tag 15 base image f32[3WH].
+static int cmd_sfd(const Args& a) {
+    Scene scene_initial = Scene::load_GMM(get(a, "scene"));
+    int W = std::stoi(get(a, "w", "32")), H = std::stoi(get(a, "h", "32"));
+    int spp = std::stoi(get(a, "spp", "16"));
+    int S = std::stoi(get(a, "S", "4")), iters = std::stoi(get(a, "iters", "1"));
+    float lr = std::stof(get(a, "lr", "0.01"));
+    auto cam = make_camera(a);
+    auto fwd = std::make_shared<MultiScatterGaussians>(cam, spp);
+    Image I_ref = load_image_f32(get(a, "target"), W, H);
+
+    Scene scene_opt = scene_initial;
+    scene_opt.gmm = std::vector<GaussianMixtureModel>{scene_initial.gmm->at(0)};
+    Scene scene_alt = scene_initial;
+    scene_alt.gmm = std::vector<GaussianMixtureModel>{scene_initial.gmm->at(0)};
+    GaussianMixtureModel& base_gmm = scene_opt.gmm->at(0);
+    GaussianMixtureModel& alt_gmm = scene_alt.gmm->at(0);
+
+    std::vector<float> params;
+    base_gmm.pack_parameters(params);
+    if (!get(a, "params_in").empty()) {   // optional: start from given packed params
+        FILE* pf = fopen(get(a, "params_in").c_str(), "rb");
+        if (fread(params.data(), 4, params.size(), pf) != params.size()) { fprintf(stderr, "short params\n"); return 2; }
+        fclose(pf);
+    }
+    // the reference renders the *unpacked* scene from iteration 1 on; make iteration 0
+    // consistent with that so that the packed vector alone defines the scene.
+    apply_params_to_gmm_local(params, base_gmm);
+    const size_t D = params.size(), per = 11, N = base_gmm.get_num_gaussians();
+    std::vector<float> eps = make_default_eps_for_params(params);
+    AdamOptimizer adam(D, lr);
+
+    std::vector<int8_t> signs(size_t(iters) * S * D);
+    {
+        FILE* sf = fopen(get(a, "signs").c_str(), "rb");
+        if (!sf || fread(signs.data(), 1, signs.size(), sf) != signs.size()) { fprintf(stderr, "bad signs file\n"); return 2; }
+        fclose(sf);
+    }
+    FILE* f = fopen((get(a, "out") + ".bin").c_str(), "wb");
+    Image I_base(W, H), I_plus(W, H);
+    std::vector<float> loss_base, loss_plus;
+    auto T0 = std::chrono::high_resolution_clock::now();
+    for (int iter = 0; iter < iters; ++iter) {
+        wsec(f, 10, D, params.data(), D * 4);
+        std::vector<std::vector<uint32_t>> ppg(W * H);
+        fwd->render(scene_opt, I_base, &ppg);
+        compute_pixel_losses(I_base, I_ref, loss_base);
+        std::vector<std::vector<int>> gpix(N);
+        for (int p = 0; p < W * H; ++p) for (uint32_t g : ppg[p]) if (g < N) gpix[g].push_back(p);
+        std::vector<double> grads_d(D, 0.0), F_all;
+        for (int sidx = 0; sidx < S; ++sidx) {
+            const int8_t* s = signs.data() + (size_t(iter) * S + sidx) * D;
+            std::vector<float> pp(D);
+            for (size_t i = 0; i < D; ++i) pp[i] = params[i] + float(s[i]) * eps[i];
+            apply_params_to_gmm_local(pp, alt_gmm);
+            std::vector<std::vector<uint32_t>> ppg2(W * H);
+            fwd->render(scene_alt, I_plus, &ppg2);
+            compute_pixel_losses(I_plus, I_ref, loss_plus);
+            std::vector<std::vector<int>> gpix2(N);
+            for (int p = 0; p < W * H; ++p) for (uint32_t g : ppg2[p]) if (g < N) gpix2[g].push_back(p);
+            std::vector<double> F_diff(N, 0.0);
+            for (size_t g = 0; g < N; ++g) {
+                std::unordered_set<int> U(gpix[g].begin(), gpix[g].end());
+                U.insert(gpix2[g].begin(), gpix2[g].end());
+                double Fp = 0, Fb = 0;
+                for (int p : U) { Fp += double(loss_plus[p]); Fb += double(loss_base[p]); }
+                F_diff[g] = Fp - Fb;
+            }
+            for (size_t i = 0; i < D; ++i) grads_d[i] += F_diff[i / per] * double(s[i]) / double(eps[i]);
+            F_all.insert(F_all.end(), F_diff.begin(), F_diff.end());
+        }
+        std::vector<float> grads(D);
+        for (size_t i = 0; i < D; ++i) grads[i] = float(grads_d[i] / double(S));
+        wsec(f, 11, S * N, F_all.data(), F_all.size() * 8);
+        wsec(f, 12, D, grads.data(), D * 4);
+        if (!adam.step(params, grads)) return 3;
+        apply_params_to_gmm_local(params, base_gmm);
+        wsec(f, 13, D, params.data(), D * 4);
+        double ml = 0; for (float l : loss_base) ml += l; ml /= double(loss_base.size());
+        wsec(f, 14, 1, &ml, 8);
+        std::vector<float> img(size_t(3) * W * H);
+        for (int y = 0; y < H; ++y) for (int x = 0; x < W; ++x) { auto p = I_base.get_pixel(x, y); for (int c = 0; c < 3; ++c) img[3 * (size_t(y) * W + x) + c] = p[c]; }
+        wsec(f, 15, W * H, img.data(), img.size() * 4);
+    }
+    auto T1 = std::chrono::high_resolution_clock::now();
+    fclose(f);
+    printf("{\"cmd\": \"sfd\", \"iters\": %d, \"S\": %d, \"n_gaussians\": %zu, \"time_s\": %.6f, \"iters_per_s\": %.6f, \"threads\": %d}\n",
+           iters, S, N, std::chrono::duration<double>(T1 - T0).count(),
+           iters / std::chrono::duration<double>(T1 - T0).count(), omp_get_max_threads());
+    return 0;
+}
+
+// dump pack_parameters() of a scene (used to seed the CUDA inverse path)
+static int cmd_pack(const Args& a) {
+    Scene scene = Scene::load_GMM(get(a, "scene"));
+    std::vector<float> params;
+    scene.gmm->at(0).pack_parameters(params);
+    FILE* f = fopen(get(a, "out").c_str(), "wb");
+    fwrite(params.data(), 4, params.size(), f);
+    fclose(f);
+    printf("{\"cmd\": \"pack\", \"D\": %zu}\n", params.size());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+static int cmd_spheres(const Args& a) {
+    Scene scene = Scene::load_SMM(get(a, "scene"));
+    int W = std::stoi(get(a, "w", "64")), H = std::stoi(get(a, "h", "64"));
+    auto cam = make_camera(a);
+    Image image(W, H);
+    std::string integ = get(a, "integrator", "march_spheres");
+    float step = std::stof(get(a, "step", "0.01"));
+    int env = std::stoi(get(a, "env", "5"));
+    auto t0 = std::chrono::high_resolution_clock::now();
+    if (integ == "test") { TestIntegrator ti(cam); ti.render(scene, image); }
+    else if (integ == "march_pure") { PureRayMarching pm(cam, step, env); pm.render(scene, image); }
+    else { RayMarchingSpheres rm(cam, step, env); rm.render(scene, image); }
+    auto t1 = std::chrono::high_resolution_clock::now();
+    dump_image(image, get(a, "out"));
+    printf("{\"cmd\": \"spheres\", \"w\": %d, \"h\": %d, \"time_s\": %.6f, \"threads\": %d}\n", W, H,
+           std::chrono::duration<double>(t1 - t0).count(), omp_get_max_threads());
+    return 0;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|kat|sfd|pack|spheres key=value...\n"); return 1; }
+    Args a = parse_args(argc, argv, 2);
+    std::string c(argv[1]);
+    // the reference prints banners on stdout; keep our JSON line last.
+    try {
+        if (c == "render") return cmd_render(a);
+        if (c == "kat") return cmd_kat(a);
+        if (c == "sfd") return cmd_sfd(a);
+        if (c == "pack") return cmd_pack(a);
+        if (c == "spheres") return cmd_spheres(a);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "error: %s\n", e.what());
+        return 2;
+    }
+    fprintf(stderr, "unknown command %s\n", c.c_str());
+    return 1;
+}
