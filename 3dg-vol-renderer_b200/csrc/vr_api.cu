@@ -1,0 +1,222 @@
+// vr_api.cu -- C-ABI of libvolrender_b200.so: context, scene upload, Integrator::render.
+// There is deliberately NO CPU code path: without a CUDA device vr_create fails with
+// VR_ERR_NO_DEVICE and nothing else can be called.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "vr_bvh.h"
+#include "vr_context.h"
+
+using namespace vr;
+
+vr::SceneDev vr_context::scene_dev() const {
+    SceneDev S{};
+    S.gauss = gauss_leaf.as<float4>();
+    S.nodes = nodes.as<float4>();
+    S.orig = perm.as<uint32_t>();
+    S.n = n;
+    S.nl = nl;
+    S.lpos = lpos.as<float>();
+    S.lint = lint.as<float>();
+    S.env[0] = env[0]; S.env[1] = env[1]; S.env[2] = env[2];
+    return S;
+}
+
+namespace vr {
+int fail(vr_context* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    return code;
+}
+int cuda_fail(vr_context* c, cudaError_t e, const char* what) {
+    std::string m = std::string(what) + ": " + cudaGetErrorString(e);
+    cudaGetLastError();
+    return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, m);
+}
+}  // namespace vr
+
+extern "C" {
+
+const char* vr_version(void) { return "volrender_b200 0.1 (sm_100a)"; }
+
+int vr_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int vr_create(vr_context** out, int device_id) {
+    if (!out) return VR_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    int ndev = vr_device_count();
+    if (ndev <= 0 || device_id < 0 || device_id >= ndev) return VR_ERR_NO_DEVICE;
+    vr_context* ctx = new vr_context();
+    ctx->device = device_id;
+    *out = ctx;  // returned even on failure so that vr_last_error can be read; vr_destroy is still required
+    VR_CUDA(cudaSetDevice(device_id));
+    cudaDeviceProp prop;
+    VR_CUDA(cudaGetDeviceProperties(&prop, device_id));
+    if (prop.major < 10) return fail(ctx, VR_ERR_UNSUPPORTED, "device is not sm_100 class: kernels are built for sm_100a only");
+    ctx->num_sms = prop.multiProcessorCount;
+    VR_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (auto& e : ctx->ev) VR_CUDA(cudaEventCreate(&e));
+    VR_CUDA(cudaMallocHost((void**)&ctx->h_stats, sizeof(unsigned long long) * kNumStats));
+    VR_CUDA(cudaMallocHost((void**)&ctx->h_counters, sizeof(unsigned int) * 4));
+    VR_CUDA(ctx->stats.ensure(sizeof(unsigned long long) * kNumStats));
+    VR_CUDA(ctx->counters.ensure(sizeof(unsigned int) * 4));
+    ctx->blocks_per_sm_main = std::max(1, path_kernel_blocks_per_sm(false));
+    ctx->blocks_per_sm_arena = std::max(1, std::min(2, path_kernel_blocks_per_sm(true)));
+    return VR_OK;
+}
+
+void vr_destroy(vr_context* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    sfd_destroy(ctx);
+    for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
+                      &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->spheres, &ctx->lpos, &ctx->lint,
+                      &ctx->image, &ctx->sampleL, &ctx->counters, &ctx->stats, &ctx->overflow_list, &ctx->arena,
+                      &ctx->record_bits, &ctx->scratch})
+        b->release();
+    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+    if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* vr_last_error(const vr_context* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+void* vr_stream(vr_context* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int vr_set_option(vr_context* ctx, const char* name, double value) {
+    if (!ctx || !name) return VR_ERR_INVALID_ARGUMENT;
+    if (!strcmp(name, "hit_capacity")) { ctx->hit_capacity = (int)value; ctx->arena.release(); return VR_OK; }
+    if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
+    if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
+    return fail(ctx, VR_ERR_INVALID_ARGUMENT, std::string("unknown option ") + name);
+}
+
+// ------------------------------------------------------------------------------------------
+// scene
+// ------------------------------------------------------------------------------------------
+int vr_set_gmm(vr_context* ctx, int n, const float* mean3, const float* cov6, const float* density,
+               const float* albedo) {
+    if (!ctx || n < 0 || (n > 0 && (!mean3 || !cov6 || !density || !albedo))) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_set_gmm: bad arguments");
+    if (n >= (1 << 28)) return fail(ctx, VR_ERR_UNSUPPORTED, "vr_set_gmm: more than 2^28 Gaussians");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    const size_t m = (size_t)std::max(n, 1);
+    VR_CUDA(ctx->mean3.ensure(m * 12)); VR_CUDA(ctx->cov6.ensure(m * 24));
+    VR_CUDA(ctx->density.ensure(m * 4)); VR_CUDA(ctx->albedo.ensure(m * 4));
+    if (n > 0) {
+        VR_CUDA(cudaMemcpyAsync(ctx->mean3.p, mean3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(ctx->cov6.p, cov6, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(ctx->density.p, density, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(ctx->albedo.p, albedo, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return set_gmm_from_device(ctx, n);
+}
+
+int vr_set_gmm_params(vr_context* ctx, int n, const float* params11) {
+    if (!ctx || n < 0 || (n > 0 && !params11)) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_set_gmm_params: bad arguments");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    const size_t m = (size_t)std::max(n, 1);
+    VR_CUDA(ctx->mean3.ensure(m * 12)); VR_CUDA(ctx->cov6.ensure(m * 24));
+    VR_CUDA(ctx->density.ensure(m * 4)); VR_CUDA(ctx->albedo.ensure(m * 4));
+    VR_CUDA(ctx->scratch.ensure(m * 44));
+    if (n > 0) {
+        VR_CUDA(cudaMemcpyAsync(ctx->scratch.p, params11, (size_t)n * 44, cudaMemcpyHostToDevice, ctx->stream));
+        launch_unpack_params(n, ctx->scratch.as<float>(), ctx->mean3.as<float>(), ctx->cov6.as<float>(),
+                             ctx->density.as<float>(), ctx->albedo.as<float>(), ctx->stream);
+    }
+    return set_gmm_from_device(ctx, n);
+}
+
+int vr_unpack_params(vr_context* ctx, int n, const float* params11, float* mean3, float* cov6, float* density,
+                     float* albedo) {
+    if (!ctx || n <= 0 || !params11 || !mean3 || !cov6 || !density || !albedo) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_unpack_params: bad arguments");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    VR_CUDA(ctx->scratch.ensure((size_t)n * (44 + 12 + 24 + 8)));
+    float* d = ctx->scratch.as<float>();
+    float *dm = d + (size_t)11 * n, *dc = dm + (size_t)3 * n, *dd = dc + (size_t)6 * n, *da = dd + n;
+    VR_CUDA(cudaMemcpyAsync(d, params11, (size_t)n * 44, cudaMemcpyHostToDevice, ctx->stream));
+    launch_unpack_params(n, d, dm, dc, dd, da, ctx->stream);
+    VR_CUDA(cudaMemcpyAsync(mean3, dm, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(cov6, dc, (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(density, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(albedo, da, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VR_OK;
+}
+
+int vr_set_lights(vr_context* ctx, int nl, const float* pos3, const float* intensity3, const float* env_rgb) {
+    if (!ctx || nl < 0 || (nl > 0 && (!pos3 || !intensity3))) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_set_lights: bad arguments");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    VR_CUDA(ctx->lpos.ensure((size_t)std::max(nl, 1) * 12));
+    VR_CUDA(ctx->lint.ensure((size_t)std::max(nl, 1) * 12));
+    if (nl > 0) {
+        VR_CUDA(cudaMemcpyAsync(ctx->lpos.p, pos3, (size_t)nl * 12, cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(ctx->lint.p, intensity3, (size_t)nl * 12, cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->nl = nl;
+    if (env_rgb) { ctx->env[0] = env_rgb[0]; ctx->env[1] = env_rgb[1]; ctx->env[2] = env_rgb[2]; }
+    return VR_OK;
+}
+
+int vr_set_camera(vr_context* ctx, int kind, const float* pos3, const float* view3, const float* right3,
+                  const float* up3, const float* pinhole3) {
+    if (!ctx || !pos3 || !view3 || !right3 || !up3 || (kind != VR_CAMERA_PINHOLE && kind != VR_CAMERA_ORTHOGRAPHIC) ||
+        (kind == VR_CAMERA_PINHOLE && !pinhole3))
+        return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_set_camera: bad arguments");
+    ctx->cam.kind = kind;
+    for (int k = 0; k < 3; ++k) {
+        ctx->cam.pos[k] = pos3[k]; ctx->cam.view[k] = view3[k]; ctx->cam.right[k] = right3[k]; ctx->cam.up[k] = up3[k];
+        ctx->cam.pinhole[k] = pinhole3 ? pinhole3[k] : 0.0f;
+    }
+    ctx->has_camera = true;
+    return VR_OK;
+}
+
+}  // extern "C"
+
+namespace vr {
+// Sigma^-1 / norm / boxes on the device, hierarchy on the host (vr_bvh.cpp), permutation on the device
+int set_gmm_from_device(vr_context* ctx, int n) {
+    ctx->has_gmm = false;
+    ctx->rec_valid = false;
+    const size_t m = (size_t)std::max(n, 1);
+    VR_CUDA(ctx->gauss_orig.ensure(m * 48)); VR_CUDA(ctx->gauss_leaf.ensure(m * 48));
+    VR_CUDA(ctx->perm.ensure(m * 4)); VR_CUDA(ctx->leaf_of_orig.ensure(m * 4));
+    VR_CUDA(ctx->box_lo.ensure(m * 12)); VR_CUDA(ctx->box_hi.ensure(m * 12));
+    VR_CUDA(ctx->nodes.ensure(64));
+    ctx->n = n; ctx->n_nodes = 0;
+    if (n > 0) {
+        // slab tests run on (lo*idir - o*idir): position error ~ 1 ulp of the larger of |lo|, |o|.  Pad for
+        // origins within ~16 units of the coordinate origin (cameras further out are clamped by has_far_origin()).
+        const float pad_abs = 2e-6f * 32.0f;
+        launch_prepare_gaussians(n, ctx->mean3.as<float>(), ctx->cov6.as<float>(), ctx->density.as<float>(),
+                                 ctx->albedo.as<float>(), ctx->gauss_orig.as<float4>(), ctx->box_lo.as<float>(),
+                                 ctx->box_hi.as<float>(), pad_abs, ctx->stream);
+        std::vector<float> lo((size_t)3 * n), hi((size_t)3 * n);
+        VR_CUDA(cudaMemcpyAsync(lo.data(), ctx->box_lo.p, lo.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(hi.data(), ctx->box_hi.p, hi.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        BvhBuildResult bvh;
+        build_bvh(n, lo.data(), hi.data(), &bvh);
+        if (bvh.max_depth > kStackDepth - 2)
+            return fail(ctx, VR_ERR_UNSUPPORTED, "hierarchy deeper than the traversal stack");
+        VR_CUDA(ctx->nodes.ensure(bvh.nodes.size() * sizeof(BvhNode)));
+        VR_CUDA(cudaMemcpyAsync(ctx->nodes.p, bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode), cudaMemcpyHostToDevice, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(ctx->perm.p, bvh.perm.data(), (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        launch_permute_gaussians(n, ctx->gauss_orig.as<float4>(), ctx->perm.as<uint32_t>(), ctx->gauss_leaf.as<float4>(),
+                                 ctx->leaf_of_orig.as<uint32_t>(), ctx->stream);
+        VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        VR_CUDA(cudaGetLastError());
+        ctx->n_nodes = (int)bvh.nodes.size();
+        ctx->bvh_depth = bvh.max_depth;
+    }
+    ctx->has_gmm = true;
+    return VR_OK;
+}
+}  // namespace vr

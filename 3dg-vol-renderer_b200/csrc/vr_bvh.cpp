@@ -1,0 +1,161 @@
+// vr_bvh.cpp -- binned-SAH builder (host).  See vr_bvh.h.
+#include "vr_bvh.h"
+
+#include <algorithm>
+#include <cmath>
+#include <limits>
+
+namespace vr {
+namespace {
+
+struct Box {
+    float lo[3], hi[3];
+    void reset() {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::numeric_limits<float>::infinity(); hi[k] = -lo[k]; }
+    }
+    void grow(const float* l, const float* h) {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], l[k]); hi[k] = std::max(hi[k], h[k]); }
+    }
+    void grow(const Box& b) { grow(b.lo, b.hi); }
+    float half_area() const {
+        float ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
+        if (!(ex >= 0.f) || !(ey >= 0.f) || !(ez >= 0.f)) return 0.f;
+        return ex * ey + ey * ez + ez * ex;
+    }
+};
+
+struct Builder {
+    int n;
+    const float* lo;
+    const float* hi;
+    std::vector<uint32_t>& perm;
+    std::vector<BvhNode>& nodes;
+    int max_depth = 0, max_leaf = 0;
+
+    static constexpr int kBins = 16;
+    static constexpr float kTrav = 1.0f, kIsect = 2.0f;
+
+    Box range_box(int first, int count) const {
+        Box b; b.reset();
+        for (int i = first; i < first + count; ++i) b.grow(lo + 3 * perm[i], hi + 3 * perm[i]);
+        return b;
+    }
+    float centroid(uint32_t g, int axis) const { return 0.5f * (lo[3 * g + axis] + hi[3 * g + axis]); }
+
+    static int leaf_code(int first, int count) { return ~((first << 3) | (count - 1)); }
+
+    void set_child_box(BvhNode& nd, int c, const Box& b) {
+        if (c == 0) {
+            nd.c0x[0] = b.lo[0]; nd.c0x[1] = b.hi[0]; nd.c0y[0] = b.lo[1]; nd.c0y[1] = b.hi[1];
+            nd.c0z[0] = b.lo[2]; nd.c0z[1] = b.hi[2];
+        } else {
+            nd.c1x[0] = b.lo[0]; nd.c1x[1] = b.hi[0]; nd.c1y[0] = b.lo[1]; nd.c1y[1] = b.hi[1];
+            nd.c1z[0] = b.lo[2]; nd.c1z[1] = b.hi[2];
+        }
+    }
+
+    // chooses a split of [first, first+count); returns the size of the left part (0 = make a leaf)
+    int split(int first, int count, const Box& box) {
+        Box cb; cb.reset();
+        for (int i = first; i < first + count; ++i) {
+            float c[3] = {centroid(perm[i], 0), centroid(perm[i], 1), centroid(perm[i], 2)};
+            cb.grow(c, c);
+        }
+        float best_cost = std::numeric_limits<float>::infinity();
+        int best_axis = -1, best_bin = -1;
+        for (int axis = 0; axis < 3; ++axis) {
+            float cmin = cb.lo[axis], cext = cb.hi[axis] - cb.lo[axis];
+            if (!(cext > 0.f)) continue;
+            Box bb[kBins]; int bc[kBins];
+            for (int b = 0; b < kBins; ++b) { bb[b].reset(); bc[b] = 0; }
+            float scale = kBins / cext;
+            for (int i = first; i < first + count; ++i) {
+                uint32_t g = perm[i];
+                int b = std::min(kBins - 1, std::max(0, (int)((centroid(g, axis) - cmin) * scale)));
+                bb[b].grow(lo + 3 * g, hi + 3 * g); bc[b]++;
+            }
+            float right_area[kBins]; int right_cnt[kBins];
+            Box acc; acc.reset(); int cnt = 0;
+            for (int b = kBins - 1; b > 0; --b) { acc.grow(bb[b]); cnt += bc[b]; right_area[b] = acc.half_area(); right_cnt[b] = cnt; }
+            acc.reset(); cnt = 0;
+            for (int b = 0; b < kBins - 1; ++b) {
+                acc.grow(bb[b]); cnt += bc[b];
+                if (cnt == 0 || right_cnt[b + 1] == 0) continue;
+                float cost = acc.half_area() * cnt + right_area[b + 1] * right_cnt[b + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = b; }
+            }
+        }
+        float parent_area = box.half_area();
+        if (best_axis >= 0 && count <= kMaxLeaf) {
+            float split_cost = kTrav + kIsect * best_cost / std::max(parent_area, 1e-30f);
+            if (split_cost >= kIsect * count) return 0;  // cheaper as a leaf
+        }
+        if (best_axis < 0) {
+            if (count <= kMaxLeaf) return 0;
+            // all centroids coincide: median split by index to bound the leaf size
+            return count / 2;
+        }
+        float cmin = cb.lo[best_axis], scale = kBins / (cb.hi[best_axis] - cb.lo[best_axis]);
+        int axis = best_axis, bin = best_bin;
+        auto mid = std::stable_partition(perm.begin() + first, perm.begin() + first + count, [&](uint32_t g) {
+            int b = std::min(kBins - 1, std::max(0, (int)((centroid(g, axis) - cmin) * scale)));
+            return b <= bin;
+        });
+        int left = (int)(mid - (perm.begin() + first));
+        if (left == 0 || left == count) return count <= kMaxLeaf ? 0 : count / 2;
+        return left;
+    }
+
+    // builds the subtree over [first, first+count) (count >= 2, to be split) into nodes[ni]
+    void build_node(int ni, int first, int count, int left, int depth) {
+        max_depth = std::max(max_depth, depth);
+        int parts[2][2] = {{first, left}, {first + left, count - left}};
+        for (int c = 0; c < 2; ++c) {
+            int f = parts[c][0], k = parts[c][1];
+            Box b = range_box(f, k);
+            set_child_box(nodes[ni], c, b);
+            int l = (k >= 2) ? split(f, k, b) : 0;
+            if (l == 0) {
+                nodes[ni].child[c] = leaf_code(f, k);
+                max_leaf = std::max(max_leaf, k);
+            } else {
+                int ci = (int)nodes.size();
+                nodes.push_back(BvhNode{});
+                nodes[ni].child[c] = ci;
+                build_node(ci, f, k, l, depth + 1);
+            }
+        }
+    }
+};
+
+}  // namespace
+
+void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
+    out->nodes.clear();
+    out->perm.resize((size_t)std::max(n, 0));
+    out->max_depth = 0; out->max_leaf = 0;
+    if (n <= 0) return;
+    for (int i = 0; i < n; ++i) out->perm[i] = (uint32_t)i;
+    Builder b{n, lo, hi, out->perm, out->nodes};
+    out->nodes.reserve((size_t)n);
+    out->nodes.push_back(BvhNode{});
+    Box root = b.range_box(0, n);
+    int left = (n >= 2) ? b.split(0, n, root) : 0;
+    if (left == 0) {
+        // a single leaf: child 0 = everything (split into runs of <= 8 is not needed: n <= kMaxLeaf here),
+        // child 1 = empty box that no ray enters
+        BvhNode& nd = out->nodes[0];
+        b.set_child_box(nd, 0, root);
+        Box empty; empty.reset();
+        b.set_child_box(nd, 1, empty);
+        nd.child[0] = Builder::leaf_code(0, n);
+        nd.child[1] = Builder::leaf_code(0, 1);
+        b.max_leaf = n;
+    } else {
+        b.build_node(0, 0, n, left, 1);
+    }
+    out->max_depth = b.max_depth;
+    out->max_leaf = b.max_leaf;
+}
+
+}  // namespace vr

@@ -1,0 +1,36 @@
+// vr_bvh.h -- host-side builder of the culling hierarchy over the 3-sigma ellipsoids.
+//
+// Replaces GaussianMixtureModel::BuildBVH / SubdivideNode (gmm.h:231-446) as a *culling* structure
+// only: the quadric test (gaussian.h:126-164) still decides every overlap, so the set of
+// components a ray gathers is the reference's; the hierarchy itself is free to differ.  Ours is a
+// binned-SAH binary tree over tight boxes (half extent 3*sqrt(Sigma_kk), padded), flattened so
+// that one 64-byte node holds BOTH children's boxes (four 128-bit loads per traversal step), with
+// the Gaussians permuted into leaf order so that a leaf is a contiguous run of 48-byte records.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace vr {
+
+struct BvhNode {       // 64 B, 16-byte aligned, read as 4 x float4
+    float c0x[2], c0y[2];  // child 0: (lo.x, hi.x, lo.y, hi.y)
+    float c1x[2], c1y[2];  // child 1
+    float c0z[2], c1z[2];  // (lo0.z, hi0.z, lo1.z, hi1.z)
+    int32_t child[2];      // >= 0: node index; < 0: leaf, ~((first << 3) | (count - 1))
+    int32_t pad[2];
+};
+static_assert(sizeof(BvhNode) == 64, "BvhNode must be 64 bytes");
+
+struct BvhBuildResult {
+    std::vector<BvhNode> nodes;     // nodes[0] is the root (always present when n > 0)
+    std::vector<uint32_t> perm;     // leaf order -> original Gaussian index
+    int max_depth = 0;
+    int max_leaf = 0;
+};
+
+constexpr int kMaxLeaf = 4;         // <= 8 by the 3-bit count field
+
+// lo/hi: 3*n floats each (per-Gaussian boxes).  Deterministic.
+void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out);
+
+}  // namespace vr

@@ -1,0 +1,83 @@
+// vr_context.h -- the opaque context behind the C-ABI (include/volrender.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/volrender.h"
+#include "vr_internal.h"
+
+namespace vr {
+
+// grow-only device buffer
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t need) {
+        if (need <= bytes) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; bytes = 0; }
+        cudaError_t e = cudaMalloc(&p, need);
+        if (e == cudaSuccess) bytes = need;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct SfdState;  // vr_inverse.cu
+
+}  // namespace vr
+
+struct vr_context {
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::string err = "";
+
+    // ---- Gaussian mixture
+    bool has_gmm = false;
+    int n = 0, n_nodes = 0, bvh_depth = 0;
+    vr::DevBuf mean3, cov6, density, albedo;       // inputs as given (original order)
+    vr::DevBuf gauss_orig, gauss_leaf, nodes, perm, leaf_of_orig, box_lo, box_hi;
+    // ---- sphere mixture
+    bool has_smm = false;
+    int n_spheres = 0;
+    vr::DevBuf spheres;                            // 6 floats per sphere: c3, r, sigma_a, sigma_s
+    // ---- lights / camera
+    int nl = 0;
+    vr::DevBuf lpos, lint;
+    float env[3] = {0.53f, 0.81f, 0.92f};          // scene.h:29
+    bool has_camera = false;
+    vr::CameraPod cam{};
+    // ---- render state
+    vr::DevBuf image, sampleL, counters, stats, overflow_list, arena, record_bits, scratch;
+    int img_w = 0, img_h = 0;
+    int rec_w = 0, rec_h = 0, rec_words = 0, rec_n = 0;
+    bool rec_valid = false;
+    unsigned long long* h_stats = nullptr;         // pinned
+    unsigned int* h_counters = nullptr;            // pinned
+    // ---- options
+    int hit_capacity = 0;                          // 0 = min(n, 4096)
+    double max_pass_samples = 268435456.0;         // 2^28 samples = 4 GiB of per-sample radiance
+    int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
+    // ---- inverse
+    vr::SfdState* sfd = nullptr;
+
+    vr::SceneDev scene_dev() const;
+};
+
+namespace vr {
+int fail(vr_context* c, int code, const std::string& msg);
+int cuda_fail(vr_context* c, cudaError_t e, const char* what);
+int render_device_impl(vr_context* c, const vr_render_params* p, vr_render_stats* st);
+int set_gmm_from_device(vr_context* c, int n);  // mean3/cov6/density/albedo device buffers already filled
+void sfd_destroy(vr_context* c);
+}  // namespace vr
+
+#define VR_CUDA(call)                                                        \
+    do {                                                                     \
+        cudaError_t _e = (call);                                             \
+        if (_e != cudaSuccess) return vr::cuda_fail(ctx, _e, #call);         \
+    } while (0)

@@ -1,0 +1,67 @@
+// vr_internal.h -- launch-level interface between the C-ABI (vr_api.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "vr_device.cuh"
+
+namespace vr {
+
+// statistics counters accumulated by the path kernels (device array of kNumStats u64)
+enum { ST_SCATTER_RAYS = 0, ST_SHADOW_RAYS, ST_HITS, ST_OVERFLOW, ST_ERRORS, kNumStats };
+
+struct RenderArgs {
+    SceneDev scene;
+    CameraPod cam;
+    int W, H, spp, nsq;
+    int integrator;        // 0 single scatter, 1 multi scatter
+    int solver, min_bounces;
+    int x0, y0, win_w;     // owned pixel p -> x = x0 + p % win_w, y = y0 + (p / win_w) * part_count + part_rank
+    int part_rank, part_count;
+    unsigned int pixel_base;      // first owned pixel of this pass
+    unsigned int work_count;      // samples in this pass = pass pixels * spp
+    unsigned int* counter;        // work-fetch counter of this pass
+    const unsigned int* worklist; // nullptr: work ids 0..work_count-1; else ids taken from this list (re-trace kernel)
+    float4* sampleL;              // per-sample radiance of this pass, [pass pixel][si]
+    uint32_t* record_bits;        // per image pixel bitmap of contributing Gaussians (or nullptr)
+    int record_words;
+    unsigned long long* stats;
+    unsigned int* overflow_list;
+    unsigned int* overflow_count;
+    float* arena;                 // re-trace kernel: kArenaFields * arena_cap * 32 floats per warp
+    int arena_cap;
+};
+
+constexpr int kBlockThreads = 128;
+constexpr int kLocalCap = 32;        // overlaps kept in local memory by the main kernel
+
+// grid sizes chosen by occupancy query (persistent kernels)
+int path_kernel_blocks_per_sm(bool arena);
+void launch_path_kernel(const RenderArgs& a, int blocks, bool arena, cudaStream_t s);
+// mean over spp in sample order (integrator.h:702-706), writes image[3*(y*W+x)]
+void launch_pixel_reduce(const RenderArgs& a, unsigned int pass_pixels, float* image, cudaStream_t s);
+
+void launch_transmittance(const SceneDev& S, int n, const float* o3, const float* d3, const float* tmax, float* out,
+                          cudaStream_t s);
+
+// known-answer kernels
+void launch_kat_pcg(int n, const int32_t* xysi, uint64_t* seed, uint32_t* u32x4, float* unix4, cudaStream_t s);
+void launch_kat_gaussian(const SceneDev& S, const uint32_t* leaf_of_orig, int n, const float* o3, const float* d3,
+                         const int32_t* gidx, const float* frac, int32_t* hit, float* t0, float* t1, float* tau,
+                         float* mu, int32_t* ok, float* tsol, cudaStream_t s);
+void launch_kat_camera(const CameraPod& cam, int n, const float* uv, float* o3, float* d3, cudaStream_t s);
+void launch_kat_events(const SceneDev& S, const float* o3, const float* d3, int cap, float* arena, float* t,
+                       int32_t* entering, uint32_t* index, int* n_events, cudaStream_t s);
+void launch_kat_libm(int n, const float* x, float* s_out, float* c_out, float* a_out, cudaStream_t s);
+void launch_kat_erfinv(int n, const double* x, double* y, cudaStream_t s);
+
+// scene preparation: cov6 -> Sigma^-1, norm, padded 3-sigma boxes (gaussian.h:52-56,304-319)
+void launch_prepare_gaussians(int n, const float* mean3, const float* cov6, const float* density, const float* albedo,
+                              float4* gauss_orig_order, float* box_lo, float* box_hi, float pad_abs, cudaStream_t s);
+void launch_permute_gaussians(int n, const float4* src, const uint32_t* perm, float4* dst, uint32_t* leaf_of_orig,
+                              cudaStream_t s);
+// apply_params_to_gmm_local math (gmm.h:634-674)
+void launch_unpack_params(int n, const float* params11, float* mean3, float* cov6, float* density, float* albedo,
+                          cudaStream_t s);
+
+}  // namespace vr

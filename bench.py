@@ -1,0 +1,299 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 volume-path renderer.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun, one rank per GPU)
+    python bench.py --impl reference ...                      (the reference's own CPU renderer, host cores)
+
+Metric (BASELINE.json): Msamples/s, 1 sample = one camera path (x, y, si) with all its bounces and
+shadow rays.  Workload at every N: config C2 of SURVEY.md 8(d) -- seeded make_nonuniform_random scene,
+10 000 Gaussians, 1024^2, 256 spp, MultiScatterGaussians(min_bounces 5), pinhole camera of
+tests/main.cpp.  One step = one full render of that image; with N GPUs the image rows are interleaved
+over the ranks (strong scaling: total work fixed), no data-path collective.
+
+value  = samples of all ranks / (max over ranks of the device time of K steps), scene resident in HBM.
+e2e    = same through the host-buffer C-ABI call a user makes: vr_set_gmm (scene H2D + hierarchy
+         build) + vr_render (image rows D2H into pinned host memory) every step.
+roofline = FP32 issue roofline of SURVEY.md 8(d) (this path has no dense contraction and ~0 bytes of
+         compulsory HBM traffic per sample, so neither "hbm" nor "tensor" bounds it): algorithmic
+         FLOP per sample measured by the oracle's counters on this scene x samples per launch /
+         measured launch time, against SMs x 128 lanes x 2 x the SM clock seen under load.
+cpu_baseline = the reference renderer itself (oracle/_ref/ref_driver: the untouched reference headers
+         compiled by oracle/Makefile) on all host cores, bounded sample of the same scene/camera.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib.util
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ENV = (0.53, 0.81, 0.92)
+CONFIGS = {
+    # name: (n_gaussians, seed, nonuniform, W, H, spp, integrator)
+    "c1": dict(n=1000, seed=1, nonuniform=False, W=512, H=512, spp=64, integrator="ss",
+               label="C1: make_random 1k Gaussians, 512^2, 64 spp, FreeFlightGaussians"),
+    "c2": dict(n=10000, seed=2, nonuniform=True, W=1024, H=1024, spp=256, integrator="ms",
+               label="C2: make_nonuniform_random 10k Gaussians, 1024^2, 256 spp, MultiScatterGaussians"),
+}
+
+
+def _pkg(name):
+    key = "volrender_b200_" + name
+    if key in sys.modules:
+        return sys.modules[key]
+    spec = importlib.util.spec_from_file_location(key, os.path.join(ROOT, "3dg-vol-renderer_b200", name + ".py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[key] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def make_scene(cfg):
+    sg = _pkg("scenegen")
+    return sg.generate(cfg["n"], cfg["seed"], nonuniform=cfg["nonuniform"])
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the reference itself (oracle/_ref/ref_driver) or, if it is absent, the oracle port
+# ----------------------------------------------------------------------------------------------
+def cpu_render_sample(cfg, scene, seconds_target=15.0):
+    """Times a bounded sample of the workload on the host cores.  Returns dict(value Msamples/s, ...)."""
+    from oracle import oracle_binding as ob
+    ob.build()
+    integ = cfg["integrator"]
+    cores = os.cpu_count() or 1
+    if ob.have_ref():
+        sg = _pkg("scenegen")
+        tmp = tempfile.mkdtemp()
+        path = os.path.join(tmp, "scene.txt")
+        sg.write_gmm(path, scene)
+        kw = dict(scene=path, integrator=integ, cam="pinhole", pos="0,1,6", look="0,1,0", fov="0.78539816339")
+        probe = ob.run_ref("render", w=64, h=64, spp=4, **kw)
+        rate = max(probe["msamples_per_s"], 1e-6) * 1e6
+        side = int(min(cfg["W"], max(64, (seconds_target * rate / 16) ** 0.5)))
+        r = ob.run_ref("render", w=side, h=side, spp=16, repeat=1, **kw)
+        return dict(value=r["msamples_per_s"], unit="Msamples/s", cores=int(r["threads"]), kind="reference",
+                    sample=f"same scene and camera at {side}x{side}, 16 spp ({side * side * 16} samples, "
+                           f"{r['time_s']:.1f} s), unmodified reference headers via oracle/_ref/ref_driver")
+    gm = ob.Gmm(scene)
+    cam = ob.make_camera("pinhole", (0, 1, 6), look=(0, 1, 0))
+    it = ob.INTEGRATOR_SS if integ == "ss" else ob.INTEGRATOR_MS
+    t0 = time.perf_counter(); ob.render(gm, scene["lights"], ENV, cam, it, 64, 64, 4); dt = time.perf_counter() - t0
+    rate = 64 * 64 * 4 / max(dt, 1e-6)
+    side = int(min(cfg["W"], max(64, (seconds_target * rate / 16) ** 0.5)))
+    t0 = time.perf_counter(); ob.render(gm, scene["lights"], ENV, cam, it, side, side, 16); dt = time.perf_counter() - t0
+    return dict(value=side * side * 16 / dt * 1e-6, unit="Msamples/s", cores=int(ob.lib().vo_num_threads()), kind="port",
+                sample=f"same scene and camera at {side}x{side}, 16 spp ({dt:.1f} s), C port oracle/volpath_oracle.c")
+
+
+def algorithmic_flop_per_sample(cfg, scene):
+    """F_alg = 74 H + 44 OD + 28 MU + 40 SA + 40 V FLOP per sample, with the counts
+    measured by the oracle on this exact scene/camera (a 64x64, 16 spp sample of the image)."""
+    from oracle import oracle_binding as ob
+    gm = ob.Gmm(scene)
+    cam = ob.make_camera("pinhole", (0, 1, 6), look=(0, 1, 0))
+    it = ob.INTEGRATOR_SS if cfg["integrator"] == "ss" else ob.INTEGRATOR_MS
+    ob.counters_reset()
+    ob.render(gm, scene["lights"], ENV, cam, it, 64, 64, 16)
+    c = ob.counters()
+    n = max(c["paths"], 1)
+    per = {k: v / n for k, v in c.items()}
+    flop = 74 * per["hits"] + 44 * per["optical_depth"] + 28 * per["mu_t"] + 40 * per["analytic"] + 40 * per["scatter_rays"]
+    return flop, per
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.index = index; self.rows = []; self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True); self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 7 and r[3 + k].lower().startswith("active") for r in self.rows)]
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None, reasons=reasons,
+                    samples=len(sm))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--spp", type=int, default=0, help="override spp (perfect square) for quick runs")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    cfg = dict(CONFIGS[a.config])
+    if a.spp:
+        cfg["spp"] = a.spp
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    workload = f"{cfg['label']}; seed {cfg['seed']}; pinhole (0,1,6)->(0,1,0) fov pi/4; 3 point lights + env"
+    scene = make_scene(cfg)
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        vals = []
+        for _ in range(max(1, a.warmup // 3)):   # warm the page cache / thread pool once
+            cpu_render_sample(cfg, scene, seconds_target=2.0)
+        last = None
+        for _ in range(a.steps):
+            last = cpu_render_sample(cfg, scene, seconds_target=max(4.0, 60.0 / max(a.steps, 1)))
+            vals.append(last["value"])
+        v = float(np.mean(vals))
+        cb = dict(last); cb["value"] = v
+        print(json.dumps({"impl": "reference", "metric": "Msamples/sec", "value": v, "unit": "Msamples/s", "n_gpus": a.gpus,
+                          "steps": a.steps, "warmup": a.warmup, "ms_per_step": None, "higher_is_better": True,
+                          "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                          "config": {"workload": workload, "note": "CPU reference, each step a bounded sample: " + cb["sample"]},
+                          "cpu_baseline": cb, "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0,
+                                                      "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    vr = _pkg("volrender")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = vr.Context(local_rank)
+    cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
+    ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cam); ctx.set_gmm(scene)
+    integ = vr.INTEGRATOR_SS if cfg["integrator"] == "ss" else vr.INTEGRATOR_MS
+    W, H, spp = cfg["W"], cfg["H"], cfg["spp"]
+    p = vr.Context.params(integ, W, H, spp, part=(rank, world))
+    owned_rows = len(range(rank, H, world))
+    total_samples = W * H * spp
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- value: scene resident, result left in HBM --------------------------------------------
+    for _ in range(a.warmup):
+        ctx.render_device(p)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t_wall = time.perf_counter()
+    dev_ms = 0.0; kern_ms = 0.0; launches = 0; stats = None
+    for _ in range(a.steps):
+        flush.zero_()                      # L2 flush between timed iterations
+        torch.cuda.synchronize()
+        stats = ctx.render_device(p)
+        dev_ms += stats["total_ms"]; kern_ms += stats["kernel_ms"]; launches += stats["kernel_launches"]
+    barrier()
+    wall_ms = (time.perf_counter() - t_wall) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = max_over_ranks(dev_ms); wall_ms = max_over_ranks(wall_ms); kern_ms_max = max_over_ranks(kern_ms)
+    ms_per_step = dev_ms / a.steps
+    value = total_samples / (ms_per_step * 1e-3) * 1e-6
+
+    # ---- e2e: host buffers through the C-ABI, copies inside the timed region --------------------
+    host_img = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    pinned = {k: torch.from_numpy(np.ascontiguousarray(scene[k], np.float32)).pin_memory() for k in ("mean", "cov6", "density", "albedo")}
+    pscene = {k: v.numpy() for k, v in pinned.items()}
+    h2d = sum(v.numel() * 4 for v in pinned.values())
+    d2h = owned_rows * W * 3 * 4
+    for _ in range(min(a.warmup, 2)):
+        ctx.set_gmm(pscene); ctx.render_into(p, host_img.data_ptr())
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        ctx.set_gmm(pscene)
+        ctx.render_into(p, host_img.data_ptr())
+        _ = float(host_img[rank % H, 0, 0])    # the result is read on the host
+    barrier()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / a.steps
+    e2e_value = total_samples / (e2e_ms * 1e-3) * 1e-6
+    ctx.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+
+    # ---- roofline of the dominant kernel (path_kernel) ------------------------------------------
+    flop_per_sample, per = algorithmic_flop_per_sample(cfg, scene)
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        peaks = {}
+    sm_clock = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    n_sms = 148
+    peak_tflops = n_sms * 128 * 2 * sm_clock * 1e6 * 1e-12
+    samples_per_launch = total_samples / world          # this rank's share; one path-kernel launch per pass
+    launch_ms = kern_ms_max / a.steps
+    achieved = flop_per_sample * samples_per_launch / (launch_ms * 1e-3) * 1e-12
+    roof = dict(bound="fp32", achieved=achieved, peak=peak_tflops, unit="TFLOP/s", frac=achieved / peak_tflops, traffic=None,
+                note=f"algorithmic FP32 FLOP/sample {flop_per_sample:.0f} (oracle counters: " +
+                     ", ".join(f"{k} {v:.2f}" for k, v in per.items() if k != "paths") +
+                     f"); peak = {n_sms} SMs x 128 x 2 x {sm_clock:.0f} MHz (clock sampled under load); "
+                     f"hbm for context: {3 * 4 * W * H / world / (launch_ms * 1e-3) * 1e-9:.2f} GB/s compulsory vs "
+                     f"{peaks.get('hbm_gbs', 6650.0)} GB/s measured peak")
+    cpu = None
+    if not a.no_cpu_baseline:
+        cpu = cpu_render_sample(cfg, scene)
+    print(json.dumps({
+        "metric": "Msamples/sec", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms_per_step, "wall_ms_per_step": wall_ms / a.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload, "image": [W, H], "spp": spp, "partition": f"rows interleaved over {world} rank(s)",
+                   "l2": "256 MiB device buffer zeroed between timed iterations (L2 flush)"},
+        "e2e": {"value": e2e_value, "unit": "Msamples/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+        "rays": {k: stats[k] for k in ("samples", "scatter_rays", "shadow_rays", "hits", "overflow_samples")},
+    }))
+
+
+if __name__ == "__main__":
+    main()

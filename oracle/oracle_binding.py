@@ -80,6 +80,7 @@ def lib():
     L.vo_pixel_samples.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(Camera), C.c_int, C.c_int,
                                    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
     L.vo_num_threads.restype = C.c_int
+    L.vo_counters_get.argtypes = [np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")]
     L.vo_pixel_losses.argtypes = [_f32p, _f32p, C.c_int, _f32p]
     L.vo_sfd_fdiff.argtypes = [C.c_int, C.c_int, _i32p, _u32p, _i32p, _u32p, C.c_int, _f32p, _f32p, _f64p]
     L.vo_sfd_accumulate.argtypes = [C.c_int, _f64p, _i8p, _f32p, _f64p]
@@ -159,6 +160,21 @@ def render(gmm: Gmm, lights, env, cam: Camera, integrator: int, W: int, H: int, 
     lib().vo_render(gmm.h, lights.shape[0], lpos, lint, _c(env), C.byref(cam), integrator, solver, W, H, spp,
                     min_bounces, x0, y0, x1, y1, out.reshape(-1), pc, pi, record_cap)
     return (out, cnt, idx) if record_cap > 0 else out
+
+
+COUNTER_NAMES = ("scatter_rays", "shadow_rays", "hits", "optical_depth", "mu_t", "analytic", "newton", "bisection",
+                 "paths")
+
+
+def counters_reset():
+    lib().vo_counters_reset()
+
+
+def counters() -> dict:
+    """algorithmic-work counters accumulated by render() since counters_reset()"""
+    c = np.zeros(len(COUNTER_NAMES), np.uint64)
+    lib().vo_counters_get(c)
+    return dict(zip(COUNTER_NAMES, (int(v) for v in c)))
 
 
 def pixel_samples(gmm: Gmm, lights, env, cam, integrator, W, H, spp, x, y, min_bounces=5,

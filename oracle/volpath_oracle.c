@@ -38,6 +38,21 @@
 #define VO_PI 3.14159265358979323846 /* std::numbers::pi (double) */
 #define VO_EXPORT __attribute__((visibility("default")))
 
+/* algorithmic-work counters: per-thread, folded into totals at the end of vo_render.
+ * [0] free-flight rays V  [1] shadow rays  [2] ray-Gaussian overlaps H on free-flight rays
+ * [3] optical_depth evaluations OD  [4] mu_t evaluations MU  [5] analytic solves SA
+ * [6] Newton solves  [7] bisection solves  [8] camera paths */
+enum { VO_C_V = 0, VO_C_SHADOW, VO_C_H, VO_C_OD, VO_C_MU, VO_C_SA, VO_C_NEWTON, VO_C_BISECT, VO_C_PATHS, VO_NCOUNT };
+static __thread uint64_t vo_cnt[VO_NCOUNT];
+static uint64_t vo_cnt_total[VO_NCOUNT];
+VO_EXPORT void vo_counters_reset(void) { memset(vo_cnt_total, 0, sizeof(vo_cnt_total)); }
+VO_EXPORT void vo_counters_get(uint64_t* out) { memcpy(out, vo_cnt_total, sizeof(vo_cnt_total)); }
+static void vo_counters_fold(void) {
+#pragma omp critical(vo_counters)
+    { for (int i = 0; i < VO_NCOUNT; ++i) vo_cnt_total[i] += vo_cnt[i]; }
+    memset(vo_cnt, 0, sizeof(vo_cnt));
+}
+
 /* ------------------------------------------------------------------------- */
 /* RNG -- include/rng.h:13-57                                                 */
 /* ------------------------------------------------------------------------- */
@@ -157,6 +172,7 @@ static inline v3 mat_mul(const float* m, v3 v) {
                    m[6] * v.x + (m[7] * v.y + m[8] * v.z));
 }
 static inline float gauss_mu_t(const vo_gauss* g, v3 x) { /* gaussian.h:111-117 */
+    ++vo_cnt[VO_C_MU];
     v3 d = v3_sub(x, v3_make(g->mean[0], g->mean[1], g->mean[2]));
     /* -0.5f * d^T * inv_cov * d parses as ((-0.5f d^T) * M) * d */
     v3 h = v3_make(-0.5f * d.x, -0.5f * d.y, -0.5f * d.z);
@@ -187,6 +203,7 @@ static inline int gauss_intersect(const vo_gauss* g, const vo_ray* ray, float* t
 }
 static inline float gauss_optical_depth(const vo_gauss* g, const vo_ray* ray, float t0, float t1) {
     /* gaussian.h:208-231, with its float/double mix */
+    ++vo_cnt[VO_C_OD];
     v3 p = v3_sub(ray->o, v3_make(g->mean[0], g->mean[1], g->mean[2]));
     v3 Md = mat_mul(g->inv, ray->d);
     v3 Mp = mat_mul(g->inv, p);
@@ -201,6 +218,7 @@ static inline float gauss_optical_depth(const vo_gauss* g, const vo_ray* ray, fl
 }
 static inline int gauss_solve_t(const vo_gauss* g, const vo_ray* ray, float t0, float tb, float target_tau,
                                 float* t_out) { /* gaussian.h:235-297 (all double) */
+    ++vo_cnt[VO_C_SA];
     v3 p = v3_sub(ray->o, v3_make(g->mean[0], g->mean[1], g->mean[2]));
     v3 Md = mat_mul(g->inv, ray->d);
     v3 Mp = mat_mul(g->inv, p);
@@ -371,6 +389,7 @@ typedef struct { int* s; int cap; } vo_stack;
 static void gmm_intersect_events(const vo_gmm* m, const vo_ray* ray, vo_events* ev, vo_stack* st) {
     /* gmm.h:457-515 */
     ev->n = 0;
+    ++vo_cnt[VO_C_V];
     if (m->n == 0) return;
     if (st->cap < m->n_nodes + 2) { st->cap = m->n_nodes + 2; st->s = (int*)realloc(st->s, (size_t)st->cap * sizeof(int)); }
     int sp = 0;
@@ -402,11 +421,13 @@ static void gmm_intersect_events(const vo_gmm* m, const vo_ray* ray, vo_events* 
             }
         }
     }
+    vo_cnt[VO_C_H] += (uint64_t)ev->n / 2;
     if (ev->n > 1) qsort(ev->e, (size_t)ev->n, sizeof(vo_event), event_cmp);
 }
 
 static float gmm_transmittance_up_to(const vo_gmm* m, const vo_ray* ray, float tmax, vo_stack* st) {
     /* gmm.h:517-578: unsorted sum of clipped optical depths, double accumulator */
+    ++vo_cnt[VO_C_SHADOW];
     if (tmax <= 0.0f) return 1.0f;
     if (m->n == 0) return 1.0f;
     double sum = 0.0;
@@ -465,6 +486,7 @@ static inline float clampf(float v, float lo, float hi) { return (v < lo) ? lo :
 
 static float solve_bisection(const vo_gmm* m, const vo_ray* ray, float ta, float tb, const uint32_t* act, int na,
                              float target) { /* distance_solvers.h:25-57 (15 iters, tol 1e-6) */
+    ++vo_cnt[VO_C_BISECT];
     float a = ta, b = tb;
     for (int i = 0; i < 15; ++i) {
         float mid = 0.5f * (a + b);
@@ -485,6 +507,7 @@ static float newton_f(const vo_gmm* m, const vo_ray* ray, float ta, float b, con
 }
 static float solve_newton(const vo_gmm* m, const vo_ray* ray, float ta, float tb, const uint32_t* act, int na,
                           float target) { /* distance_solvers.h:62-127 (8 iters, tol 1e-6) */
+    ++vo_cnt[VO_C_NEWTON];
     const float tol = 1e-6f;
     float a = ta, b = tb;
     float t = 0.5f * (a + b);
@@ -834,6 +857,7 @@ VO_EXPORT void vo_render(const vo_gmm* m, int nl, const float* lpos, const float
             for (int x = x0; x < x1; ++x) {
                 float pix[3] = {0.0f, 0.0f, 0.0f};
                 s.n_pix = 0;
+                vo_cnt[VO_C_PATHS] += (uint64_t)spp;
                 for (int si = 0; si < spp; ++si) {
                     float Ls[3];
                     if (integrator == VO_INTEGRATOR_SS) ss_sample(m, &L, cam, x, y, si, spp, W, H, solver, &s, Ls);
@@ -849,6 +873,7 @@ VO_EXPORT void vo_render(const vo_gmm* m, int nl, const float* lpos, const float
             }
         }
         scratch_free(&s);
+        vo_counters_fold();
     }
 }
 /* per-sample radiance of one pixel (debug aid for single-sample flip attribution) */

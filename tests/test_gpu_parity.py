@@ -1,0 +1,402 @@
+"""GPU parity tests proper: the CUDA path, called through the C-ABI (include/volrender.h), against
+(a) golden vectors emitted by the unmodified reference and (b) the pinned C oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star): per-pixel radiance 1e-4 relative with identical sample
+streams, analytic transmittance 1e-5; integer work (PCG stream, recorded sets) bit-exact.  A small
+fraction of pixels may differ through single-sample decision flips: the bound is on
+the fraction of pixels inside the tolerance, stated in each test."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from conftest import CAMS, ENV, SCENES, decode_record, load_pkg_module
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def vr():
+    mod = load_pkg_module("volrender")
+    if not os.path.exists(mod.LIB_PATH):
+        mod.build()
+    return mod
+
+
+@pytest.fixture(scope="module")
+def ctx(vr):
+    c = vr.Context(0)   # raises without a GPU: no fallback
+    yield c
+    c.close()
+
+
+def cam_dict(ob, vr, name):
+    """the oracle's camera struct -> the C-ABI camera arguments (bitwise the same camera)"""
+    c = CAMS[name]
+    oc = ob.make_camera(c["kind"], c["pos"], look=c["look"], fov=c["fov"])
+    d = dict(kind=int(oc.kind), pos=np.array(oc.pos[:], np.float32), view=np.array(oc.view[:], np.float32),
+             right=np.array(oc.right[:], np.float32), up=np.array(oc.up[:], np.float32),
+             pinhole=np.array(oc.pinhole[:], np.float32))
+    return oc, d
+
+
+def load_scene(scenegen, name):
+    return scenegen.load_gmm(os.path.join(SCENES, name + ".txt"))
+
+
+def setup(ctx, ob, vr, scenegen, scene_name, cam_name, scene=None):
+    scene = scene if scene is not None else load_scene(scenegen, scene_name)
+    oc, cd = cam_dict(ob, vr, cam_name)
+    ctx.set_gmm(scene)
+    ctx.set_lights(scene["lights"], ENV)
+    ctx.set_camera(cd)
+    return scene, oc
+
+
+def frac_within(a, b, rtol, atol=1e-6):
+    return float((np.abs(a - b) <= atol + rtol * np.abs(b)).all(axis=-1).mean())
+
+
+# ------------------------------------------------------------------------------------------------
+# known-answer vectors from the reference
+# ------------------------------------------------------------------------------------------------
+def test_pcg_stream_bit_exact(ctx, golden):
+    rec = golden["kat/rand50/1"].reshape(-1, 13)
+    seed, u32, uni = ctx.kat_pcg(rec[:, 0:3].astype(np.int32))
+    assert np.array_equal(seed, rec[:, 3].astype(np.uint64) | (rec[:, 4].astype(np.uint64) << np.uint64(32)))
+    assert np.array_equal(u32, rec[:, 5:9])
+    assert np.array_equal(uni.view(np.uint32), rec[:, 9:13])
+
+
+def test_libm_ports_match_host_libm(ctx):
+    """sinf/cosf/acosf are ports of the host's glibc algorithms (vr_math.cuh): bit-exact on the
+    arguments the renderer produces (theta in [0,2pi), phi in [0,pi], x in [-1,1])."""
+    libm = C.CDLL("libm.so.6")
+    for f in (libm.sinf, libm.cosf, libm.acosf):
+        f.restype = C.c_float; f.argtypes = [C.c_float]
+    rs = np.random.RandomState(3)
+    xi = (rs.randint(0, 1 << 24, size=20000).astype(np.float32) / np.float32(16777216.0)).astype(np.float32)
+    theta = (np.float64(6.283185307179586) * xi.astype(np.float64)).astype(np.float32)
+    x = (np.float32(1.0) - np.float32(2.0) * xi).astype(np.float32)
+    s, c, _ = ctx.kat_libm(theta)
+    _, _, a = ctx.kat_libm(x)
+    hs = np.array([libm.sinf(float(v)) for v in theta], np.float32)
+    hc = np.array([libm.cosf(float(v)) for v in theta], np.float32)
+    ha = np.array([libm.acosf(float(v)) for v in x], np.float32)
+    assert np.array_equal(a.view(np.uint32), ha.view(np.uint32))
+    assert (s.view(np.uint32) == hs.view(np.uint32)).mean() > 0.9999
+    assert (c.view(np.uint32) == hc.view(np.uint32)).mean() > 0.9999
+    sp, cp, _ = ctx.kat_libm(a)
+    hsp = np.array([libm.sinf(float(v)) for v in ha], np.float32)
+    assert (sp.view(np.uint32) == hsp.view(np.uint32)).mean() > 0.9999
+
+
+def test_erfinv_approx(ctx, golden):
+    rec = golden["kat/rand50/2"].reshape(-1, 2)
+    got = ctx.kat_erfinv(rec[:, 0])
+    np.testing.assert_allclose(got, rec[:, 1], rtol=1e-13, atol=0)
+
+
+@pytest.mark.parametrize("sc", ["two_gauss", "rand50", "rand300"])
+def test_gaussian_primitives(ctx, ob, vr, golden, scenegen, sc):
+    """intersect_direct bit-exact; optical_depth / mu_t to libm precision; analytic inverse bit-exact
+    on >= 99% (double erf/exp/log differ from glibc in the last bit only)."""
+    rec = golden[f"kat/{sc}/3"].reshape(-1, 16)
+    setup(ctx, ob, vr, scenegen, sc, "pin")
+    gi = np.ascontiguousarray(rec[:, 6]).view(np.uint32).astype(np.int32)
+    r = ctx.kat_gaussian(rec[:, 0:3], rec[:, 3:6], gi, rec[:, 12])
+    hit = rec[:, 7].astype(np.int32)
+    assert np.array_equal(r["hit"], hit)
+    h = hit == 1
+    assert np.array_equal(r["t0"][h], rec[h, 8]) and np.array_equal(r["t1"][h], rec[h, 9])
+    np.testing.assert_allclose(r["tau"][h], rec[h, 10], rtol=2e-5, atol=1e-9)
+    np.testing.assert_allclose(r["mu"][h], rec[h, 11], rtol=2e-6, atol=0)
+    assert np.array_equal(r["ok"][h], rec[h, 13].astype(np.int32))
+    ok = h & (rec[:, 13] == 1)
+    np.testing.assert_allclose(r["t_solved"][ok], rec[ok, 14], rtol=2e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("sc", ["two_gauss", "rand50", "rand300"])
+def test_transmittance_golden(ctx, ob, vr, golden, scenegen, sc):
+    """transmittance_up_to (gmm.h:517-578) within 1e-5 of the reference's values."""
+    rec = golden[f"kat/{sc}/4"].reshape(-1, 8)
+    setup(ctx, ob, vr, scenegen, sc, "pin")
+    got = ctx.transmittance(rec[:, 0:3], rec[:, 3:6], rec[:, 6])
+    np.testing.assert_allclose(got, rec[:, 7], rtol=1e-5, atol=1e-7)
+
+
+def test_transmittance_vs_oracle_200k_rays(ctx, ob, vr, scenegen):
+    scene = scenegen.generate(2000, 21, nonuniform=True, diameter_range=(0.02, 0.12))
+    setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
+    rs = np.random.RandomState(5)
+    n = 200000
+    o = rs.uniform(-1.5, 1.5, size=(n, 3)).astype(np.float32); o[:, 1] += 1
+    t = rs.uniform(-1, 1, size=(n, 3)).astype(np.float32); t[:, 1] += 1
+    d = t - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    tmax = np.where(rs.rand(n) < 0.5, np.inf, rs.uniform(0, 4, n)).astype(np.float32)
+    ref = ob.Gmm(scene).transmittance(o, d, tmax)
+    got = ctx.transmittance(o, d, tmax)
+    np.testing.assert_allclose(got, ref, rtol=1e-5, atol=1e-7)
+    assert (ref < 0.99).mean() > 0.2  # the rays do cross the medium
+
+
+@pytest.mark.parametrize("sc", ["two_gauss", "rand50", "rand300"])
+def test_event_lists(ctx, ob, vr, golden, scenegen, sc):
+    raw = golden[f"kat/{sc}/5"]
+    setup(ctx, ob, vr, scenegen, sc, "pin")
+    off = 0
+    while off < raw.size:
+        o = raw[off:off + 3]; d = raw[off + 3:off + 6]
+        n = int(raw[off + 6]); off += 7
+        ev = raw[off:off + 3 * n].reshape(n, 3); off += 3 * n
+        t, e, idx = ctx.kat_events(o, d)
+        assert t.size == n
+        assert np.array_equal(t, ev[:, 0])
+        a = sorted(zip(t.tolist(), e.tolist(), idx.tolist()))
+        b = sorted(zip(ev[:, 0].tolist(), ev[:, 1].astype(int).tolist(), ev[:, 2].astype(int).tolist()))
+        assert a == b
+
+
+def test_camera_rays_bit_exact(ctx, ob, vr, golden):
+    rec = golden["kat/rand50/6"].reshape(-1, 9)
+    for kind, name in ((0, "pin"), (1, "ortho")):
+        _, cd = cam_dict(ob, vr, name)
+        ctx.set_camera(cd)
+        r = rec[rec[:, 0] == kind]
+        o, d = ctx.kat_camera_rays(r[:, 1:3])
+        assert np.array_equal(o, r[:, 3:6]) and np.array_equal(d, r[:, 6:9])
+
+
+# ------------------------------------------------------------------------------------------------
+# Integrator::render against the reference's own images
+# ------------------------------------------------------------------------------------------------
+RENDERS = [("two_gauss", "pin", 16), ("two_gauss", "ortho", 4), ("rand50", "pin", 16), ("rand50", "pin2", 9),
+           ("rand300", "pin", 16), ("rand2k", "pin", 16), ("rand2k", "pin2", 4)]
+
+
+@pytest.mark.parametrize("sc,cam,spp", RENDERS)
+@pytest.mark.parametrize("integ", ["ss", "ms"])
+def test_render_matches_reference(ctx, ob, vr, golden, scenegen, sc, cam, spp, integ):
+    """>= 98% of pixels within 1e-4 relative of the reference's float image; mean within 1e-3."""
+    setup(ctx, ob, vr, scenegen, sc, cam)
+    ref = golden[f"render/{sc}/{cam}/{integ}/{spp}"]
+    p = vr.Context.params(vr.INTEGRATOR_SS if integ == "ss" else vr.INTEGRATOR_MS, 32, 32, spp)
+    img, st = ctx.render(p)
+    assert st["samples"] == 32 * 32 * spp
+    assert frac_within(img, ref, 1e-4) >= 0.98, frac_within(img, ref, 1e-4)
+    assert abs(float(img.mean()) - float(ref.mean())) <= 1e-3 * float(ref.mean())
+
+
+def test_render_min_bounces(ctx, ob, vr, golden, scenegen):
+    setup(ctx, ob, vr, scenegen, "rand50", "pin")
+    img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 16, min_bounces=1))
+    assert frac_within(img, golden["render/rand50/pin/ms/16/minb1"], 1e-4) >= 0.98
+
+
+@pytest.mark.parametrize("solver", [0, 1, 2, 3])
+def test_render_all_solvers_vs_oracle(ctx, ob, vr, scenegen, solver):
+    """runtime form of the solver #define block (distance_solvers.h:143-147)"""
+    scene, oc = setup(ctx, ob, vr, scenegen, "rand300", "pin2")
+    ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 48, 48, 9, solver=solver)
+    img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 48, 48, 9, solver=solver))
+    assert frac_within(img, ref, 1e-4) >= 0.98
+
+
+@pytest.mark.parametrize("integ", ["ss", "ms"])
+def test_render_vs_oracle_2k_nonuniform(ctx, ob, vr, scenegen, integ):
+    scene = scenegen.generate(2000, 31, nonuniform=True)
+    _, oc = setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
+    it_o = ob.INTEGRATOR_SS if integ == "ss" else ob.INTEGRATOR_MS
+    it_g = vr.INTEGRATOR_SS if integ == "ss" else vr.INTEGRATOR_MS
+    ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, it_o, 96, 96, 16)
+    img, _ = ctx.render(vr.Context.params(it_g, 96, 96, 16))
+    assert frac_within(img, ref, 1e-4) >= 0.98
+
+
+def test_render_overflow_path_vs_oracle(ctx, ob, vr, scenegen):
+    """rays overlapping more components than the local store holds are re-traced by the arena kernel"""
+    scene = scenegen.generate(300, 41, diameter_range=(0.5, 1.2))
+    scene["density"] = (scene["density"] * np.float32(0.02)).astype(np.float32)  # optically thin: nothing is pruned
+    _, oc = setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
+    ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 24, 24, 4)
+    img, st = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 4))
+    assert st["overflow_samples"] > 0
+    assert frac_within(img, ref, 2e-4) >= 0.97
+    ctx.set_option("hit_capacity", 40)   # too small on purpose: must fail loudly, not silently drop overlaps
+    with pytest.raises(vr.VolRenderError) as e:
+        ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 4))
+    assert e.value.code == 5
+    ctx.set_option("hit_capacity", 0)
+
+
+def test_recorded_sets_match_reference(ctx, ob, vr, golden, scenegen):
+    for sc, cam, spp in [("two_gauss", "pin", 16), ("rand50", "pin", 16), ("rand2k", "pin2", 4)]:
+        setup(ctx, ob, vr, scenegen, sc, cam)
+        ref = decode_record(golden[f"render/{sc}/{cam}/ms/{spp}/record"])
+        ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, spp, record=True))
+        cnt, idx = ctx.recorded(32, 32, 256)
+        same = sum(set(r.tolist()) == set(idx[p, :cnt[p]].tolist()) for p, r in enumerate(ref))
+        assert same / len(ref) >= 0.98
+
+
+# ------------------------------------------------------------------------------------------------
+# edge cases and size-independent properties
+# ------------------------------------------------------------------------------------------------
+def test_empty_and_tiny_scenes(ctx, ob, vr, scenegen):
+    _, cd = cam_dict(ob, vr, "pin")
+    ctx.set_camera(cd)
+    empty = dict(mean=np.zeros((0, 3), np.float32), cov6=np.zeros((0, 6), np.float32), density=np.zeros(0, np.float32),
+                 albedo=np.zeros(0, np.float32))
+    ctx.set_gmm(empty)
+    ctx.set_lights(np.zeros((0, 6), np.float32), ENV)
+    img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 16, 16, 4))
+    assert np.array_equal(img, np.broadcast_to(np.array(ENV, np.float32), img.shape))   # every ray escapes
+    one = scenegen.generate(1, 3, diameter_range=(0.4, 0.6))
+    one["mean"][:] = (0, 1, 0)
+    ctx.set_gmm(one)
+    oc, _ = cam_dict(ob, vr, "pin")
+    for lights in (np.zeros((0, 6), np.float32), one["lights"]):   # nl == 0: environment only (integrator.h:657)
+        ctx.set_lights(lights, ENV)
+        ref = ob.render(ob.Gmm(one), lights, ENV, oc, ob.INTEGRATOR_MS, 32, 32, 4)
+        img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 4))
+        assert frac_within(img, ref, 1e-4) >= 0.98
+
+
+def test_window_and_row_partition_are_exact(ctx, ob, vr, scenegen):
+    """tiles / row partitions reproduce the full image bit for bit (every sample's stream depends on
+    (x, y, si) only, rng.h:52-57) -- the multi-GPU decomposition, checked on one device."""
+    setup(ctx, ob, vr, scenegen, "rand2k", "pin")
+    W, H, spp = 40, 36, 9
+    full, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp))
+    acc = np.full((H, W, 3), -1.0, np.float32)
+    for r in range(3):
+        ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp, part=(r, 3)), out=acc)
+    assert np.array_equal(acc, full)
+    win = np.full((H, W, 3), -1.0, np.float32)
+    ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp, window=(5, 7, 29, 30)), out=win)
+    assert np.array_equal(win[7:30, 5:29], full[7:30, 5:29])
+    assert (win[:7] == -1).all() and (win[:, :5] == -1).all() and (win[30:] == -1).all()
+    ctx.set_option("max_pass_samples", 1000)   # many passes give the same image
+    multi, st = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp))
+    ctx.set_option("max_pass_samples", 2 ** 28)
+    assert np.array_equal(multi, full) and st["kernel_launches"] > 10
+
+
+def test_full_size_config1_properties(ctx, ob, vr, scenegen):
+    """BASELINE config 1 (1k Gaussians, 512^2, 64 spp, single scatter) at full size: deterministic,
+    radiance finite and bounded, and a window of it equals the oracle's."""
+    scene = scenegen.generate(1000, 1)
+    _, oc = setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
+    p = vr.Context.params(vr.INTEGRATOR_SS, 512, 512, 64)
+    a, st = ctx.render(p)
+    b, _ = ctx.render(p)
+    assert np.array_equal(a, b)
+    assert np.isfinite(a).all() and a.min() >= 0
+    assert st["samples"] == 512 * 512 * 64
+    win = (240, 200, 272, 232)
+    ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_SS, 512, 512, 64, window=win)
+    assert frac_within(a[200:232, 240:272], ref[200:232, 240:272], 1e-4) >= 0.98
+
+
+# ------------------------------------------------------------------------------------------------
+# inverse path
+# ------------------------------------------------------------------------------------------------
+def test_unpack_params_vs_oracle(ctx, ob, golden):
+    p = golden["sfd/params0"]
+    n = p.size // 11
+    mean = np.empty((n, 3), np.float32); cov6 = np.empty((n, 6), np.float32)
+    den = np.empty(n, np.float32); alb = np.empty(n, np.float32)
+    ob.lib().vo_unpack_params(n, np.ascontiguousarray(p), mean.reshape(-1), cov6.reshape(-1), den, alb)
+    gm, gc, gd, ga = ctx.unpack_params(p)
+    assert np.array_equal(gm, mean)
+    np.testing.assert_allclose(gc, cov6, rtol=3e-6, atol=1e-9)
+    np.testing.assert_allclose(gd, den, rtol=3e-7); np.testing.assert_allclose(ga, alb, rtol=3e-7)
+
+
+def test_adam_step_bit_exact(ctx, ob, golden):
+    g = golden["sfd/iter0/12"]
+    D = g.size
+    p = golden["sfd/iter0/10"].copy(); m = np.zeros(D, np.float32); v = np.zeros(D, np.float32)
+    t = ctx.adam_step(p, g, m, v, 0)
+    assert t == 1
+    np.testing.assert_allclose(p, golden["sfd/iter0/13"], rtol=0, atol=1e-7)
+    g1 = golden["sfd/iter1/12"]
+    p = golden["sfd/iter1/10"].copy()
+    ctx.adam_step(p, g1, m, v, t)
+    np.testing.assert_allclose(p, golden["sfd/iter1/13"], rtol=0, atol=1e-7)
+
+
+def test_sfd_iterations_vs_reference(ctx, ob, vr, golden, scenegen):
+    """two SFD + Adam iterations with the injected sign vectors the reference was run with"""
+    scene = load_scene(scenegen, "rand50")
+    _, cd = cam_dict(ob, vr, "pin")
+    ctx.set_camera(cd); ctx.set_lights(scene["lights"], ENV)
+    W = H = 24
+    signs = golden["sfd/signs"]
+    D = golden["sfd/params0"].size; N = D // 11
+    eps = np.empty(D, np.float32); ob.lib().vo_default_eps(D, eps)
+    rp = vr.Context.params(vr.INTEGRATOR_MS, W, H, 16)
+    for it in range(2):
+        ctx.sfd_begin(golden[f"sfd/iter{it}/10"], eps, lr=0.01)
+        ctx.sfd_set_target(golden["sfd/target"])
+        F, loss_sum, npx = ctx.sfd_fdiff(rp, signs[it])
+        assert npx == W * H
+        assert abs(loss_sum / npx - float(golden[f"sfd/iter{it}/14"][0])) < 2e-4
+        F_ref = golden[f"sfd/iter{it}/11"].reshape(2, N)
+        for s in range(2):
+            assert np.abs(F[s] - F_ref[s]).max() <= 2e-2 * np.abs(F_ref[s]).max()
+        # gradient + Adam from the REFERENCE F_diff: isolates :182-207 from render noise
+        grad = ctx.sfd_apply(signs[it], F_ref)
+        np.testing.assert_allclose(grad, golden[f"sfd/iter{it}/12"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(ctx.sfd_params(), _adam_from(golden, it), rtol=0, atol=2e-6)
+
+
+def _adam_from(golden, it):
+    # sfd_begin resets Adam, so iteration `it` is always a first step from params_before
+    p = golden[f"sfd/iter{it}/10"].astype(np.float32).copy()
+    g = golden[f"sfd/iter{it}/12"].astype(np.float32)
+    b1, b2, lr, eps = np.float32(0.9), np.float32(0.999), np.float32(0.01), np.float32(1e-8)
+    a = lr * np.sqrt(np.float32(1) - b2, dtype=np.float32) / (np.float32(1) - b1)
+    m = (np.float32(1) - b1) * g
+    v = (np.float32(1) - b2) * g * g
+    return (p - a * (m / (np.sqrt(v, dtype=np.float32) + eps))).astype(np.float32)
+
+
+def test_sfd_partition_sums_are_exact(ctx, ob, vr, golden, scenegen):
+    """F_diff accumulated over row partitions (as ranks would) equals the single-context result bit
+    for bit -- fixed-point accumulation is associative."""
+    scene = load_scene(scenegen, "rand50")
+    _, cd = cam_dict(ob, vr, "pin")
+    ctx.set_camera(cd); ctx.set_lights(scene["lights"], ENV)
+    D = golden["sfd/params0"].size
+    eps = np.empty(D, np.float32); ob.lib().vo_default_eps(D, eps)
+    ctx.sfd_begin(golden["sfd/params0"], eps)
+    ctx.sfd_set_target(golden["sfd/target"])
+    signs = golden["sfd/signs"][0]
+    F1, l1, _ = ctx.sfd_fdiff(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 16), signs)
+    ctx.sfd_reset(2)
+    for r in range(3):
+        ctx.sfd_accumulate(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 16, part=(r, 3)), signs)
+    F3, l3 = ctx.sfd_read(2)
+    assert np.array_equal(F1, F3) and l1 == l3
+
+
+# ------------------------------------------------------------------------------------------------
+# sphere path (config 0)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["one_sphere", "three_spheres"])
+def test_spheres_vs_oracle(ctx, ob, vr, golden, scenegen, name):
+    """RayMarchingSpheres with the oracle's seeded environment directions: per-pixel 1e-4; against the
+    reference's random_device-seeded image only statistically (parity unpinned)."""
+    smm = scenegen.load_smm(os.path.join(SCENES, name + ".txt"))
+    oc, cd = cam_dict(ob, vr, "ortho")
+    ctx.set_camera(cd); ctx.set_smm(smm); ctx.set_lights(smm["lights"], ENV)
+    ref = ob.render_spheres(smm, ENV, oc, 48, 48, 0.01, 5)
+    img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MARCH_SPHERES, 48, 48, 1, march_step=0.01, env_samples=5))
+    assert frac_within(img, ref, 1e-4) >= 0.99
+    gold = golden[f"spheres/{name}/ortho"]
+    assert abs(float(img.mean()) - float(gold.mean())) < 0.01 * float(gold.mean())
