@@ -42,7 +42,7 @@ struct Builder {
     }
     float centroid(uint32_t g, int axis) const { return 0.5f * (lo[3 * g + axis] + hi[3 * g + axis]); }
 
-    static int leaf_code(int first, int count) { return ~((first << 3) | (count - 1)); }
+    static int leaf_code(int first, int count) { return ~((first << 3) | count); }
 
     void set_child_box(BvhNode& nd, int c, const Box& b) {
         if (c == 0) {
@@ -142,14 +142,14 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
     Box root = b.range_box(0, n);
     int left = (n >= 2) ? b.split(0, n, root) : 0;
     if (left == 0) {
-        // a single leaf: child 0 = everything (split into runs of <= 8 is not needed: n <= kMaxLeaf here),
-        // child 1 = empty box that no ray enters
+        // a single leaf: child 0 = everything (n <= kMaxLeaf here), child 1 = a leaf of ZERO Gaussians
+        // (an inverted box is not enough: min/max in the slab test re-order lo and hi)
         BvhNode& nd = out->nodes[0];
         b.set_child_box(nd, 0, root);
         Box empty; empty.reset();
         b.set_child_box(nd, 1, empty);
         nd.child[0] = Builder::leaf_code(0, n);
-        nd.child[1] = Builder::leaf_code(0, 1);
+        nd.child[1] = Builder::leaf_code(0, 0);
         b.max_leaf = n;
     } else {
         b.build_node(0, 0, n, left, 1);

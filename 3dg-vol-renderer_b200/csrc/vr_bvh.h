@@ -16,7 +16,7 @@ struct BvhNode {       // 64 B, 16-byte aligned, read as 4 x float4
     float c0x[2], c0y[2];  // child 0: (lo.x, hi.x, lo.y, hi.y)
     float c1x[2], c1y[2];  // child 1
     float c0z[2], c1z[2];  // (lo0.z, hi0.z, lo1.z, hi1.z)
-    int32_t child[2];      // >= 0: node index; < 0: leaf, ~((first << 3) | (count - 1))
+    int32_t child[2];      // >= 0: node index; < 0: leaf, ~((first << 3) | count), count 0..7
     int32_t pad[2];
 };
 static_assert(sizeof(BvhNode) == 64, "BvhNode must be 64 bytes");
@@ -28,7 +28,7 @@ struct BvhBuildResult {
     int max_leaf = 0;
 };
 
-constexpr int kMaxLeaf = 4;         // <= 8 by the 3-bit count field
+constexpr int kMaxLeaf = 4;         // <= 7 by the 3-bit count field
 
 // lo/hi: 3*n floats each (per-Gaussian boxes).  Deterministic.
 void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out);

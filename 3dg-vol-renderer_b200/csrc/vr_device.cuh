@@ -110,7 +110,7 @@ __device__ int gather_overlaps(const SceneDev& S, f3 o, f3 d, float target_tau, 
             if (h1) { cur = c1; continue; }
         } else {
             const uint32_t code = ~(uint32_t)cur;
-            const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+            const uint32_t first = code >> 3, cnt = code & 7u;
             for (uint32_t i = 0; i < cnt; ++i) {
                 const GaussRec g = load_gauss(S.gauss, first + i);
                 const RayQuad q = ray_quad(g, o, d);
@@ -157,7 +157,7 @@ static __device__ float shadow_transmittance(const SceneDev& S, f3 o, f3 d, floa
             if (h1) { cur = c1; continue; }
         } else {
             const uint32_t code = ~(uint32_t)cur;
-            const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+            const uint32_t first = code >> 3, cnt = code & 7u;
             for (uint32_t i = 0; i < cnt; ++i) {
                 const GaussRec g = load_gauss(S.gauss, first + i);
                 const RayQuad q = ray_quad(g, o, d);
