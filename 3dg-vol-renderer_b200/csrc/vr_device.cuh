@@ -181,17 +181,17 @@ static __device__ float shadow_transmittance(const SceneDev& S, f3 o, f3 d, floa
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return (v < lo) ? lo : ((hi < v) ? hi : v); }
 
 template <class St>
-__device__ float sum_depth_to(St& st, int na, float tt) {  // sum_k tau_k(ta, tt), float, active order
+__device__ __noinline__ float sum_depth_to(St& st, int na, float tt) {  // sum_k tau_k(ta, tt), float, active order
     float sum = 0.0f;
     for (int k = 0; k < na; ++k) {
         const int s = (int)st.U(U_ACT, k);
         const DepthConst c = hit_const(st, s);
-        sum = __fadd_rn(sum, __fmul_rn(c.K, __fsub_rn(erff(erf_arg(c, tt)), st.F(F_ACTF, k))));
+        sum = __fadd_rn(sum, __fmul_rn(c.K, __fsub_rn(erff_ni(erf_arg(c, tt)), st.F(F_ACTF, k))));
     }
     return sum;
 }
 template <class St>
-__device__ float solve_bisection(St& st, int na, float ta, float tb, float target) {  // :25-57
+__device__ __noinline__ float solve_bisection(St& st, int na, float ta, float tb, float target) {  // :25-57
     float a = ta, b = tb;
     for (int i = 0; i < 15; ++i) {
         float mid = __fmul_rn(0.5f, __fadd_rn(a, b));
@@ -202,7 +202,7 @@ __device__ float solve_bisection(St& st, int na, float ta, float tb, float targe
     return __fmul_rn(0.5f, __fadd_rn(a, b));
 }
 template <class St>
-__device__ float solve_newton(St& st, int na, float ta, float tb, float target) {  // :62-127
+__device__ __noinline__ float solve_newton(St& st, int na, float ta, float tb, float target) {  // :62-127
     const float tol = 1e-6f;
     const float a = ta, b = tb;
     float t = __fmul_rn(0.5f, __fadd_rn(a, b));
@@ -316,7 +316,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
             float seg = 0.0f;
             for (int k = 0; k < na; ++k) {
                 const DepthConst c = hit_const(st, (int)st.U(U_ACT, k));
-                const float Fn = erff(erf_arg(c, t_evt));
+                const float Fn = erff_ni(erf_arg(c, t_evt));
                 seg = __fadd_rn(seg, __fmul_rn(c.K, __fsub_rn(Fn, st.F(F_ACTF, k))));
                 st.F(F_ACTF, k) = Fn;
             }
@@ -327,7 +327,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
             double seg = 0.0;
             for (int k = 0; k < na; ++k) {
                 const DepthConst c = hit_const(st, (int)st.U(U_ACT, k));
-                const float Fn = erff(erf_arg(c, t_evt));
+                const float Fn = erff_ni(erf_arg(c, t_evt));
                 seg = __dadd_rn(seg, (double)__fmul_rn(c.K, __fsub_rn(Fn, st.F(F_ACTF, k))));
                 st.F(F_ACTF, k) = Fn;
             }
@@ -337,12 +337,12 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
         }
         if (hit_target) {
             for (int k = 0; k < na; ++k)  // restore erf(arg(t_prev)) for the solver
-                st.F(F_ACTF, k) = erff(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
+                st.F(F_ACTF, k) = erff_ni(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
             *na_out = na;
             return solve_distance(S, st, na, o, d, t_prev, t_evt, remaining, solver);
         }
         if (take_enter) {
-            const float F0 = erff(erf_arg(hit_const(st, se), t_evt));
+            const float F0 = erff_ni(erf_arg(hit_const(st, se), t_evt));
             int pos = na;
             if (ss) {  // FreeFlightGaussians rescans a bool vector in ascending index order (integrator.h:344-346)
                 const uint32_t oe = __ldg(S.orig + st.U(U_GI, se));

@@ -9,7 +9,11 @@
 //                        accumulation order (integrator.h:702-706) -- deterministic, no atomics.
 //   transmittance_kernel batch of GaussianMixtureModel::transmittance_up_to (gmm.h:517-578).
 //   kat_*                known-answer hooks over the same device functions.
+#include "vr_bvh.h"
 #include "vr_internal.h"
+#include "vr_warp.cuh"
+
+static_assert(vr::kMaxLeafDev == vr::kMaxLeaf, "device leaf width must match the host builder");
 
 namespace vr {
 
@@ -217,15 +221,19 @@ __global__ void __launch_bounds__(kBlockThreads) path_kernel(const __grid_consta
     }
 }
 
+constexpr size_t kWarpKernelSmem = sizeof(WarpShared) * (kBlockThreads / 32);
 int path_kernel_blocks_per_sm(bool arena) {
     int nb = 0;
     if (arena) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, path_kernel<ArenaStore, true>, kBlockThreads, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, path_kernel<LocalStore<kLocalCap>, false>, kBlockThreads, 0);
+    else {
+        cudaFuncSetAttribute(warp_path_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWarpKernelSmem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, warp_path_kernel, kBlockThreads, kWarpKernelSmem);
+    }
     return nb;
 }
 void launch_path_kernel(const RenderArgs& a, int blocks, bool arena, cudaStream_t s) {
     if (arena) path_kernel<ArenaStore, true><<<blocks, kBlockThreads, 0, s>>>(a);
-    else path_kernel<LocalStore<kLocalCap>, false><<<blocks, kBlockThreads, 0, s>>>(a);
+    else warp_path_kernel<<<blocks, kBlockThreads, kWarpKernelSmem, s>>>(a);
 }
 
 // mean of a pixel's samples in sample order (integrator.h:557,702-706)

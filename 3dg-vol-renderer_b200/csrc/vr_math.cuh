@@ -226,9 +226,12 @@ __device__ __forceinline__ DepthConst depth_const(const GaussRec& g, const RayQu
 __device__ __forceinline__ float erf_arg(const DepthConst& c, float t) {
     return __fdiv_rn(__fadd_rn(c.B, __fmul_rn(__fmul_rn(2.0f, c.A), t)), c.den);
 }
+// one out-of-line copy of erff per kernel: it is evaluated at a dozen call sites and inlining each
+// (~60 instructions) bloated the path kernels past the instruction caches (profiles/r01_v0)
+static __device__ __noinline__ float erff_ni(float x) { return erff(x); }
 __device__ __forceinline__ float depth_between(const DepthConst& c, float t0, float t1) {
-    float F1 = erff(erf_arg(c, t1));
-    float F0 = erff(erf_arg(c, t0));
+    float F1 = erff_ni(erf_arg(c, t1));
+    float F0 = erff_ni(erf_arg(c, t0));
     return __fmul_rn(c.K, __fsub_rn(F1, F0));
 }
 // gaussian.h:111-117
@@ -253,8 +256,8 @@ __device__ __forceinline__ double erfinv_approx(double x) {
     return sign * __dsqrt_rn(__dsub_rn(__dsqrt_rn(inside), first));
 }
 // gaussian.h:235-297, all double
-__device__ __forceinline__ bool solve_t_given_tau(const GaussRec& g, const RayQuad& q, float t0, float tb, float target_tau,
-                                                  float* t_out) {
+static __device__ __noinline__ bool solve_t_given_tau(const GaussRec& g, const RayQuad& q, float t0, float tb, float target_tau,
+                                                      float* t_out) {
     double A = (double)q.A;
     if (!(A > 0.0) || !isfinite(A)) return false;
     double B = (double)q.B;  // 2.0 * (double)dot == (double)(2.0f * dot): scaling by 2 is exact
