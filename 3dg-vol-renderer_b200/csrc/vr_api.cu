@@ -61,7 +61,7 @@ int vr_create(vr_context** out, int device_id) {
     VR_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (auto& e : ctx->ev) VR_CUDA(cudaEventCreate(&e));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_stats, sizeof(unsigned long long) * kNumStats));
-    VR_CUDA(cudaMallocHost((void**)&ctx->h_counters, sizeof(unsigned int) * 4));
+    VR_CUDA(cudaMallocHost((void**)&ctx->h_counters, sizeof(unsigned int) * 32));
     VR_CUDA(ctx->stats.ensure(sizeof(unsigned long long) * kNumStats));
     VR_CUDA(ctx->counters.ensure(sizeof(unsigned int) * 4));
     ctx->blocks_per_sm_main = std::max(1, path_kernel_blocks_per_sm(false));
@@ -77,7 +77,7 @@ void vr_destroy(vr_context* ctx) {
     for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
                       &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->spheres, &ctx->lpos, &ctx->lint,
                       &ctx->image, &ctx->sampleL, &ctx->counters, &ctx->stats, &ctx->overflow_list, &ctx->arena,
-                      &ctx->record_bits, &ctx->scratch})
+                      &ctx->record_bits, &ctx->scratch, &ctx->wavepool})
         b->release();
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
@@ -94,6 +94,8 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "hit_capacity")) { ctx->hit_capacity = (int)value; ctx->arena.release(); return VR_OK; }
     if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
+    if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
+    if (!strcmp(name, "wave_slots")) { ctx->wave_slots = std::max(0, (int)value); ctx->wavepool.release(); return VR_OK; }
     return fail(ctx, VR_ERR_INVALID_ARGUMENT, std::string("unknown option ") + name);
 }
 

@@ -52,7 +52,7 @@ struct vr_context {
     bool has_camera = false;
     vr::CameraPod cam{};
     // ---- render state
-    vr::DevBuf image, sampleL, counters, stats, overflow_list, arena, record_bits, scratch;
+    vr::DevBuf image, sampleL, counters, stats, overflow_list, arena, record_bits, scratch, wavepool;
     int img_w = 0, img_h = 0;
     int rec_w = 0, rec_h = 0, rec_words = 0, rec_n = 0;
     bool rec_valid = false;
@@ -62,6 +62,8 @@ struct vr_context {
     int hit_capacity = 0;                          // 0 = min(n, 4096)
     double max_pass_samples = 268435456.0;         // 2^28 samples = 4 GiB of per-sample radiance
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
+    int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
+    int wave_slots = 0;                            // 0 = 8192 per SM
     // ---- inverse
     vr::SfdState* sfd = nullptr;
 

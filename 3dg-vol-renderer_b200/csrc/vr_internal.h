@@ -32,6 +32,34 @@ struct RenderArgs {
     int arena_cap;
 };
 
+// ---- wavefront engine (vr_wave.cu): a pool of P path slots whose state lives in global memory
+// (sized to stay resident in the 126 MB L2), advanced one ray per iteration by four small kernels.
+constexpr int kWaveCap = 16;         // free-flight overlaps kept per path slot (more = re-trace by the arena kernel)
+enum { WC_NT0 = 0, WC_NT1, WC_NA, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR, kWaveCounters = 16 };
+struct WavePool {
+    int P;
+    float4* ray_o;        // o.xyz, lim (scatter: sampled optical depth, shadow: tmax)
+    float4* ray_d;        // d.xyz, kind bits
+    float4* ps0;          // L0 L1 L2 thr
+    uint4* ps1;           // rng state lo/hi, work (pass-local sample id), bounce
+    float4* ps2;          // target_tau, albedo, nee_dist, nee_light bits
+    int* hit_count;
+    float* hit_t0;        // [kWaveCap][P]
+    float* hit_t1;
+    uint32_t* hit_gi;
+    long long* tau_fixed; // shadow rays: sum of clipped optical depths in 2^-40 units
+    unsigned int* listT[2];
+    unsigned int* listA;
+    unsigned int* listB;
+    unsigned int* listC;
+    unsigned int* cnt;    // kWaveCounters
+};
+size_t wave_pool_bytes(int P);
+void wave_pool_carve(WavePool* q, int P, void* base);
+// runs the whole pass (a.work_count samples) ; returns the number of iterations enqueued, < 0 on CUDA error
+int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsigned int* h_cnt_pinned, cudaStream_t s,
+                       unsigned int* launches);
+
 constexpr int kBlockThreads = 128;
 constexpr int kLocalCap = 32;        // overlaps kept in local memory by the main kernel
 

@@ -1,0 +1,27 @@
+// vr_pathcommon.cuh -- small pieces shared by the path engines (vr_warp.cuh, vr_wave.cu)
+#pragma once
+#include "vr_internal.h"
+
+namespace vr {
+
+constexpr int kMaxLeafDev = 4;                 // == vr::kMaxLeaf of the host builder (vr_bvh.h)
+constexpr double kTauFixed = 1099511627776.0;  // 2^40: shadow optical depth in fixed point
+enum { RAY_SCATTER = 0, RAY_SHADOW = 1 };
+__device__ __forceinline__ long long tau_cutoff_fixed() { return (long long)((double)kShadowTauCutoff * kTauFixed); }
+
+__device__ __forceinline__ void lane_xy(const RenderArgs& A, unsigned int work, int* x, int* y, int* si) {
+    const unsigned int p = A.pixel_base + work / (unsigned int)A.spp;
+    *si = (int)(work % (unsigned int)A.spp);
+    *x = A.x0 + (int)(p % (unsigned int)A.win_w);
+    *y = A.y0 + (int)(p / (unsigned int)A.win_w) * A.part_count + A.part_rank;
+}
+
+// heavy helpers are kept out of line ONCE so the scheduler + traversal loop stays compact
+static __device__ __noinline__ f3 sample_direction_ni(uint64_t* state) {
+    Pcg rng; rng.state = *state; rng.inc = 3;
+    const f3 d = normalized3(sample_uniform_direction(rng));  // Ray ctor normalises (ray.h:11-12)
+    *state = rng.state;
+    return d;
+}
+
+}  // namespace vr

@@ -93,7 +93,15 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             A.overflow_list = ctx->overflow_list.as<unsigned int>();
             VR_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(unsigned int) * 4, s));
             VR_CUDA(cudaEventRecord(ctx->ev[2], s));
-            launch_path_kernel(A, grid_main, false, s); ++launches;
+            if (ctx->engine == 0) {
+                const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 8192;
+                VR_CUDA(ctx->wavepool.ensure(wave_pool_bytes(P)));
+                WavePool Q;
+                wave_pool_carve(&Q, P, ctx->wavepool.p);
+                if (run_wavefront_pass(A, Q, ctx->num_sms, ctx->h_counters + 8, s, &launches) < 0) VR_CUDA(cudaGetLastError());
+            } else {
+                launch_path_kernel(A, grid_main, false, s); ++launches;
+            }
             VR_CUDA(cudaGetLastError());
             VR_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(unsigned int) * 4, cudaMemcpyDeviceToHost, s));
             VR_CUDA(cudaStreamSynchronize(s));

@@ -24,14 +24,13 @@
 // paths are independent.  All control flow of the scheduler is warp-uniform (ballots).
 #pragma once
 #include "vr_internal.h"
+#include "vr_pathcommon.cuh"
 
 namespace vr {
 
 constexpr int kSmemCap = 8;                    // free-flight overlaps per lane kept in shared memory
-constexpr int kMaxLeafDev = 4;                 // == vr::kMaxLeaf of the host builder (vr_bvh.h)
 constexpr int kQueueCap = 32 + 32 * kMaxLeafDev;  // candidates: < 32 left over + one leaf per lane
 constexpr int kHitQueueCap = 64;               // shadow overlaps: < 32 left over + one quadric batch
-constexpr double kTauFixed = 1099511627776.0;  // 2^40: shadow optical depth in fixed point
 constexpr unsigned kPostThreshold = 16;        // run a post kind when this many lanes wait for it
 
 struct WarpShared {
@@ -52,7 +51,6 @@ struct WarpShared {
 typedef LocalStore<kSmemCap> PostStore;
 
 enum LaneMode { M_REGEN = 0, M_TRAV, M_WAIT, M_POSTA, M_POSTB, M_IDLE };
-enum { RAY_SCATTER = 0, RAY_SHADOW = 1 };
 
 struct LaneState {
     // path
@@ -72,22 +70,6 @@ struct LaneState {
 
 struct WarpCounters { unsigned int scatter, shadow, hits, over; };
 
-__device__ __forceinline__ long long tau_cutoff_fixed() { return (long long)((double)kShadowTauCutoff * kTauFixed); }
-
-__device__ __forceinline__ void lane_xy(const RenderArgs& A, unsigned int work, int* x, int* y, int* si) {
-    const unsigned int p = A.pixel_base + work / (unsigned int)A.spp;
-    *si = (int)(work % (unsigned int)A.spp);
-    *x = A.x0 + (int)(p % (unsigned int)A.win_w);
-    *y = A.y0 + (int)(p / (unsigned int)A.win_w) * A.part_count + A.part_rank;
-}
-
-// heavy helpers are kept out of line ONCE so the scheduler + traversal loop stays compact
-static __device__ __noinline__ f3 sample_direction_ni(uint64_t* state) {
-    Pcg rng; rng.state = *state; rng.inc = 3;
-    const f3 d = normalized3(sample_uniform_direction(rng));  // Ray ctor normalises (ray.h:11-12)
-    *state = rng.state;
-    return d;
-}
 
 // start traversing the lane's current ray
 __device__ __forceinline__ void begin_ray(const SceneDev& S, WarpShared& w, int lane, LaneState& ls, int kind, float lim) {

@@ -157,6 +157,8 @@ def main():
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (perfect square) for quick runs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
+    ap.add_argument("--wave-slots", type=int, default=0)
     a = ap.parse_args()
     cfg = dict(CONFIGS[a.config])
     if a.spp:
@@ -195,6 +197,9 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = vr.Context(local_rank)
+    ctx.set_option("engine", a.engine)
+    if a.wave_slots:
+        ctx.set_option("wave_slots", a.wave_slots)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
     ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cam); ctx.set_gmm(scene)
     integ = vr.INTEGRATOR_SS if cfg["integrator"] == "ss" else vr.INTEGRATOR_MS
@@ -292,6 +297,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": "Msamples/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
         "rays": {k: stats[k] for k in ("samples", "scatter_rays", "shadow_rays", "hits", "overflow_samples")},
+        "engine": "wavefront" if a.engine == 0 else "warp-scheduled single kernel",
     }))
 
 
