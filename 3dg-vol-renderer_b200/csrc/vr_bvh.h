@@ -28,7 +28,7 @@ struct BvhBuildResult {
     int max_leaf = 0;
 };
 
-constexpr int kMaxLeaf = 4;         // <= 7 by the 3-bit count field
+constexpr int kMaxLeaf = 1;         // one Gaussian per leaf: the traversal kernels queue a leaf CHILD as a candidate directly
 
 // lo/hi: 3*n floats each (per-Gaussian boxes).  Deterministic.
 void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out);

@@ -35,7 +35,7 @@ struct RenderArgs {
 // ---- wavefront engine (vr_wave.cu): a pool of P path slots whose state lives in global memory
 // (sized to stay resident in the 126 MB L2), advanced one ray per iteration by four small kernels.
 constexpr int kWaveCap = 16;         // free-flight overlaps kept per path slot (more = re-trace by the arena kernel)
-enum { WC_NT0 = 0, WC_NT1, WC_NA, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR, kWaveCounters = 16 };
+enum { WC_NTS = 0, WC_NTH, WC_NA, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, kWaveCounters = 16 };
 struct WavePool {
     int P;
     float4* ray_o;        // o.xyz, lim (scatter: sampled optical depth, shadow: tmax)
@@ -48,7 +48,8 @@ struct WavePool {
     float* hit_t1;
     uint32_t* hit_gi;
     long long* tau_fixed; // shadow rays: sum of clipped optical depths in 2^-40 units
-    unsigned int* listT[2];
+    unsigned int* listTs;  // slots whose free-flight ray waits for traversal
+    unsigned int* listTh;  // slots whose shadow ray waits for traversal
     unsigned int* listA;
     unsigned int* listB;
     unsigned int* listC;

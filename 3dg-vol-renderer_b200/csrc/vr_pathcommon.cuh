@@ -4,7 +4,7 @@
 
 namespace vr {
 
-constexpr int kMaxLeafDev = 4;                 // == vr::kMaxLeaf of the host builder (vr_bvh.h)
+constexpr int kMaxLeafDev = 1;                 // == vr::kMaxLeaf of the host builder (vr_bvh.h)
 constexpr double kTauFixed = 1099511627776.0;  // 2^40: shadow optical depth in fixed point
 enum { RAY_SCATTER = 0, RAY_SHADOW = 1 };
 __device__ __forceinline__ long long tau_cutoff_fixed() { return (long long)((double)kShadowTauCutoff * kTauFixed); }

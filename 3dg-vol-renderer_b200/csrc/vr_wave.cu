@@ -6,7 +6,7 @@
 // KERNELS over a pool of P path slots in global memory (sized to stay in the 126 MB L2):
 //
 //   wave_regen   slots without a path take the next (pixel, sample) and generate the camera ray;
-//   wave_trav    every slot's current ray (free-flight or shadow) is traversed by persistent warps
+//   wave_trav<K> every slot's current ray of kind K (free-flight / shadow) is traversed by persistent warps
 //                with a shared-memory candidate queue and batched quadric / optical-depth tests;
 //                a lane whose ray is done immediately FETCHES another ray of the wave, so ~all lanes
 //                stay inside the hierarchy; results go to the slot: (t0, t1, index) overlap records
@@ -46,256 +46,13 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     q->hit_t0 = (float*)take(p * 4 * kWaveCap); q->hit_t1 = (float*)take(p * 4 * kWaveCap);
     q->hit_gi = (uint32_t*)take(p * 4 * kWaveCap);
     q->tau_fixed = (long long*)take(p * 8);
-    q->listT[0] = (unsigned int*)take(p * 4); q->listT[1] = (unsigned int*)take(p * 4);
+    q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4);
     q->listA = (unsigned int*)take(p * 4); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
     q->cnt = (unsigned int*)take(kWaveCounters * 4);
 }
 
 // ------------------------------------------------------------------------------------------
-// wave_trav
-// ------------------------------------------------------------------------------------------
-constexpr int kTravQueueCap = 32 + 32 * kMaxLeafDev;
-constexpr int kTravHitQueueCap = 64;
-constexpr unsigned kFetchThreshold = 8;   // fetch new rays when this many lanes are free
-
-struct TravShared {
-    float ray[7][32];               // o.xyz d.xyz lim of the lane's current ray
-    int kind[32];
-    unsigned int pid[32];           // pool slot of the lane's ray
-    int count[32];                  // free-flight overlaps found (may exceed kWaveCap = overflow)
-    int pending[32];                // queued candidates / shadow overlaps of the lane
-    unsigned int t_bound[32];       // pruning bound of a free-flight ray, float bits
-    long long tau[32];              // shadow ray: fixed-point optical depth
-    uint32_t queue[kTravQueueCap];  // (owner lane << 27) | leaf-order Gaussian index
-    uint32_t hq_id[kTravHitQueueCap];
-    float hq_a[kTravHitQueueCap], hq_b[kTravHitQueueCap];
-};
-
-enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
-
-struct TravLane {
-    int mode, kind, cur, sp;
-    bool has_result;
-    f3 idir, ood;
-    float tmax;
-};
-
-__device__ __forceinline__ void trav_quadric_batch(const SceneDev& S, const WavePool& Q, TravShared& w, int lane, int q_begin,
-                                                   int nb, int& nH) {
-    bool to_hq = false;
-    uint32_t e = 0; float ha = 0.f, hb = 0.f;
-    if (lane < nb) {
-        e = w.queue[q_begin + lane];
-        const int owner = (int)(e >> 27);
-        const uint32_t gi = e & 0x07ffffffu;
-        const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
-        const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
-        const float lim = w.ray[6][owner];
-        const GaussRec g = load_gauss(S.gauss, gi);
-        const RayQuad q = ray_quad(g, o, d);
-        float t0, t1;
-        bool keep_pending = false;
-        if (quad_intersect(q, &t0, &t1)) {
-            if (w.kind[owner] == RAY_SCATTER) {
-                const float tb = __uint_as_float(w.t_bound[owner]);
-                if (!(t0 > tb)) {
-                    const int slot = atomicAdd(&w.count[owner], 1);
-                    if (slot < kWaveCap) {
-                        const size_t at = (size_t)slot * Q.P + w.pid[owner];
-                        Q.hit_t0[at] = t0; Q.hit_t1[at] = t1; Q.hit_gi[at] = gi;
-                        if (t1 < tb) {
-                            // pruning only: CONSERVATIVE estimate of this component's full optical depth
-                            // (fast intrinsics; 1.5x margin covers the FP32 slack of the exact expression)
-                            const float dn = g.density * g.norm;
-                            const float inv4A = __fdividef(1.0f, 4.0f * q.A);
-                            const float K = dn * sqrtf(6.2831853f * inv4A) * __expf(-0.5f * (q.C0 - q.B * q.B * inv4A));
-                            const float iden = rsqrtf(8.0f * q.A);
-                            const float full = K * (erff_ni((q.B + 2.0f * q.A * t1) * iden) - erff_ni((q.B + 2.0f * q.A * t0) * iden));
-                            if (full > 1.5f * lim) atomicMin(&w.t_bound[owner], __float_as_uint(t1));
-                        }
-                    }
-                }
-            } else if (w.tau[owner] <= tau_cutoff_fixed()) {
-                ha = fmaxf(0.0f, t0); hb = fminf(lim, t1);
-                to_hq = hb > ha;
-                keep_pending = to_hq;   // stays pending until the depth batch has added it
-            }
-        }
-        if (!keep_pending) atomicSub(&w.pending[owner], 1);
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, to_hq);
-    if (to_hq) {
-        const int pos = nH + __popc(m & ((1u << lane) - 1u));
-        w.hq_id[pos] = e; w.hq_a[pos] = ha; w.hq_b[pos] = hb;
-    }
-    nH += __popc(m);
-}
-
-// exact clipped optical depth of up to 32 shadow overlaps (gmm.h:563-571, gaussian.h:208-231)
-__device__ __forceinline__ void trav_depth_batch(const SceneDev& S, TravShared& w, int lane, int h_begin, int nb) {
-    if (lane < nb) {
-        const uint32_t e = w.hq_id[h_begin + lane];
-        const int owner = (int)(e >> 27);
-        const uint32_t gi = e & 0x07ffffffu;
-        const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
-        const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
-        const GaussRec g = load_gauss(S.gauss, gi);
-        const RayQuad q = ray_quad(g, o, d);
-        const DepthConst c = depth_const(g, q);
-        const float F1 = erff_ni(erf_arg(c, w.hq_b[h_begin + lane]));
-        const float F0 = erff_ni(erf_arg(c, w.hq_a[h_begin + lane]));
-        const float tau = __fmul_rn(c.K, __fsub_rn(F1, F0));
-        atomicAdd((unsigned long long*)&w.tau[owner], (unsigned long long)__double2ll_rn((double)tau * kTauFixed));
-        atomicSub(&w.pending[owner], 1);
-    }
-}
-
-__device__ __forceinline__ void trav_finish(TravShared& w, int lane, TravLane& tl) {
-    if (w.pending[lane] > 0) tl.mode = T_WAIT;
-    else { tl.mode = T_FETCH; tl.has_result = true; }
-}
-
-// node rounds: slab steps for lanes inside the hierarchy; leaf lanes queue their Gaussians.  Runs until
-// a full candidate batch is queued, enough lanes are free to fetch, or no lane traverses.
-__device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared& w, int lane, TravLane& tl, int stack[kStackDepth],
-                                            int& nQ, bool can_fetch) {
-    while (true) {
-        bool fin = false;
-        if (tl.mode == T_TRAV && tl.cur >= 0) {
-            float tlimit;
-            bool stop;
-            if (tl.kind == RAY_SCATTER) { tlimit = __uint_as_float(w.t_bound[lane]); stop = w.count[lane] > kWaveCap; }
-            else { tlimit = tl.tmax; stop = w.tau[lane] > tau_cutoff_fixed(); }
-            RaySetup rs; rs.idir = tl.idir; rs.ood = tl.ood;
-            bool h0, h1; float tn0, tn1; int c0, c1;
-            node_slabs(S.nodes, tl.cur, rs, tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
-            if (stop) { h0 = h1 = false; tl.sp = 0; }
-            if (h0 && h1) {
-                const bool swap = tn1 < tn0;
-                stack[tl.sp++] = swap ? c0 : c1;
-                tl.cur = swap ? c1 : c0;
-            } else if (h0) tl.cur = c0;
-            else if (h1) tl.cur = c1;
-            else if (tl.sp > 0) tl.cur = stack[--tl.sp];
-            else { trav_finish(w, lane, tl); fin = true; }
-        }
-        const bool at_leaf = tl.mode == T_TRAV && tl.cur < 0;
-        if (__ballot_sync(0xffffffffu, at_leaf)) {
-            uint32_t first = 0, cnt = 0;
-            if (at_leaf) {
-                const uint32_t code = ~(uint32_t)tl.cur;
-                first = code >> 3; cnt = code & 7u;
-                w.pending[lane] += (int)cnt;
-            }
-#pragma unroll 1
-            for (uint32_t i = 0; i < (uint32_t)kMaxLeafDev; ++i) {
-                const bool has = i < cnt;
-                const unsigned m = __ballot_sync(0xffffffffu, has);
-                if (m == 0) break;
-                if (has) w.queue[nQ + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | (first + i);
-                nQ += __popc(m);
-            }
-            if (at_leaf) {
-                if (tl.sp > 0) tl.cur = stack[--tl.sp];
-                else { trav_finish(w, lane, tl); fin = true; }
-            }
-        }
-        if (nQ >= 32) break;
-        if (__ballot_sync(0xffffffffu, fin)) {
-            if (can_fetch && __popc(__ballot_sync(0xffffffffu, tl.mode == T_FETCH)) >= kFetchThreshold) break;
-            if (__ballot_sync(0xffffffffu, tl.mode == T_TRAV) == 0) break;
-        }
-    }
-    __syncwarp();
-}
-
-__global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_constant__ SceneDev S, const __grid_constant__ WavePool Q,
-                                                                  int cur_list) {
-    __shared__ TravShared wsh[kBlockThreads / 32];
-    TravShared& w = wsh[threadIdx.x >> 5];
-    const int lane = threadIdx.x & 31;
-    const unsigned int nT = Q.cnt[WC_NT0 + cur_list];
-    const unsigned int* __restrict__ list = Q.listT[cur_list];
-    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NC] = 0;  // wave_regen (previous kernel) has consumed listC
-    int stack[kStackDepth];
-    TravLane tl;
-    tl.mode = T_FETCH; tl.kind = RAY_SCATTER; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f;
-    int nQ = 0, nH = 0;
-    bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
-    while (true) {
-        const unsigned mT = __ballot_sync(0xffffffffu, tl.mode == T_TRAV);
-        if (nH >= 32 || (nH > 0 && mT == 0 && nQ == 0)) {
-            const int nb = min(nH, 32);
-            nH -= nb;
-            trav_depth_batch(S, w, lane, nH, nb);
-            __syncwarp();
-            if (tl.mode == T_WAIT && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
-            continue;
-        }
-        if (nQ >= 32 || (nQ > 0 && mT == 0)) {
-            const int nb = min(nQ, 32);
-            nQ -= nb;
-            trav_quadric_batch(S, Q, w, lane, nQ, nb, nH);
-            __syncwarp();
-            if (tl.mode == T_WAIT && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
-            continue;
-        }
-        const unsigned mF = __ballot_sync(0xffffffffu, tl.mode == T_FETCH);
-        if (mF && (__popc(mF) >= kFetchThreshold || mT == 0)) {
-            // ---- flush finished rays: result to the slot, slot to the list of its post kernel
-            const bool flush = tl.mode == T_FETCH && tl.has_result;
-            const unsigned int p = w.pid[lane];
-            const bool fa = flush && tl.kind == RAY_SCATTER, fb = flush && tl.kind == RAY_SHADOW;
-            const unsigned ma = __ballot_sync(0xffffffffu, fa), mb = __ballot_sync(0xffffffffu, fb);
-            unsigned int base_a = 0, base_b = 0;
-            if (ma && lane == __ffs(ma) - 1) base_a = atomicAdd(&Q.cnt[WC_NA], (unsigned int)__popc(ma));
-            if (mb && lane == __ffs(mb) - 1) base_b = atomicAdd(&Q.cnt[WC_NB], (unsigned int)__popc(mb));
-            if (ma) base_a = __shfl_sync(0xffffffffu, base_a, __ffs(ma) - 1);
-            if (mb) base_b = __shfl_sync(0xffffffffu, base_b, __ffs(mb) - 1);
-            if (fa) { Q.hit_count[p] = w.count[lane]; Q.listA[base_a + __popc(ma & ((1u << lane) - 1u))] = p; }
-            if (fb) { Q.tau_fixed[p] = w.tau[lane]; Q.listB[base_b + __popc(mb & ((1u << lane) - 1u))] = p; }
-            tl.has_result = false;
-            // ---- fetch the next rays of the wave
-            if (!exhausted) {
-                unsigned int base = 0;
-                if (lane == __ffs(mF) - 1) base = atomicAdd(&Q.cnt[WC_CURSOR], (unsigned int)__popc(mF));
-                base = __shfl_sync(0xffffffffu, base, __ffs(mF) - 1);
-                if (tl.mode == T_FETCH) {
-                    const unsigned int idx = base + (unsigned int)__popc(mF & ((1u << lane) - 1u));
-                    if (idx < nT) {
-                        const unsigned int np = __ldg(list + idx);
-                        const float4 ro = Q.ray_o[np], rd = Q.ray_d[np];
-                        const int kind = __float_as_int(rd.w);
-                        w.ray[0][lane] = ro.x; w.ray[1][lane] = ro.y; w.ray[2][lane] = ro.z;
-                        w.ray[3][lane] = rd.x; w.ray[4][lane] = rd.y; w.ray[5][lane] = rd.z;
-                        w.ray[6][lane] = ro.w;
-                        w.kind[lane] = kind; w.pid[lane] = np;
-                        w.count[lane] = 0; w.pending[lane] = 0; w.t_bound[lane] = 0x7f800000u; w.tau[lane] = 0LL;
-                        const RaySetup rs = ray_setup(mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
-                        tl.idir = rs.idir; tl.ood = rs.ood;
-                        tl.kind = kind; tl.tmax = ro.w; tl.sp = 0; tl.cur = 0;
-                        const bool nothing = S.n == 0 || (kind == RAY_SHADOW && !(ro.w > 0.0f));
-                        if (nothing) tl.has_result = true;   // stays in T_FETCH: flushed at the next fetch step
-                        else tl.mode = T_TRAV;
-                    } else {
-                        tl.mode = T_DONE;
-                    }
-                }
-                if (base + (unsigned int)__popc(mF) >= nT) exhausted = true;
-            } else if (tl.mode == T_FETCH) {
-                tl.mode = T_DONE;
-            }
-            __syncwarp();
-            continue;
-        }
-        if (mT == 0) break;  // queues empty, nothing to flush or fetch: every lane is done
-        trav_rounds(S, w, lane, tl, stack, nQ, !exhausted);
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// post kernels: one thread per listed slot, grid-stride in whole warps so that the aggregated
-// list appends at the end of each round are executed by converged warps
+// list / counter helpers
 // ------------------------------------------------------------------------------------------
 struct WaveCounters { unsigned int scatter, shadow, hits, over; };
 
@@ -324,6 +81,290 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
 }
 enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2 };
 
+
+// ------------------------------------------------------------------------------------------
+// wave_trav<KIND>: one kernel per ray kind (free-flight / shadow), so that neither the node loop nor
+// the batches carry the other kind's code.  Leaves hold ONE Gaussian and a leaf CHILD hit by the ray
+// is queued as a candidate straight from its parent's slab test (no leaf visit).
+// ------------------------------------------------------------------------------------------
+constexpr int kTravQueueCap = 32 + 64;    // < 32 left over + two leaf children per lane and round
+constexpr int kTravHitQueueCap = 64;      // shadow overlaps: < 32 left over + one quadric batch
+constexpr unsigned kFetchThreshold = 8;   // fetch new rays when this many lanes are free
+
+template <int KIND> struct TravShared;
+template <> struct TravShared<RAY_SCATTER> {
+    float ray[7][32];               // o.xyz d.xyz lim of the lane's current ray
+    unsigned int pid[32];           // pool slot of the lane's ray
+    int count[32];                  // overlaps found (may exceed kWaveCap = overflow)
+    int pending[32];                // queued candidates of the lane
+    unsigned int t_bound[32];       // pruning bound, float bits (non-negative floats order as uints)
+    uint32_t queue[kTravQueueCap];  // (owner lane << 27) | leaf-order Gaussian index
+};
+template <> struct TravShared<RAY_SHADOW> {
+    float ray[7][32];
+    unsigned int pid[32];
+    int pending[32];                // queued candidates + queued overlaps of the lane
+    long long tau[32];              // fixed-point optical depth
+    uint32_t queue[kTravQueueCap];
+    uint32_t hq_id[kTravHitQueueCap];
+    float hq_a[kTravHitQueueCap], hq_b[kTravHitQueueCap];
+};
+
+enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
+
+struct TravLane {
+    int mode, cur, sp;
+    bool has_result;
+    f3 idir, ood;
+    float tmax;
+};
+
+// free-flight rays: quadric test of up to 32 candidates; overlaps go to the owner's slot as (t0, t1, index)
+__device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const WavePool& Q, TravShared<RAY_SCATTER>& w, int lane,
+                                                      int q_begin, int nb) {
+    if (lane < nb) {
+        const uint32_t e = w.queue[q_begin + lane];
+        const int owner = (int)(e >> 27);
+        const uint32_t gi = e & 0x07ffffffu;
+        const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
+        const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
+        const GaussRec g = load_gauss(S.gauss, gi);
+        const RayQuad q = ray_quad(g, o, d);
+        float t0, t1;
+        if (quad_intersect(q, &t0, &t1)) {
+            const float tb = __uint_as_float(w.t_bound[owner]);
+            if (!(t0 > tb)) {
+                const int slot = atomicAdd(&w.count[owner], 1);
+                if (slot < kWaveCap) {
+                    const size_t at = (size_t)slot * Q.P + w.pid[owner];
+                    Q.hit_t0[at] = t0; Q.hit_t1[at] = t1; Q.hit_gi[at] = gi;
+                    if (t1 < tb) {
+                        // pruning only: CONSERVATIVE estimate of this component's full optical depth
+                        // (fast intrinsics; 1.5x margin covers the FP32 slack of the exact expression)
+                        const float dn = g.density * g.norm;
+                        const float inv4A = __fdividef(1.0f, 4.0f * q.A);
+                        const float K = dn * sqrtf(6.2831853f * inv4A) * __expf(-0.5f * (q.C0 - q.B * q.B * inv4A));
+                        const float iden = rsqrtf(8.0f * q.A);
+                        const float full = K * (erff_ni((q.B + 2.0f * q.A * t1) * iden) - erff_ni((q.B + 2.0f * q.A * t0) * iden));
+                        if (full > 1.5f * w.ray[6][owner]) atomicMin(&w.t_bound[owner], __float_as_uint(t1));
+                    }
+                }
+            }
+        }
+        atomicSub(&w.pending[owner], 1);
+    }
+}
+
+// shadow rays: quadric test; overlaps with a non-empty clipped interval go to the depth queue
+__device__ __forceinline__ void shadow_quadric_batch(const SceneDev& S, TravShared<RAY_SHADOW>& w, int lane, int q_begin, int nb,
+                                                     int& nH) {
+    bool to_hq = false;
+    uint32_t e = 0; float ha = 0.f, hb = 0.f;
+    if (lane < nb) {
+        e = w.queue[q_begin + lane];
+        const int owner = (int)(e >> 27);
+        const uint32_t gi = e & 0x07ffffffu;
+        const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
+        const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
+        const GaussRec g = load_gauss(S.gauss, gi);
+        const RayQuad q = ray_quad(g, o, d);
+        float t0, t1;
+        if (quad_intersect(q, &t0, &t1) && w.tau[owner] <= tau_cutoff_fixed()) {
+            ha = fmaxf(0.0f, t0); hb = fminf(w.ray[6][owner], t1);
+            to_hq = hb > ha;   // stays pending until the depth batch has added it
+        }
+        if (!to_hq) atomicSub(&w.pending[owner], 1);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, to_hq);
+    if (to_hq) {
+        const int pos = nH + __popc(m & ((1u << lane) - 1u));
+        w.hq_id[pos] = e; w.hq_a[pos] = ha; w.hq_b[pos] = hb;
+    }
+    nH += __popc(m);
+}
+
+// exact clipped optical depth of up to 32 shadow overlaps (gmm.h:563-571, gaussian.h:208-231)
+__device__ __forceinline__ void shadow_depth_batch(const SceneDev& S, TravShared<RAY_SHADOW>& w, int lane, int h_begin, int nb) {
+    if (lane < nb) {
+        const uint32_t e = w.hq_id[h_begin + lane];
+        const int owner = (int)(e >> 27);
+        const uint32_t gi = e & 0x07ffffffu;
+        const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
+        const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
+        const GaussRec g = load_gauss(S.gauss, gi);
+        const RayQuad q = ray_quad(g, o, d);
+        const DepthConst c = depth_const(g, q);
+        const float F1 = erff_ni(erf_arg(c, w.hq_b[h_begin + lane]));
+        const float F0 = erff_ni(erf_arg(c, w.hq_a[h_begin + lane]));
+        const float tau = __fmul_rn(c.K, __fsub_rn(F1, F0));
+        atomicAdd((unsigned long long*)&w.tau[owner], (unsigned long long)__double2ll_rn((double)tau * kTauFixed));
+        atomicSub(&w.pending[owner], 1);
+    }
+}
+
+// node rounds: one slab step per traversing lane and round; hit leaf children are queued as candidates.
+// Runs until a full candidate batch is queued, enough lanes are free to fetch, or no lane traverses.
+template <int KIND>
+__device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>& w, int lane, TravLane& tl, int stack[kStackDepth],
+                                            int& nQ, bool can_fetch) {
+    while (true) {
+        bool l0 = false, l1 = false, fin = false;
+        int c0 = 0, c1 = 0;
+        if (tl.mode == T_TRAV) {
+            float tlimit;
+            bool stop;
+            if (KIND == RAY_SCATTER) {
+                TravShared<RAY_SCATTER>& ws = reinterpret_cast<TravShared<RAY_SCATTER>&>(w);
+                tlimit = __uint_as_float(ws.t_bound[lane]); stop = ws.count[lane] > kWaveCap;
+            } else {
+                TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
+                tlimit = tl.tmax; stop = wh.tau[lane] > tau_cutoff_fixed();
+            }
+            RaySetup rs; rs.idir = tl.idir; rs.ood = tl.ood;
+            bool h0, h1; float tn0, tn1;
+            node_slabs(S.nodes, tl.cur, rs, tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
+            if (stop) { h0 = h1 = false; tl.sp = 0; }
+            l0 = h0 && c0 < 0 && ((~c0) & 7);   // leaf child with a Gaussian in it
+            l1 = h1 && c1 < 0 && ((~c1) & 7);
+            const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
+            w.pending[lane] += (int)l0 + (int)l1;
+            if (i0 && i1) {
+                const bool swap = tn1 < tn0;
+                stack[tl.sp++] = swap ? c0 : c1;
+                tl.cur = swap ? c1 : c0;
+            } else if (i0) tl.cur = c0;
+            else if (i1) tl.cur = c1;
+            else if (tl.sp > 0) tl.cur = stack[--tl.sp];
+            else { fin = true; tl.mode = T_WAIT; }   // resolved below once the pushes are counted
+        }
+        const unsigned m0 = __ballot_sync(0xffffffffu, l0);
+        if (l0) w.queue[nQ + __popc(m0 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | ((uint32_t)(~c0) >> 3);
+        nQ += __popc(m0);
+        const unsigned m1 = __ballot_sync(0xffffffffu, l1);
+        if (l1) w.queue[nQ + __popc(m1 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | ((uint32_t)(~c1) >> 3);
+        nQ += __popc(m1);
+        if (fin && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
+        if (nQ >= 32) break;
+        if (__ballot_sync(0xffffffffu, fin)) {
+            if (can_fetch && __popc(__ballot_sync(0xffffffffu, tl.mode == T_FETCH)) >= kFetchThreshold) break;
+            if (__ballot_sync(0xffffffffu, tl.mode == T_TRAV) == 0) break;
+        }
+    }
+    __syncwarp();
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
+    __shared__ TravShared<KIND> wsh[kBlockThreads / 32];
+    TravShared<KIND>& w = wsh[threadIdx.x >> 5];
+    const SceneDev& S = A.scene;
+    const int lane = threadIdx.x & 31;
+    const unsigned int nT = Q.cnt[KIND == RAY_SCATTER ? WC_NTS : WC_NTH];
+    const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : Q.listTh;
+    unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : WC_CURSOR_H];
+    // the list consumed by the previous kernel of the chain (regen -> travS -> postA -> travH -> postB) is free again
+    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[KIND == RAY_SCATTER ? WC_NC : WC_NA] = 0;
+    int stack[kStackDepth];
+    TravLane tl;
+    tl.mode = T_FETCH; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f;
+    int nQ = 0, nH = 0;
+    unsigned int n_escaped = 0;
+    bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
+    while (true) {
+        const unsigned mT = __ballot_sync(0xffffffffu, tl.mode == T_TRAV);
+        if (KIND == RAY_SHADOW) {
+            if (nH >= 32 || (nH > 0 && mT == 0 && nQ == 0)) {
+                TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
+                const int nb = min(nH, 32);
+                nH -= nb;
+                shadow_depth_batch(S, wh, lane, nH, nb);
+                __syncwarp();
+                if (tl.mode == T_WAIT && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
+                continue;
+            }
+        }
+        if (nQ >= 32 || (nQ > 0 && mT == 0)) {
+            const int nb = min(nQ, 32);
+            nQ -= nb;
+            if (KIND == RAY_SCATTER) scatter_quadric_batch(S, Q, reinterpret_cast<TravShared<RAY_SCATTER>&>(w), lane, nQ, nb);
+            else shadow_quadric_batch(S, reinterpret_cast<TravShared<RAY_SHADOW>&>(w), lane, nQ, nb, nH);
+            __syncwarp();
+            if (tl.mode == T_WAIT && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
+            continue;
+        }
+        const unsigned mF = __ballot_sync(0xffffffffu, tl.mode == T_FETCH);
+        if (mF && (__popc(mF) >= kFetchThreshold || mT == 0)) {
+            // ---- flush finished rays: result to the slot, slot to the list of its post kernel
+            const bool flush = tl.mode == T_FETCH && tl.has_result;
+            const unsigned int p = w.pid[lane];
+            if (KIND == RAY_SCATTER) {
+                TravShared<RAY_SCATTER>& ws = reinterpret_cast<TravShared<RAY_SCATTER>&>(w);
+                const int K = flush ? ws.count[lane] : 0;
+                // a ray that overlapped nothing ends the path here: environment radiance, sample written,
+                // slot back to the regeneration list (integrator.h:594-597; the target draw is not committed)
+                const bool esc = flush && K == 0;
+                if (esc) {
+                    const float4 s0 = Q.ps0[p];
+                    const uint4 s1 = Q.ps1[p];
+                    A.sampleL[s1.z] = make_float4(__fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0])), __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1])),
+                                                  __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2])), (float)s1.w);
+                }
+                if (flush && K > 0) Q.hit_count[p] = K;
+                wave_append(Q.listC, &Q.cnt[WC_NC], esc, p);
+                wave_append(Q.listA, &Q.cnt[WC_NA], flush && K > 0, p);
+            } else {
+                TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
+                if (flush) Q.tau_fixed[p] = wh.tau[lane];
+                wave_append(Q.listB, &Q.cnt[WC_NB], flush, p);
+            }
+            tl.has_result = false;
+            // ---- fetch the next rays of the wave
+            if (!exhausted) {
+                unsigned int base = 0;
+                if (lane == __ffs(mF) - 1) base = atomicAdd(cursor, (unsigned int)__popc(mF));
+                base = __shfl_sync(0xffffffffu, base, __ffs(mF) - 1);
+                if (tl.mode == T_FETCH) {
+                    const unsigned int idx = base + (unsigned int)__popc(mF & ((1u << lane) - 1u));
+                    if (idx < nT) {
+                        const unsigned int np = __ldg(list + idx);
+                        const float4 ro = Q.ray_o[np], rd = Q.ray_d[np];
+                        w.ray[0][lane] = ro.x; w.ray[1][lane] = ro.y; w.ray[2][lane] = ro.z;
+                        w.ray[3][lane] = rd.x; w.ray[4][lane] = rd.y; w.ray[5][lane] = rd.z;
+                        w.ray[6][lane] = ro.w;
+                        w.pid[lane] = np; w.pending[lane] = 0;
+                        if (KIND == RAY_SCATTER) {
+                            TravShared<RAY_SCATTER>& ws = reinterpret_cast<TravShared<RAY_SCATTER>&>(w);
+                            ws.count[lane] = 0; ws.t_bound[lane] = 0x7f800000u;
+                        } else {
+                            reinterpret_cast<TravShared<RAY_SHADOW>&>(w).tau[lane] = 0LL;
+                        }
+                        const RaySetup rs = ray_setup(mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
+                        tl.idir = rs.idir; tl.ood = rs.ood;
+                        tl.tmax = ro.w; tl.sp = 0; tl.cur = 0;
+                        const bool nothing = S.n == 0 || (KIND == RAY_SHADOW && !(ro.w > 0.0f));
+                        if (nothing) tl.has_result = true;   // stays in T_FETCH: flushed at the next fetch step
+                        else tl.mode = T_TRAV;
+                    } else {
+                        tl.mode = T_DONE;
+                    }
+                }
+                if (base + (unsigned int)__popc(mF) >= nT) exhausted = true;
+            } else if (tl.mode == T_FETCH) {
+                tl.mode = T_DONE;
+            }
+            __syncwarp();
+            continue;
+        }
+        if (mT == 0) break;  // queues empty, nothing to flush or fetch: every lane is done
+        trav_rounds<KIND>(S, w, lane, tl, stack, nQ, !exhausted);
+    }
+    (void)n_escaped;
+}
+
+// ------------------------------------------------------------------------------------------
+// post kernels: one thread per listed slot, grid-stride in whole warps so that the aggregated
+// list appends at the end of each round are executed by converged warps
+// ------------------------------------------------------------------------------------------
 // draw the free-flight target on a copy of the stream (committed in post A only if the ray overlaps
 // something, integrator.h:593-600) and publish the slot's next free-flight ray
 __device__ __forceinline__ void publish_scatter_ray(const WavePool& Q, unsigned int p, f3 o, f3 d, uint64_t rng_state, float* target) {
@@ -335,12 +376,9 @@ __device__ __forceinline__ void publish_scatter_ray(const WavePool& Q, unsigned 
 }
 
 // wave_regen: integrator.h:557-570
-__global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q,
-                                                          int cur_list) {
+__global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const unsigned int nC = Q.cnt[WC_NC];
-    if (blockIdx.x == 0 && threadIdx.x == 0) {  // lists consumed by the previous iteration's post kernels
-        Q.cnt[WC_NT0 + (cur_list ^ 1)] = 0; Q.cnt[WC_NA] = 0; Q.cnt[WC_NB] = 0;
-    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NB] = 0;  // consumed by wave_post_b, the previous kernel of the chain
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (nC + stride - 1) / stride;
@@ -374,16 +412,24 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
             ++cn.scatter;
             to_trav = true;
         }
-        wave_append(Q.listT[cur_list], &Q.cnt[WC_NT0 + cur_list], to_trav, p);
+        wave_append(Q.listTs, &Q.cnt[WC_NTS], to_trav, p);
     }
     wave_flush_counters(A, cn);
+    // listC is refilled by the very next kernel (escaping rays in wave_trav), so its counter is cleared
+    // here by the LAST block of this kernel to finish (every block has read nC by then)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned int t = atomicAdd(&Q.cnt[WC_TICKET], 1u);
+        if (t == gridDim.x - 1) { Q.cnt[WC_NC] = 0; Q.cnt[WC_TICKET] = 0; __threadfence(); }
+    }
 }
 
 // wave_post_a: integrator.h:593-678
-__global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q,
-                                                           int nxt_list) {
+__global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
     const unsigned int nA = Q.cnt[WC_NA];
+    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (nA + stride - 1) / stride;
@@ -472,18 +518,19 @@ __global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant_
                 }
             }
         }
-        wave_append(Q.listT[nxt_list], &Q.cnt[WC_NT0 + nxt_list], dest == DEST_TRAV, p);
+        wave_append(Q.listTh, &Q.cnt[WC_NTH], dest == DEST_TRAV, p);
         wave_append(Q.listC, &Q.cnt[WC_NC], dest == DEST_REGEN, p);
     }
     wave_flush_counters(A, cn);
 }
 
 // wave_post_b: integrator.h:669-699
-__global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q,
-                                                           int nxt_list) {
+__global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
     const unsigned int nB = Q.cnt[WC_NB];
-    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_CURSOR] = 0;  // wave_trav of this iteration is over
+    if (blockIdx.x == 0 && threadIdx.x == 0) {  // both traversal kernels of this iteration are over
+        Q.cnt[WC_NTH] = 0; Q.cnt[WC_CURSOR_S] = 0; Q.cnt[WC_CURSOR_H] = 0;
+    }
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (nB + stride - 1) / stride;
@@ -548,7 +595,7 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
                 }
             }
         }
-        wave_append(Q.listT[nxt_list], &Q.cnt[WC_NT0 + nxt_list], dest == DEST_TRAV, p);
+        wave_append(Q.listTs, &Q.cnt[WC_NTS], dest == DEST_TRAV, p);
         wave_append(Q.listC, &Q.cnt[WC_NC], dest == DEST_REGEN, p);
     }
     wave_flush_counters(A, cn);
@@ -565,43 +612,48 @@ __global__ void wave_init_kernel(const __grid_constant__ WavePool Q, unsigned in
 // ------------------------------------------------------------------------------------------
 int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsigned int* h_cnt, cudaStream_t s,
                        unsigned int* launches) {
-    static int trav_blocks_per_sm = 0;
-    if (!trav_blocks_per_sm) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trav_blocks_per_sm, wave_trav_kernel, kBlockThreads, 0);
-        if (trav_blocks_per_sm < 1) trav_blocks_per_sm = 1;
+    static int bps_s = 0, bps_h = 0;
+    if (!bps_s) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_h, wave_trav_kernel<RAY_SHADOW>, kBlockThreads, 0);
+        bps_s = std::max(bps_s, 1); bps_h = std::max(bps_h, 1);
     }
     const unsigned int slots = (unsigned int)std::min<unsigned long long>((unsigned long long)q.P, a.work_count);
     wave_init_kernel<<<(std::max(slots, (unsigned int)kWaveCounters) + 255) / 256, 256, 0, s>>>(q, slots);
     ++*launches;
-    const int grid_trav = num_sms * trav_blocks_per_sm;
+    // persistent traversal grids, but never more warps than a wave of `slots` rays can keep busy
+    const int need_blocks = (int)std::max(1u, (slots + kBlockThreads - 1) / kBlockThreads);
+    const int grid_s = std::min(num_sms * bps_s, need_blocks), grid_h = std::min(num_sms * bps_h, need_blocks);
     const int grid_post = std::max(1, (int)std::min<unsigned int>((slots + 127) / 128, (unsigned int)num_sms * 16));
     const int grid_post256 = std::max(1, (grid_post + 1) / 2);
-    int cur = 0, iters = 0;
-    const int kBatch = 16;
+    int iters = 0;
+    const int kBatch = 8;
     cudaEvent_t ev;
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return -1;
     const char* prof_env = getenv("VR_WAVE_PROFILE");
     const bool prof = prof_env && prof_env[0] == '1';
-    cudaEvent_t pe[5];
-    double pt[4] = {0, 0, 0, 0};
+    cudaEvent_t pe[6];
+    double pt[5] = {0, 0, 0, 0, 0};
     if (prof) for (auto& e : pe) cudaEventCreate(&e);
     while (true) {
         for (int b = 0; b < kBatch; ++b) {
+            // chain: every kernel consumes the list the previous one filled
             if (prof) cudaEventRecord(pe[0], s);
-            wave_regen_kernel<<<grid_post256, 256, 0, s>>>(a, q, cur);
+            wave_regen_kernel<<<grid_post256, 256, 0, s>>>(a, q);
             if (prof) cudaEventRecord(pe[1], s);
-            wave_trav_kernel<<<grid_trav, kBlockThreads, 0, s>>>(a.scene, q, cur);
+            wave_trav_kernel<RAY_SCATTER><<<grid_s, kBlockThreads, 0, s>>>(a, q);
             if (prof) cudaEventRecord(pe[2], s);
-            wave_post_a_kernel<<<grid_post, 128, 0, s>>>(a, q, cur ^ 1);
+            wave_post_a_kernel<<<grid_post, 128, 0, s>>>(a, q);
             if (prof) cudaEventRecord(pe[3], s);
-            wave_post_b_kernel<<<grid_post256, 256, 0, s>>>(a, q, cur ^ 1);
+            wave_trav_kernel<RAY_SHADOW><<<grid_h, kBlockThreads, 0, s>>>(a, q);
+            if (prof) cudaEventRecord(pe[4], s);
+            wave_post_b_kernel<<<grid_post256, 256, 0, s>>>(a, q);
             if (prof) {
-                cudaEventRecord(pe[4], s);
-                cudaEventSynchronize(pe[4]);
-                for (int k = 0; k < 4; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); pt[k] += ms; }
+                cudaEventRecord(pe[5], s);
+                cudaEventSynchronize(pe[5]);
+                for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); pt[k] += ms; }
             }
-            *launches += 4;
-            cur ^= 1;
+            *launches += 5;
             ++iters;
         }
         if (cudaMemcpyAsync(h_cnt, q.cnt, sizeof(unsigned int) * kWaveCounters, cudaMemcpyDeviceToHost, s) != cudaSuccess ||
@@ -609,15 +661,15 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
             cudaEventDestroy(ev);
             return -1;
         }
-        // after an iteration: rays left = listT[cur] (filled by the post kernels) + slots waiting for regeneration
+        // after wave_post_b: rays left = listTs + slots waiting for a new sample
         const bool more_samples = h_cnt[WC_NEXT_SAMPLE] < a.work_count;
-        if (h_cnt[WC_NT0 + cur] == 0 && (h_cnt[WC_NC] == 0 || !more_samples)) break;
+        if (h_cnt[WC_NTS] == 0 && (h_cnt[WC_NC] == 0 || !more_samples)) break;
         if (iters > (1 << 24)) break;
     }
     cudaEventDestroy(ev);
     if (prof) {
-        fprintf(stderr, "[wave] samples %u iters %d  regen %.3f ms  trav %.3f ms  post_a %.3f ms  post_b %.3f ms\n", a.work_count, iters,
-                pt[0], pt[1], pt[2], pt[3]);
+        fprintf(stderr, "[wave] samples %u iters %d  regen %.3f  trav_scatter %.3f  post_a %.3f  trav_shadow %.3f  post_b %.3f ms\n",
+                a.work_count, iters, pt[0], pt[1], pt[2], pt[3], pt[4]);
         for (auto& e : pe) cudaEventDestroy(e);
     }
     return iters;
