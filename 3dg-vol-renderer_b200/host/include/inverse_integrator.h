@@ -1,0 +1,175 @@
+// inverse_integrator.h -- InverseIntegrator / StochasticFiniteDiffInverseIntegrator of the drop-in
+// API (reference inverse_integrator.h:34-247).
+//
+// optimize() keeps the reference's contract: Scene by value, false when there is nothing to optimise
+// or a step fails, progress as ./sfd_output/iter_%04d.ppm + stdout lines every save_every iterations,
+// a final high-spp render.  One iteration is the reference's estimator (:114-207): a recorded base
+// render, S sign vectors s in {-1,+1}^D, S recorded renders of params + s*eps, per-Gaussian loss
+// differences over the union of the pixels either render touched, grad = mean_s F_diff*s/eps, Adam.
+// All of it runs on the device behind vr_sfd_begin / vr_sfd_accumulate / vr_sfd_apply; with several
+// devices (VR_DEVICES) the image rows are split, the per-Gaussian partial sums (exact fixed point)
+// are added on the host in device order, and every device applies the same Adam step.
+//
+// Differences, all additive: the sign vectors come from a SEEDED mt19937 (SFDDConfig::seed; the
+// reference seeds from std::random_device) so runs are reproducible; the optimised
+// scene, which the reference discards, is available from optimized_scene() afterwards; output
+// directory and the final render's spp are configurable (defaults = the reference's).
+#pragma once
+#include <chrono>
+#include <cstdio>
+#include <filesystem>
+#include <iomanip>
+#include <iostream>
+#include <random>
+#include <sstream>
+
+#include "integrator.h"
+#include "optimizer.h"
+
+static inline void ensure_dir_exists(const std::string& path) {
+    std::filesystem::path p(path);
+    if (!std::filesystem::exists(p)) std::filesystem::create_directories(p);
+}
+static inline std::string out_filename(const std::string& dir, int it) {
+    char name[32];
+    std::snprintf(name, sizeof name, "/iter_%04d.ppm", it);
+    return dir + name;
+}
+// per-pixel L1 loss (inverse_integrator.h:20-29)
+static inline void compute_pixel_losses(const Image& I, const Image& Iref, std::vector<float>& out) {
+    const size_t n = size_t(I.get_width()) * I.get_height();
+    out.assign(n, 0.0f);
+    const float *a = I.data(), *b = Iref.data();
+    for (size_t p = 0; p < n; ++p) out[p] = std::abs(a[3 * p] - b[3 * p]) + std::abs(a[3 * p + 1] - b[3 * p + 1]) + std::abs(a[3 * p + 2] - b[3 * p + 2]);
+}
+
+class InverseIntegrator {
+protected:
+    const std::shared_ptr<Camera> camera;
+
+public:
+    InverseIntegrator(const std::shared_ptr<Camera>& cam) : camera(cam) {}
+    virtual ~InverseIntegrator() = default;
+    virtual bool optimize(Scene scene_initial, const Image& I_ref) = 0;
+};
+
+struct SFDDConfig {
+    int max_iters = 1000;
+    int save_every = 25;
+    int num_stoch_samples = 4;
+    float lr = 1e-2f;
+    // ---- additions
+    uint32_t seed = 0x5fdd2025u;           // sign-vector stream
+    std::string output_dir = "./sfd_output";
+    int final_samples = 16384;             // inverse_integrator.h:231
+    bool verbose = true;
+};
+
+class StochasticFiniteDiffInverseIntegrator : public InverseIntegrator {
+    std::shared_ptr<MultiScatterGaussians> forward_integrator;
+    SFDDConfig cfg;
+    Scene result;
+    std::vector<float> final_params;
+    double last_mean_loss = 0.0;
+
+    static double mean_loss(const Image& a, const Image& ref) {
+        std::vector<float> l;
+        compute_pixel_losses(a, ref, l);
+        double s = 0.0;
+        for (float x : l) s += x;
+        return l.empty() ? 0.0 : s / double(l.size());
+    }
+
+public:
+    StochasticFiniteDiffInverseIntegrator(const std::shared_ptr<Camera>& cam, const std::shared_ptr<MultiScatterGaussians>& fwd,
+                                          const SFDDConfig& config = SFDDConfig())
+        : InverseIntegrator(cam), forward_integrator(fwd), cfg(config) {}
+
+    bool optimize(Scene scene_initial, const Image& I_ref) override {
+        using clock = std::chrono::high_resolution_clock;
+        ensure_dir_exists(cfg.output_dir);
+        if (!scene_initial.gmm || scene_initial.gmm->empty()) {
+            std::cerr << "Scene has no GMM." << std::endl;
+            return false;
+        }
+        result = scene_initial;
+        GaussianMixtureModel& model = result.gmm->at(0);
+        std::vector<float> params;
+        model.pack_parameters(params);
+        if (params.empty()) {
+            std::cerr << "No params to optimize." << std::endl;
+            return false;
+        }
+        const std::vector<float> eps = make_default_eps_for_params(params);
+        const int n = int(model.get_num_gaussians());
+        const int D = int(params.size());
+        const int W = int(I_ref.get_width()), H = int(I_ref.get_height());
+        const int S = cfg.num_stoch_samples;
+
+        vrhost::Session& dev = vrhost::Session::get();
+        const int nd = dev.num_devices();
+        for (int i = 0; i < nd; ++i) {
+            vrhost::upload_lights_and_camera(dev, i, result, *camera);
+            dev.check(i, vr_sfd_begin(dev.ctx(i), n, params.data(), eps.data(), cfg.lr, 0.9f, 0.999f, 1e-8f));
+            dev.check(i, vr_sfd_set_target(dev.ctx(i), W, H, I_ref.data()));
+        }
+        std::mt19937 rng(cfg.seed);
+        std::vector<int8_t> signs(size_t(S) * D);
+        std::vector<double> F(size_t(S) * n), Fpart(size_t(S) * n);
+        Image I_base(W, H);
+        const auto t0 = clock::now();
+
+        for (int iter = 0; iter < cfg.max_iters; ++iter) {
+            for (int8_t& s : signs) s = (rng() & 1u) ? 1 : -1;
+            vrhost::for_each_device(dev, [&](int i) {
+                vr_render_params rp{};
+                rp.integrator = VR_INTEGRATOR_MULTI_SCATTER; rp.solver = forward_integrator->get_solver();
+                rp.width = W; rp.height = H; rp.spp = forward_integrator->get_num_samples(); rp.min_bounces = forward_integrator->get_min_bounces();
+                rp.x1 = W; rp.y1 = H; rp.part_rank = i; rp.part_count = nd; rp.record = 1;
+                dev.check(i, vr_sfd_reset_fdiff(dev.ctx(i), S));
+                dev.check(i, vr_sfd_accumulate(dev.ctx(i), &rp, S, signs.data()));
+            });
+            if (nd == 1) {
+                dev.check(0, vr_sfd_apply(dev.ctx(0), S, signs.data(), nullptr, nullptr));
+            } else {
+                std::fill(F.begin(), F.end(), 0.0);
+                for (int i = 0; i < nd; ++i) {
+                    dev.check(i, vr_sfd_read(dev.ctx(i), Fpart.data(), nullptr));
+                    for (size_t k = 0; k < F.size(); ++k) F[k] += Fpart[k];
+                }
+                for (int i = 0; i < nd; ++i) dev.check(i, vr_sfd_apply(dev.ctx(i), S, signs.data(), F.data(), nullptr));
+            }
+            if (iter % cfg.save_every == 0) {
+                dev.check(0, vr_sfd_get_params(dev.ctx(0), params.data()));
+                apply_params_to_gmm_local(params, model);
+                const std::string fn = out_filename(cfg.output_dir, iter);
+                forward_integrator->render(result, I_base);
+                I_base.make_PPM(fn);
+                last_mean_loss = mean_loss(I_base, I_ref);
+                if (cfg.verbose) {
+                    const std::chrono::duration<double> el = clock::now() - t0;
+                    std::cout << "[SFD] iter " << iter << " saving " << fn << std::endl;
+                    std::cout << "[SFD] iter " << iter << " mean loss: " << last_mean_loss << std::endl;
+                    std::cout << "[SFD] iter " << iter << " elapsed " << el.count() << "s" << std::endl;
+                }
+            }
+        }
+        dev.check(0, vr_sfd_get_params(dev.ctx(0), params.data()));
+        apply_params_to_gmm_local(params, model);
+        final_params = params;
+        forward_integrator->set_num_samples(cfg.final_samples);
+        forward_integrator->render(result, I_base);
+        I_base.make_PPM(out_filename(cfg.output_dir, cfg.max_iters - 1));
+        last_mean_loss = mean_loss(I_base, I_ref);
+        if (cfg.verbose) {
+            std::cout << "[SFD] Optimization finished." << std::endl;
+            std::cout << "Final mean loss: " << last_mean_loss << std::endl;
+        }
+        return true;
+    }
+
+    // ---- additions: what the reference throws away
+    const Scene& optimized_scene() const { return result; }
+    const std::vector<float>& optimized_params() const { return final_params; }
+    double final_mean_loss() const { return last_mean_loss; }
+};

@@ -3,7 +3,7 @@
  * The drop-in boundary of the B200 implementation of the per-ray volume-integration hot path of
  * wantonsushi/3DG-vol-renderer.  The reference has no FFI: its boundary is a set of C++ abstract
  * classes.  The host-side mirror of those classes
- * (3dg-vol-renderer_b200/host/include/*.h) flattens Scene/Camera into the POD arrays below and
+ * (the headers under 3dg-vol-renderer_b200/host/include) flattens Scene/Camera into the POD arrays below and
  * calls these entry points; nothing else crosses into CUDA.
  *
  * Conventions: every function returns a vr_status (0 = ok) and never throws; a context is
