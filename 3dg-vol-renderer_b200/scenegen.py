@@ -52,6 +52,38 @@ def generate(n: int, seed: int, nonuniform: bool = False, albedo_range=(0.25, 0.
                 albedo=albedo.astype(np.float32), lights=DEFAULT_LIGHTS.astype(np.float32))
 
 
+EPS11 = np.array([0.02] * 3 + [0.10] * 3 + [0.05] * 3 + [0.25, 0.5], np.float32)   # gmm.h:677-706
+
+
+def pack_parameters(scene: dict) -> np.ndarray:
+    """11 floats per Gaussian like GaussianMixtureModel::pack_parameters (gmm.h:583-628): mean, Rodrigues
+    vector of the (proper) eigenvector rotation, log sqrt(eigenvalues), log density, logit albedo."""
+    n = len(scene["density"])
+    c = np.asarray(scene["cov6"], np.float64)
+    cov = np.empty((n, 3, 3))
+    cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2] = c.T
+    cov[:, 1, 0], cov[:, 2, 0], cov[:, 2, 1] = cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 2]
+    lam, vec = np.linalg.eigh(cov)
+    flip = np.linalg.det(vec) < 0
+    vec[flip, :, 0] *= -1.0
+    from scipy.spatial.transform import Rotation
+    rod = Rotation.from_matrix(vec).as_rotvec()
+    out = np.empty((n, 11), np.float32)
+    out[:, 0:3] = scene["mean"]
+    out[:, 3:6] = rod
+    out[:, 6:9] = np.log(np.maximum(np.sqrt(np.maximum(lam, 0.0)), 1e-12))
+    out[:, 9] = np.log(np.maximum(np.asarray(scene["density"], np.float64), 1e-12))
+    a = np.clip(np.asarray(scene["albedo"], np.float64), 1e-7, 1.0 - 1e-7)
+    out[:, 10] = np.log(a / (1.0 - a))
+    return out.reshape(-1)
+
+
+def orbit_cameras(n_views: int = 16, radius: float = 6.0, height: float = 1.0, look=(0.0, 1.0, 0.0)):
+    """camera positions on the orbit of tests/main.cpp:94-101 (look-at + (r sin a, h, r cos a))"""
+    ang = 2.0 * np.pi * np.arange(n_views) / n_views
+    return [(look[0] + radius * np.sin(a), look[1] + height, look[2] + radius * np.cos(a)) for a in ang]
+
+
 def write_gmm(path: str, scene: dict) -> None:
     with open(path, "w") as f:
         for l in scene.get("lights", []):

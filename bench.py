@@ -44,6 +44,12 @@ CONFIGS = {
                label="C1: make_random 1k Gaussians, 512^2, 64 spp, FreeFlightGaussians"),
     "c2": dict(n=10000, seed=2, nonuniform=True, W=1024, H=1024, spp=256, integrator="ms",
                label="C2: make_nonuniform_random 10k Gaussians, 1024^2, 256 spp, MultiScatterGaussians"),
+    "c3": dict(n=200000, seed=3, nonuniform=False, W=2048, H=2048, spp=1024, integrator="ms", albedo_range=(0.9, 0.999),
+               label="C3: make_random 200k Gaussians, albedo U(.9,.999), 2048^2, 1024 spp, MultiScatterGaussians"),
+    # inverse rendering: one step = one full SFD + Adam iteration over all views
+    "c4": dict(n=10000, seed=2, nonuniform=True, W=512, H=512, spp=256, integrator="ms", views=16, S=4,
+               label="C4: fit the C2 scene (10k Gaussians, 110k parameters) to 16 orbit views, 512^2, 256 spp per render, "
+                     "S=4 sign vectors, SFD + Adam"),
 }
 
 
@@ -60,7 +66,8 @@ def _pkg(name):
 
 def make_scene(cfg):
     sg = _pkg("scenegen")
-    return sg.generate(cfg["n"], cfg["seed"], nonuniform=cfg["nonuniform"])
+    kw = {"albedo_range": cfg["albedo_range"]} if "albedo_range" in cfg else {}
+    return sg.generate(cfg["n"], cfg["seed"], nonuniform=cfg["nonuniform"], **kw)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -148,6 +155,118 @@ class ClockSampler:
                     samples=len(sm))
 
 
+def run_inverse(a, cfg, scene, workload, rank, world, local_rank):
+    """Config C4: inverse rendering.  One step = one StochasticFiniteDiffInverseIntegrator iteration
+    (inverse_integrator.h:114-207) over ALL target views: per view a recorded base render and S recorded
+    perturbed renders, per-Gaussian loss differences, then -- the one real exchange -- a SUM all-reduce of
+    the S*N int64 fixed-point partial sums over NCCL, and the same Adam step on every rank.
+    Views are dealt round-robin to the ranks (rows are split instead when views < ranks)."""
+    import torch
+    import torch.distributed as dist
+    vr = _pkg("volrender"); sg = _pkg("scenegen"); mr = _pkg("multirank")
+    W, H, spp, S = cfg["W"], cfg["H"], cfg["spp"], cfg["S"]   # (main() has set the device and the process group)
+    n_views = a.views or cfg["views"]
+    N = cfg["n"]; D = 11 * N
+    ctx = vr.Context(local_rank)
+    ctx.set_lights(scene["lights"], ENV)
+    cams = [vr.camera_basis("pinhole", pos, look=(0, 1, 0), fov=0.78539816339) for pos in sg.orbit_cameras(n_views)]
+    my_views, part_rank, part_count = mr.split_for_views(rank, world, n_views)
+    # ---- setup (untimed): targets = renders of the target parameters; start = target + N(0, eps^2)
+    p_target = sg.pack_parameters(scene)
+    eps = np.tile(sg.EPS11, N)
+    rs = np.random.RandomState(1234)
+    p_start = (p_target + rs.normal(size=D).astype(np.float32) * eps).astype(np.float32)
+    rp_full = vr.Context.params(vr.INTEGRATOR_MS, W, H, spp)
+    rp = vr.Context.params(vr.INTEGRATOR_MS, W, H, spp, part=(part_rank, part_count), record=True)
+    ctx.set_gmm_params(p_target)
+    targets = {}
+    for v in my_views:
+        ctx.set_camera(cams[v])
+        img, _ = ctx.render(rp_full)
+        targets[v] = torch.from_numpy(img).pin_memory()
+    ctx.sfd_begin(p_start, eps, lr=1e-2)
+    fview = None
+    sign_rs = np.random.RandomState(4321)      # same stream on every rank: the sign vectors are shared
+
+    def iteration():
+        nonlocal fview
+        signs = np.where(sign_rs.randint(0, 2, size=(S, D)) > 0, 1, -1).astype(np.int8)
+        ctx.sfd_reset(S)
+        for v in my_views:
+            ctx.set_camera(cams[v])
+            ctx.sfd_set_target(targets[v].numpy())           # H2D of the view's target, every iteration
+            ctx.sfd_accumulate(rp, signs)
+        if world > 1:
+            if fview is None:
+                fview = mr.device_int64_view(ctx.sfd_fdiff_dev(), S * N, local_rank)
+            mr.allreduce_fdiff_(fview)
+            torch.cuda.synchronize()
+        ctx.sfd_apply(signs, None)
+        return ctx.sfd_read(S)[1]                             # base L1 loss sum of this rank (D2H)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    losses = []
+    for _ in range(a.warmup):
+        losses.append(iteration())
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(a.steps):
+        losses.append(iteration())
+    e1.record()
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([wall_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        wall_ms = float(t.item())
+        lt = torch.tensor(losses, dtype=torch.float64, device="cuda")
+        dist.all_reduce(lt)
+        losses = lt.tolist()
+    params_end = ctx.sfd_params()
+    ctx.close()
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+    if rank != 0:
+        return
+    ms_per_step = wall_ms / a.steps
+    samples_per_iter = n_views * (1 + S) * W * H * spp
+    mean_loss = [l / (n_views * W * H) for l in losses]
+    cpu = None
+    if not a.no_cpu_baseline:
+        c2 = dict(cfg); c2["integrator"] = "ms"
+        cpu = cpu_render_sample(c2, scene)
+        cpu = dict(cpu, value=cpu["value"] * 1e6 / samples_per_iter, unit="iterations/s",
+                   sample=cpu["sample"] + f"; iterations/s derived as render throughput / {samples_per_iter} samples per iteration "
+                                          "(the (1+S)*views renders are >99% of a reference iteration)")
+    print(json.dumps({
+        "metric": "inverse-render iters/sec", "value": 1e3 / ms_per_step, "unit": "iterations/s", "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload, "views": n_views, "image": [W, H], "spp": spp, "S": S, "parameters": D,
+                   "partition": f"views round-robin over {world} rank(s)" if n_views >= world else f"rows interleaved over {world} rank(s)",
+                   "collective": "all_reduce(SUM, int64, S*N) of the fixed-point F_diff sums per iteration" if world > 1 else "none (1 rank)",
+                   "timing": "host wall clock around K iterations between device synchronisations (each iteration ends in a D2H read), max over ranks",
+                   "l2": "each render streams a pass buffer larger than L2"},
+        "e2e": {"value": 1e3 / ms_per_step, "unit": "iterations/s", "ms_per_step": ms_per_step,
+                "h2d_bytes_per_step": len(my_views) * (3 * W * H * 4 + S * D) + S * D, "d2h_bytes_per_step": 8},
+        "throughput_msamples_per_s": samples_per_iter / (ms_per_step * 1e-3) * 1e-6,
+        "mean_l1_loss_per_iteration": mean_loss, "param_rms_distance_to_target": float(np.sqrt(np.mean((params_end - p_target) ** 2))),
+        "param_rms_distance_at_start": float(np.sqrt(np.mean((p_start - p_target) ** 2))),
+        "clocks": clocks, "cpu_baseline": cpu, "gpu_launches": None, "roofline": None,
+    }))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -156,6 +275,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (perfect square) for quick runs")
+    ap.add_argument("--views", type=int, default=0, help="c4: override the number of target views")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
     ap.add_argument("--wave-slots", type=int, default=0)
@@ -196,6 +316,8 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if a.config == "c4":
+        return run_inverse(a, cfg, scene, workload, rank, world, local_rank)
     ctx = vr.Context(local_rank)
     ctx.set_option("engine", a.engine)
     if a.wave_slots:
