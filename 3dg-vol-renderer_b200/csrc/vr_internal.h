@@ -35,7 +35,12 @@ struct RenderArgs {
 // ---- wavefront engine (vr_wave.cu): a pool of P path slots whose state lives in global memory
 // (sized to stay resident in the 126 MB L2), advanced one ray per iteration by four small kernels.
 constexpr int kWaveCap = 16;         // free-flight overlaps kept per path slot (more = re-trace by the arena kernel)
-enum { WC_NTS = 0, WC_NTH, WC_NA, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, kWaveCounters = 16 };
+// post-A work is binned by overlap count so that the warps of wave_post_a_kernel run slots of similar
+// length: class 0: K = 1, 1: K = 2, 2: K = 3..4, 3: K = 5..8, 4: K > 8 (incl. overflow)
+constexpr int kPostClasses = 5;
+enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, WC_NA /* kPostClasses counters */,
+       kWaveCounters = 16 };
+static_assert(WC_NA + kPostClasses <= kWaveCounters, "wave counters overflow");
 struct WavePool {
     int P;
     float4* ray_o;        // o.xyz, lim (scatter: sampled optical depth, shadow: tmax)
@@ -50,7 +55,7 @@ struct WavePool {
     long long* tau_fixed; // shadow rays: sum of clipped optical depths in 2^-40 units
     unsigned int* listTs;  // slots whose free-flight ray waits for traversal
     unsigned int* listTh;  // slots whose shadow ray waits for traversal
-    unsigned int* listA;
+    unsigned int* listA;   // [kPostClasses][P]
     unsigned int* listB;
     unsigned int* listC;
     unsigned int* cnt;    // kWaveCounters

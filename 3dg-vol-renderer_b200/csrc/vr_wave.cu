@@ -32,7 +32,7 @@ namespace vr {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t wave_pool_bytes(int P) {
     const size_t p = (size_t)P;
-    return align256(p * 16) * 5 + align256(p * 4) + align256(p * 4 * kWaveCap) * 3 + align256(p * 8) + align256(p * 4) * 5 +
+    return align256(p * 16) * 5 + align256(p * 4) + align256(p * 4 * kWaveCap) * 3 + align256(p * 8) + align256(p * 4) * 4 + align256(p * 4 * kPostClasses) +
            align256(kWaveCounters * 4);
 }
 void wave_pool_carve(WavePool* q, int P, void* base) {
@@ -47,7 +47,7 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     q->hit_gi = (uint32_t*)take(p * 4 * kWaveCap);
     q->tau_fixed = (long long*)take(p * 8);
     q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4);
-    q->listA = (unsigned int*)take(p * 4); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
+    q->listA = (unsigned int*)take(p * 4 * kPostClasses); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
     q->cnt = (unsigned int*)take(kWaveCounters * 4);
 }
 
@@ -80,6 +80,7 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
     }
 }
 enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2 };
+__device__ __forceinline__ int post_class(int K) { return K <= 1 ? 0 : K == 2 ? 1 : K <= 4 ? 2 : K <= 8 ? 3 : 4; }
 
 
 // ------------------------------------------------------------------------------------------
@@ -263,7 +264,10 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
     const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : Q.listTh;
     unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : WC_CURSOR_H];
     // the list consumed by the previous kernel of the chain (regen -> travS -> postA -> travH -> postB) is free again
-    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[KIND == RAY_SCATTER ? WC_NC : WC_NA] = 0;
+    if (blockIdx.x == 0 && threadIdx.x < kPostClasses) {
+        if (KIND == RAY_SCATTER) { if (threadIdx.x == 0) Q.cnt[WC_NC] = 0; }
+        else Q.cnt[WC_NA + threadIdx.x] = 0;
+    }
     int stack[kStackDepth];
     TravLane tl;
     tl.mode = T_FETCH; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f;
@@ -311,7 +315,10 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
                 }
                 if (flush && K > 0) Q.hit_count[p] = K;
                 wave_append(Q.listC, &Q.cnt[WC_NC], esc, p);
-                wave_append(Q.listA, &Q.cnt[WC_NA], flush && K > 0, p);
+                const int cls = post_class(K);
+#pragma unroll
+                for (int c = 0; c < kPostClasses; ++c)
+                    wave_append(Q.listA + (size_t)c * Q.P, &Q.cnt[WC_NA + c], flush && K > 0 && cls == c, p);
             } else {
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
                 if (flush) Q.tau_fixed[p] = wh.tau[lane];
@@ -425,20 +432,33 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
     }
 }
 
-// wave_post_a: integrator.h:593-678
+// wave_post_a: integrator.h:593-678.  Slots arrive binned by overlap count (post_class); every class
+// starts at a multiple of 32 in the flattened index space, so a warp only ever holds slots of one class.
+// Class 0 (one overlap, the commonest case in sparse mixtures) has a register-only fast path that
+// performs the same operations in the same order as the general walk does for K = 1.
 __global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
-    const unsigned int nA = Q.cnt[WC_NA];
+    unsigned int nA[kPostClasses], base[kPostClasses + 1];
+    base[0] = 0;
+#pragma unroll
+    for (int c = 0; c < kPostClasses; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
+    const unsigned int total = base[kPostClasses];
     if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
-    const unsigned int rounds = (nA + stride - 1) / stride;
+    const unsigned int rounds = (total + stride - 1) / stride;
     for (unsigned int r = 0; r < rounds; ++r) {
         const unsigned int i = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
         int dest = DEST_NONE;
         unsigned int p = 0;
-        if (i < nA) {
-            p = Q.listA[i];
+        int cls = 0;
+#pragma unroll
+        for (int c = 1; c < kPostClasses; ++c) cls += (i >= base[c]) ? 1 : 0;
+        unsigned int j = i, nc = nA[0];
+#pragma unroll
+        for (int c = 1; c < kPostClasses; ++c) if (cls == c) { j = i - base[c]; nc = nA[c]; }
+        if (i < total && j < nc) {
+            p = Q.listA[(size_t)cls * Q.P + j];
             const int K = Q.hit_count[p];
             float4 s0 = Q.ps0[p];
             uint4 s1 = Q.ps1[p];
@@ -458,30 +478,68 @@ __global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant_
                 cn.hits += (unsigned int)K;
                 Pcg rng; rng.state = (uint64_t)s1.x | ((uint64_t)s1.y << 32); rng.inc = 3;
                 rng.next_u32();  // commit the target draw
-                LocalStore<kWaveCap> st;
-#pragma unroll 1
-                for (int s = 0; s < K; ++s) {  // exact depth constants (gaussian.h:208-231) of the gathered overlaps
-                    const size_t at = (size_t)s * Q.P + p;
-                    const uint32_t gi = Q.hit_gi[at];
+                float t = -1.0f, albedo = 0.0f;
+                bool solved = false;
+                if (K == 1 && A.solver <= 1) {
+                    // ---- one overlap: enter event (empty segment), exit event with the single active component,
+                    //      analytic inverse when the target falls inside (integrator.h:422-498, distance_solvers.h:163-171)
+                    const uint32_t gi = Q.hit_gi[p];
+                    const float t0 = Q.hit_t0[p], t1 = Q.hit_t1[p];
                     const GaussRec g = load_gauss(S.gauss, gi);
-                    const DepthConst c = depth_const(g, ray_quad(g, o, d));
-                    st.F(F_T0, s) = Q.hit_t0[at]; st.F(F_T1, s) = Q.hit_t1[at];
-                    st.F(F_A, s) = c.A; st.F(F_B, s) = c.B; st.F(F_K, s) = c.K; st.F(F_DEN, s) = c.den;
-                    st.U(U_GI, s) = gi;
-                }
-                int na = 0;
-                const float t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na);
-                if (A.record_bits) {  // integrator.h:616-644
-                    int x, y, si;
-                    lane_xy(A, s1.z, &x, &y, &si);
-                    uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
-                    const float tlim = __fadd_rn(t, 1e-6f);
-                    for (int s = 0; s < K; ++s)
-                        if (t < 0.0f || st.F(F_T0, s) <= tlim) {
-                            const uint32_t orig = __ldg(S.orig + st.U(U_GI, s));
+                    const RayQuad q = ray_quad(g, o, d);
+                    const DepthConst c = depth_const(g, q);
+                    const float F0 = erff_ni(erf_arg(c, t0));
+                    const float F1 = erff_ni(erf_arg(c, t1));
+                    const float seg = __fmul_rn(c.K, __fsub_rn(F1, F0));
+                    if (seg > target_tau) {   // float and double comparisons agree: the conversion is exact
+                        float t_an;
+                        if (solve_t_given_tau(g, q, t0, t1, target_tau, &t_an)) { t = clampf(t_an, t0, t1); solved = true; }
+                    } else {
+                        solved = true;        // the ray leaves the component: t stays -1
+                    }
+                    if (solved) {
+                        if (t >= 0.0f) {       // evaluate_albedo over the one active component (gmm.h:128-143)
+                            const float mu = gauss_mu_t(g, add3(o, scale3(t, d)));
+                            const float a = __fdiv_rn(__fadd_rn(0.0f, __fmul_rn(mu, g.albedo)), __fadd_rn(0.0f, mu));
+                            albedo = a < 0.0f ? 0.0f : (1.0f < a ? 1.0f : a);
+                        }
+                        if (A.record_bits && (t < 0.0f || t0 <= __fadd_rn(t, 1e-6f))) {  // integrator.h:616-644
+                            int x, y, si;
+                            lane_xy(A, s1.z, &x, &y, &si);
+                            uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
+                            const uint32_t orig = __ldg(S.orig + gi);
                             const uint32_t bit = 1u << (orig & 31u);
                             if (!(row[orig >> 5] & bit)) atomicOr(row + (orig >> 5), bit);
                         }
+                    }
+                }
+                if (!solved) {
+                    LocalStore<kWaveCap> st;
+#pragma unroll 1
+                    for (int s = 0; s < K; ++s) {  // exact depth constants (gaussian.h:208-231) of the gathered overlaps
+                        const size_t at = (size_t)s * Q.P + p;
+                        const uint32_t gi = Q.hit_gi[at];
+                        const GaussRec g = load_gauss(S.gauss, gi);
+                        const DepthConst c = depth_const(g, ray_quad(g, o, d));
+                        st.F(F_T0, s) = Q.hit_t0[at]; st.F(F_T1, s) = Q.hit_t1[at];
+                        st.F(F_A, s) = c.A; st.F(F_B, s) = c.B; st.F(F_K, s) = c.K; st.F(F_DEN, s) = c.den;
+                        st.U(U_GI, s) = gi;
+                    }
+                    int na = 0;
+                    t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na);
+                    if (A.record_bits) {  // integrator.h:616-644
+                        int x, y, si;
+                        lane_xy(A, s1.z, &x, &y, &si);
+                        uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
+                        const float tlim = __fadd_rn(t, 1e-6f);
+                        for (int s = 0; s < K; ++s)
+                            if (t < 0.0f || st.F(F_T0, s) <= tlim) {
+                                const uint32_t orig = __ldg(S.orig + st.U(U_GI, s));
+                                const uint32_t bit = 1u << (orig & 31u);
+                                if (!(row[orig >> 5] & bit)) atomicOr(row + (orig >> 5), bit);
+                            }
+                    }
+                    if (t >= 0.0f) albedo = evaluate_albedo(S, st, na, add3(o, scale3(t, d)));
                 }
                 if (t < 0.0f) {
                     s0.x = __fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0]));
@@ -490,7 +548,6 @@ __global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant_
                     A.sampleL[s1.z] = make_float4(s0.x, s0.y, s0.z, (float)s1.w);
                 } else {
                     const f3 pos = add3(o, scale3(t, d));
-                    const float albedo = evaluate_albedo(S, st, na, pos);
                     const bool is_env = rng.uniform() < __fdiv_rn(1.0f, (float)(S.nl + 1));
                     ++cn.shadow;
                     f3 wi; float dist; int light;
