@@ -14,6 +14,8 @@ vr::SceneDev vr_context::scene_dev() const {
     SceneDev S{};
     S.gauss = gauss_leaf.as<float4>();
     S.nodes = nodes.as<float4>();
+    S.qnodes = qnodes.as<uint4>();
+    for (int k = 0; k < 3; ++k) { S.qorg[k] = qorg[k]; S.qcell[k] = qcell[k]; }
     S.orig = perm.as<uint32_t>();
     S.n = n;
     S.nl = nl;
@@ -191,7 +193,7 @@ int set_gmm_from_device(vr_context* ctx, int n) {
     VR_CUDA(ctx->gauss_orig.ensure(m * 48)); VR_CUDA(ctx->gauss_leaf.ensure(m * 48));
     VR_CUDA(ctx->perm.ensure(m * 4)); VR_CUDA(ctx->leaf_of_orig.ensure(m * 4));
     VR_CUDA(ctx->box_lo.ensure(m * 12)); VR_CUDA(ctx->box_hi.ensure(m * 12));
-    VR_CUDA(ctx->nodes.ensure(64));
+    VR_CUDA(ctx->nodes.ensure(64)); VR_CUDA(ctx->qnodes.ensure(32));
     ctx->n = n; ctx->n_nodes = 0;
     if (n > 0) {
         // slab tests run on (lo*idir - o*idir): position error ~ 1 ulp of the larger of |lo|, |o|.  Pad for
@@ -210,6 +212,12 @@ int set_gmm_from_device(vr_context* ctx, int n) {
             return fail(ctx, VR_ERR_UNSUPPORTED, "hierarchy deeper than the traversal stack");
         VR_CUDA(ctx->nodes.ensure(bvh.nodes.size() * sizeof(BvhNode)));
         VR_CUDA(cudaMemcpyAsync(ctx->nodes.p, bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode), cudaMemcpyHostToDevice, ctx->stream));
+        std::vector<BvhNodeQ> qn;
+        BvhQuantGrid grid;
+        quantize_bvh(bvh, &grid, &qn);
+        for (int k = 0; k < 3; ++k) { ctx->qorg[k] = grid.org[k]; ctx->qcell[k] = grid.cell[k]; }
+        VR_CUDA(ctx->qnodes.ensure(qn.size() * sizeof(BvhNodeQ)));
+        VR_CUDA(cudaMemcpyAsync(ctx->qnodes.p, qn.data(), qn.size() * sizeof(BvhNodeQ), cudaMemcpyHostToDevice, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(ctx->perm.p, bvh.perm.data(), (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
         launch_permute_gaussians(n, ctx->gauss_orig.as<float4>(), ctx->perm.as<uint32_t>(), ctx->gauss_leaf.as<float4>(),
                                  ctx->leaf_of_orig.as<uint32_t>(), ctx->stream);

@@ -158,4 +158,48 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
     out->max_leaf = b.max_leaf;
 }
 
+void quantize_bvh(const BvhBuildResult& tree, BvhQuantGrid* grid, std::vector<BvhNodeQ>* out) {
+    out->clear();
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    auto child_box = [](const BvhNode& nd, int c, int axis, float* l, float* h) {
+        const float* p = axis == 0 ? (c == 0 ? nd.c0x : nd.c1x) : axis == 1 ? (c == 0 ? nd.c0y : nd.c1y) : (c == 0 ? nd.c0z : nd.c1z);
+        *l = p[0]; *h = p[1];
+    };
+    for (const BvhNode& nd : tree.nodes)
+        for (int c = 0; c < 2; ++c)
+            for (int a = 0; a < 3; ++a) {
+                float l, h;
+                child_box(nd, c, a, &l, &h);
+                if (!(l <= h) || !std::isfinite(l) || !std::isfinite(h)) continue;
+                lo[a] = std::min(lo[a], (double)l); hi[a] = std::max(hi[a], (double)h);
+            }
+    const double kSteps = 65000.0;   // leaves room for the outward rounding below
+    for (int a = 0; a < 3; ++a) {
+        if (!(lo[a] <= hi[a])) { lo[a] = 0.0; hi[a] = 0.0; }
+        grid->cell[a] = std::max((float)((hi[a] - lo[a]) / kSteps), 1e-20f);
+        grid->cell[a] = std::nextafter(grid->cell[a], std::numeric_limits<float>::infinity());  // never under-covers the extent
+        grid->org[a] = (float)(lo[a] - 4.0 * (double)grid->cell[a]);
+    }
+    out->resize(tree.nodes.size());
+    for (size_t i = 0; i < tree.nodes.size(); ++i) {
+        const BvhNode& nd = tree.nodes[i];
+        BvhNodeQ& q = (*out)[i];
+        for (int c = 0; c < 2; ++c) {
+            for (int a = 0; a < 3; ++a) {
+                float l, h;
+                child_box(nd, c, a, &l, &h);
+                uint32_t ql = 0, qh = 0;   // an empty child (zero-count leaf) becomes a point outside the scene
+                if (l <= h && std::isfinite(l) && std::isfinite(h)) {
+                    const double org = (double)grid->org[a], cell = (double)grid->cell[a];
+                    const double fl = std::floor(((double)l - org) / cell) - 1.0, fh = std::ceil(((double)h - org) / cell) + 1.0;
+                    ql = (uint32_t)std::min(65535.0, std::max(0.0, fl));
+                    qh = (uint32_t)std::min(65535.0, std::max(0.0, fh));
+                }
+                q.box[3 * c + a] = ql | (qh << 16);
+            }
+            q.child[c] = nd.child[c];
+        }
+    }
+}
+
 }  // namespace vr

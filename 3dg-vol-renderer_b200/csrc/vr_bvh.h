@@ -30,6 +30,19 @@ struct BvhBuildResult {
 
 constexpr int kMaxLeaf = 1;         // one Gaussian per leaf: the traversal kernels queue a leaf CHILD as a candidate directly
 
+// Compact form of the same tree for the wavefront traversal kernels (vr_wave.cu), whose bound is the L1
+// data pipe (profiles/r01_v5): 32 B per node instead of 64, i.e. two 128-bit loads per step.  Child boxes
+// are quantised to 16 bits per coordinate on ONE global grid (org + q * cell) and rounded OUTWARD by a
+// full extra cell, so a quantised box always contains the float box: the hierarchy only culls and the
+// quadric test still decides every overlap, hence results cannot change.
+struct BvhNodeQ {
+    uint32_t box[6];       // child 0: x, y, z then child 1: x, y, z; each word = q_lo | (q_hi << 16)
+    int32_t child[2];      // same codes as BvhNode::child
+};
+static_assert(sizeof(BvhNodeQ) == 32, "BvhNodeQ must be 32 bytes");
+struct BvhQuantGrid { float org[3], cell[3]; };
+void quantize_bvh(const BvhBuildResult& tree, BvhQuantGrid* grid, std::vector<BvhNodeQ>* out);
+
 // lo/hi: 3*n floats each (per-Gaussian boxes).  Deterministic.
 void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out);
 

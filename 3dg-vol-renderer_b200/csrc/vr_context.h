@@ -40,7 +40,8 @@ struct vr_context {
     bool has_gmm = false;
     int n = 0, n_nodes = 0, bvh_depth = 0;
     vr::DevBuf mean3, cov6, density, albedo;       // inputs as given (original order)
-    vr::DevBuf gauss_orig, gauss_leaf, nodes, perm, leaf_of_orig, box_lo, box_hi;
+    vr::DevBuf gauss_orig, gauss_leaf, nodes, qnodes, perm, leaf_of_orig, box_lo, box_hi;
+    float qorg[3] = {0.f, 0.f, 0.f}, qcell[3] = {1.f, 1.f, 1.f};   // grid of the compact tree (vr_bvh.h BvhQuantGrid)
     // ---- sphere mixture
     bool has_smm = false;
     int n_spheres = 0;

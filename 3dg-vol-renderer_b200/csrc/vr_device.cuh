@@ -8,6 +8,8 @@ namespace vr {
 struct SceneDev {
     const float4* gauss;    // 3 x float4 per Gaussian, LEAF order
     const float4* nodes;    // 4 x float4 per hierarchy node (vr_bvh.h BvhNode)
+    const uint4* qnodes;    // 2 x uint4 per node: the same tree with 16-bit boxes (vr_bvh.h BvhNodeQ), wavefront kernels
+    float qorg[3], qcell[3];
     const uint32_t* orig;   // leaf order -> original index
     int n;
     int nl;
@@ -78,6 +80,37 @@ __device__ __forceinline__ void node_slabs(const float4* __restrict__ nodes, int
     tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tlimit));
     *h1 = tmin <= tmax; *tn1 = tmin;
     *c0 = __float_as_int(n3.x); *c1 = __float_as_int(n3.y);
+}
+
+// the same test on the compact tree: coordinate = qorg + q * qcell, so the slab distance of a quantised plane is
+// q * (qcell * idir) + (qorg * idir - o * idir) = q * s + b with per-ray s, b.  The 16-bit values are turned into
+// floats exactly (2^23 + q has q in its low mantissa bits; subtracting 2^23 is exact).
+struct RaySetupQ { f3 s, b; };
+__device__ __forceinline__ RaySetupQ ray_setup_q(const SceneDev& S, f3 o, f3 d) {
+    const RaySetup r = ray_setup(o, d);
+    RaySetupQ q;
+    q.s = mk3(S.qcell[0] * r.idir.x, S.qcell[1] * r.idir.y, S.qcell[2] * r.idir.z);
+    q.b = mk3(fmaf(S.qorg[0], r.idir.x, -r.ood.x), fmaf(S.qorg[1], r.idir.y, -r.ood.y), fmaf(S.qorg[2], r.idir.z, -r.ood.z));
+    return q;
+}
+__device__ __forceinline__ float q_lo(unsigned int w) { return __uint_as_float((w & 0xffffu) | 0x4B000000u) - 8388608.0f; }
+__device__ __forceinline__ float q_hi(unsigned int w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)) - 8388608.0f; }
+__device__ __forceinline__ void node_slabs_q(const uint4* __restrict__ qnodes, int ni, const RaySetupQ& rs, float tlimit,
+                                             bool* h0, bool* h1, float* tn0, float* tn1, int* c0, int* c1) {
+    const uint4 u = __ldg(qnodes + 2 * (size_t)ni), v = __ldg(qnodes + 2 * (size_t)ni + 1);
+    float ax = fmaf(q_lo(u.x), rs.s.x, rs.b.x), bx = fmaf(q_hi(u.x), rs.s.x, rs.b.x);
+    float ay = fmaf(q_lo(u.y), rs.s.y, rs.b.y), by = fmaf(q_hi(u.y), rs.s.y, rs.b.y);
+    float az = fmaf(q_lo(u.z), rs.s.z, rs.b.z), bz = fmaf(q_hi(u.z), rs.s.z, rs.b.z);
+    float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tlimit));
+    *h0 = tmin <= tmax; *tn0 = tmin;
+    ax = fmaf(q_lo(u.w), rs.s.x, rs.b.x); bx = fmaf(q_hi(u.w), rs.s.x, rs.b.x);
+    ay = fmaf(q_lo(v.x), rs.s.y, rs.b.y); by = fmaf(q_hi(v.x), rs.s.y, rs.b.y);
+    az = fmaf(q_lo(v.y), rs.s.z, rs.b.z); bz = fmaf(q_hi(v.y), rs.s.z, rs.b.z);
+    tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tlimit));
+    *h1 = tmin <= tmax; *tn1 = tmin;
+    *c0 = (int)v.z; *c1 = (int)v.w;
 }
 
 // ------------------------------------------------------------------------------------------

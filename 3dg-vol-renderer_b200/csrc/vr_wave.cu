@@ -116,7 +116,7 @@ enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
 struct TravLane {
     int mode, cur, sp;
     bool has_result;
-    f3 idir, ood;
+    RaySetupQ rq;
     float tmax;
 };
 
@@ -221,9 +221,8 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
                 tlimit = tl.tmax; stop = wh.tau[lane] > tau_cutoff_fixed();
             }
-            RaySetup rs; rs.idir = tl.idir; rs.ood = tl.ood;
             bool h0, h1; float tn0, tn1;
-            node_slabs(S.nodes, tl.cur, rs, tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
+            node_slabs_q(S.qnodes, tl.cur, tl.rq, tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
             if (stop) { h0 = h1 = false; tl.sp = 0; }
             l0 = h0 && c0 < 0 && ((~c0) & 7);   // leaf child with a Gaussian in it
             l1 = h1 && c1 < 0 && ((~c1) & 7);
@@ -345,8 +344,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
                         } else {
                             reinterpret_cast<TravShared<RAY_SHADOW>&>(w).tau[lane] = 0LL;
                         }
-                        const RaySetup rs = ray_setup(mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
-                        tl.idir = rs.idir; tl.ood = rs.ood;
+                        tl.rq = ray_setup_q(S, mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
                         tl.tmax = ro.w; tl.sp = 0; tl.cur = 0;
                         const bool nothing = S.n == 0 || (KIND == RAY_SHADOW && !(ro.w > 0.0f));
                         if (nothing) tl.has_result = true;   // stays in T_FETCH: flushed at the next fetch step
