@@ -173,12 +173,12 @@ void quantize_bvh(const BvhBuildResult& tree, BvhQuantGrid* grid, std::vector<Bv
                 if (!(l <= h) || !std::isfinite(l) || !std::isfinite(h)) continue;
                 lo[a] = std::min(lo[a], (double)l); hi[a] = std::max(hi[a], (double)h);
             }
-    const double kSteps = 65000.0;   // leaves room for the outward rounding below
+    const double kSteps = 64000.0;   // leaves room for the outward rounding below
     for (int a = 0; a < 3; ++a) {
         if (!(lo[a] <= hi[a])) { lo[a] = 0.0; hi[a] = 0.0; }
         grid->cell[a] = std::max((float)((hi[a] - lo[a]) / kSteps), 1e-20f);
         grid->cell[a] = std::nextafter(grid->cell[a], std::numeric_limits<float>::infinity());  // never under-covers the extent
-        grid->org[a] = (float)(lo[a] - 4.0 * (double)grid->cell[a]);
+        grid->org[a] = (float)(lo[a] - 6.0 * (double)grid->cell[a]);
     }
     out->resize(tree.nodes.size());
     for (size_t i = 0; i < tree.nodes.size(); ++i) {
@@ -191,7 +191,7 @@ void quantize_bvh(const BvhBuildResult& tree, BvhQuantGrid* grid, std::vector<Bv
                 uint32_t ql = 0, qh = 0;   // an empty child (zero-count leaf) becomes a point outside the scene
                 if (l <= h && std::isfinite(l) && std::isfinite(h)) {
                     const double org = (double)grid->org[a], cell = (double)grid->cell[a];
-                    const double fl = std::floor(((double)l - org) / cell) - 1.0, fh = std::ceil(((double)h - org) / cell) + 1.0;
+                    const double fl = std::floor(((double)l - org) / cell) - 2.0, fh = std::ceil(((double)h - org) / cell) + 2.0;
                     ql = (uint32_t)std::min(65535.0, std::max(0.0, fl));
                     qh = (uint32_t)std::min(65535.0, std::max(0.0, fh));
                 }

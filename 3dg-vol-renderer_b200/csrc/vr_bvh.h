@@ -32,8 +32,8 @@ constexpr int kMaxLeaf = 1;         // one Gaussian per leaf: the traversal kern
 
 // Compact form of the same tree for the wavefront traversal kernels (vr_wave.cu), whose bound is the L1
 // data pipe (profiles/r01_v5): 32 B per node instead of 64, i.e. two 128-bit loads per step.  Child boxes
-// are quantised to 16 bits per coordinate on ONE global grid (org + q * cell) and rounded OUTWARD by a
-// full extra cell, so a quantised box always contains the float box: the hierarchy only culls and the
+// are quantised to 16 bits per coordinate on ONE global grid (org + q * cell) and rounded OUTWARD by two
+// extra cells (one for the float rounding of the slab arithmetic, one for the folded 2^23 offset, vr_device.cuh), so a quantised box always contains the float box: the hierarchy only culls and the
 // quadric test still decides every overlap, hence results cannot change.
 struct BvhNodeQ {
     uint32_t box[6];       // child 0: x, y, z then child 1: x, y, z; each word = q_lo | (q_hi << 16)

@@ -83,32 +83,43 @@ __device__ __forceinline__ void node_slabs(const float4* __restrict__ nodes, int
 }
 
 // the same test on the compact tree: coordinate = qorg + q * qcell, so the slab distance of a quantised plane is
-// q * (qcell * idir) + (qorg * idir - o * idir) = q * s + b with per-ray s, b.  The 16-bit values are turned into
-// floats exactly (2^23 + q has q in its low mantissa bits; subtracting 2^23 is exact).
-struct RaySetupQ { f3 s, b; };
+// q * (qcell * idir) + (qorg * idir - o * idir) = q * s + b with per-ray s, b.  A 16-bit value q is turned into the
+// float 2^23 + q by ONE byte permute (q lands in the low mantissa bits of 0x4B000000) and the 2^23 is folded into the
+// per-ray offset: t = (2^23 + q) * s + (b - 2^23 * s).  Rounding that offset costs at most half a cell of slab
+// distance, which the builder's outward rounding by two whole cells covers (vr_bvh.cpp quantize_bvh).  The permute
+// selector is per ray and axis: it picks the NEAR plane (lo for a positive direction, hi for a negative one) or the
+// FAR plane directly, so no min/max between the two planes of an axis is needed.
+struct RaySetupQ {
+    f3 s, b;                    // t = float(2^23 + q) * s + b
+    unsigned int near_sel[3];   // __byte_perm selectors of the near plane; far = near ^ 0x0022
+};
 __device__ __forceinline__ RaySetupQ ray_setup_q(const SceneDev& S, f3 o, f3 d) {
     const RaySetup r = ray_setup(o, d);
     RaySetupQ q;
     q.s = mk3(S.qcell[0] * r.idir.x, S.qcell[1] * r.idir.y, S.qcell[2] * r.idir.z);
-    q.b = mk3(fmaf(S.qorg[0], r.idir.x, -r.ood.x), fmaf(S.qorg[1], r.idir.y, -r.ood.y), fmaf(S.qorg[2], r.idir.z, -r.ood.z));
+    const f3 b = mk3(fmaf(S.qorg[0], r.idir.x, -r.ood.x), fmaf(S.qorg[1], r.idir.y, -r.ood.y), fmaf(S.qorg[2], r.idir.z, -r.ood.z));
+    q.b = mk3(fmaf(-8388608.0f, q.s.x, b.x), fmaf(-8388608.0f, q.s.y, b.y), fmaf(-8388608.0f, q.s.z, b.z));
+    // selector 0x7610: bytes (w.b0, w.b1, 0x00, 0x4B) = 2^23 + lo;  0x7632: (w.b2, w.b3, 0x00, 0x4B) = 2^23 + hi
+    q.near_sel[0] = q.s.x >= 0.0f ? 0x7610u : 0x7632u;
+    q.near_sel[1] = q.s.y >= 0.0f ? 0x7610u : 0x7632u;
+    q.near_sel[2] = q.s.z >= 0.0f ? 0x7610u : 0x7632u;
     return q;
 }
-__device__ __forceinline__ float q_lo(unsigned int w) { return __uint_as_float((w & 0xffffu) | 0x4B000000u) - 8388608.0f; }
-__device__ __forceinline__ float q_hi(unsigned int w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)) - 8388608.0f; }
+__device__ __forceinline__ float q_plane(unsigned int w, unsigned int sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)); }
 __device__ __forceinline__ void node_slabs_q(const uint4* __restrict__ qnodes, int ni, const RaySetupQ& rs, float tlimit,
                                              bool* h0, bool* h1, float* tn0, float* tn1, int* c0, int* c1) {
     const uint4 u = __ldg(qnodes + 2 * (size_t)ni), v = __ldg(qnodes + 2 * (size_t)ni + 1);
-    float ax = fmaf(q_lo(u.x), rs.s.x, rs.b.x), bx = fmaf(q_hi(u.x), rs.s.x, rs.b.x);
-    float ay = fmaf(q_lo(u.y), rs.s.y, rs.b.y), by = fmaf(q_hi(u.y), rs.s.y, rs.b.y);
-    float az = fmaf(q_lo(u.z), rs.s.z, rs.b.z), bz = fmaf(q_hi(u.z), rs.s.z, rs.b.z);
-    float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-    float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tlimit));
+    const unsigned int nx = rs.near_sel[0], ny = rs.near_sel[1], nz = rs.near_sel[2];
+    const unsigned int fx = nx ^ 0x0022u, fy = ny ^ 0x0022u, fz = nz ^ 0x0022u;
+    float tmin = fmaxf(fmaxf(fmaf(q_plane(u.x, nx), rs.s.x, rs.b.x), fmaf(q_plane(u.y, ny), rs.s.y, rs.b.y)),
+                       fmaxf(fmaf(q_plane(u.z, nz), rs.s.z, rs.b.z), 0.0f));
+    float tmax = fminf(fminf(fmaf(q_plane(u.x, fx), rs.s.x, rs.b.x), fmaf(q_plane(u.y, fy), rs.s.y, rs.b.y)),
+                       fminf(fmaf(q_plane(u.z, fz), rs.s.z, rs.b.z), tlimit));
     *h0 = tmin <= tmax; *tn0 = tmin;
-    ax = fmaf(q_lo(u.w), rs.s.x, rs.b.x); bx = fmaf(q_hi(u.w), rs.s.x, rs.b.x);
-    ay = fmaf(q_lo(v.x), rs.s.y, rs.b.y); by = fmaf(q_hi(v.x), rs.s.y, rs.b.y);
-    az = fmaf(q_lo(v.y), rs.s.z, rs.b.z); bz = fmaf(q_hi(v.y), rs.s.z, rs.b.z);
-    tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-    tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tlimit));
+    tmin = fmaxf(fmaxf(fmaf(q_plane(u.w, nx), rs.s.x, rs.b.x), fmaf(q_plane(v.x, ny), rs.s.y, rs.b.y)),
+                 fmaxf(fmaf(q_plane(v.y, nz), rs.s.z, rs.b.z), 0.0f));
+    tmax = fminf(fminf(fmaf(q_plane(u.w, fx), rs.s.x, rs.b.x), fmaf(q_plane(v.x, fy), rs.s.y, rs.b.y)),
+                 fminf(fmaf(q_plane(v.y, fz), rs.s.z, rs.b.z), tlimit));
     *h1 = tmin <= tmax; *tn1 = tmin;
     *c0 = (int)v.z; *c1 = (int)v.w;
 }

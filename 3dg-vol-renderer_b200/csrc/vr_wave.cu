@@ -97,14 +97,14 @@ template <> struct TravShared<RAY_SCATTER> {
     float ray[7][32];               // o.xyz d.xyz lim of the lane's current ray
     unsigned int pid[32];           // pool slot of the lane's ray
     int count[32];                  // overlaps found (may exceed kWaveCap = overflow)
-    int pending[32];                // queued candidates of the lane
+    int pending[32];                // candidates of the lane's ray already tested (the lane counts the queued ones)
     unsigned int t_bound[32];       // pruning bound, float bits (non-negative floats order as uints)
     uint32_t queue[kTravQueueCap];  // (owner lane << 27) | leaf-order Gaussian index
 };
 template <> struct TravShared<RAY_SHADOW> {
     float ray[7][32];
     unsigned int pid[32];
-    int pending[32];                // queued candidates + queued overlaps of the lane
+    int pending[32];                // candidates of the lane's ray fully processed (rejected, or depth added)
     long long tau[32];              // fixed-point optical depth
     uint32_t queue[kTravQueueCap];
     uint32_t hq_id[kTravHitQueueCap];
@@ -115,6 +115,7 @@ enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
 
 struct TravLane {
     int mode, cur, sp;
+    int pushed;   // candidates this lane queued for its current ray; w.pending[lane] counts the ones already tested
     bool has_result;
     RaySetupQ rq;
     float tmax;
@@ -152,7 +153,7 @@ __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const W
                 }
             }
         }
-        atomicSub(&w.pending[owner], 1);
+        atomicAdd(&w.pending[owner], 1);
     }
 }
 
@@ -174,7 +175,7 @@ __device__ __forceinline__ void shadow_quadric_batch(const SceneDev& S, TravShar
             ha = fmaxf(0.0f, t0); hb = fminf(w.ray[6][owner], t1);
             to_hq = hb > ha;   // stays pending until the depth batch has added it
         }
-        if (!to_hq) atomicSub(&w.pending[owner], 1);
+        if (!to_hq) atomicAdd(&w.pending[owner], 1);
     }
     const unsigned m = __ballot_sync(0xffffffffu, to_hq);
     if (to_hq) {
@@ -199,7 +200,7 @@ __device__ __forceinline__ void shadow_depth_batch(const SceneDev& S, TravShared
         const float F0 = erff_ni(erf_arg(c, w.hq_a[h_begin + lane]));
         const float tau = __fmul_rn(c.K, __fsub_rn(F1, F0));
         atomicAdd((unsigned long long*)&w.tau[owner], (unsigned long long)__double2ll_rn((double)tau * kTauFixed));
-        atomicSub(&w.pending[owner], 1);
+        atomicAdd(&w.pending[owner], 1);
     }
 }
 
@@ -227,7 +228,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
             l0 = h0 && c0 < 0 && ((~c0) & 7);   // leaf child with a Gaussian in it
             l1 = h1 && c1 < 0 && ((~c1) & 7);
             const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
-            w.pending[lane] += (int)l0 + (int)l1;
+            tl.pushed += (int)l0 + (int)l1;
             if (i0 && i1) {
                 const bool swap = tn1 < tn0;
                 stack[tl.sp++] = swap ? c0 : c1;
@@ -243,7 +244,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
         const unsigned m1 = __ballot_sync(0xffffffffu, l1);
         if (l1) w.queue[nQ + __popc(m1 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | ((uint32_t)(~c1) >> 3);
         nQ += __popc(m1);
-        if (fin && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
+        if (fin && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
         if (nQ >= 32) break;
         if (__ballot_sync(0xffffffffu, fin)) {
             if (can_fetch && __popc(__ballot_sync(0xffffffffu, tl.mode == T_FETCH)) >= kFetchThreshold) break;
@@ -269,7 +270,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
     }
     int stack[kStackDepth];
     TravLane tl;
-    tl.mode = T_FETCH; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f;
+    tl.mode = T_FETCH; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f; tl.pushed = 0;
     int nQ = 0, nH = 0;
     unsigned int n_escaped = 0;
     bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
                 nH -= nb;
                 shadow_depth_batch(S, wh, lane, nH, nb);
                 __syncwarp();
-                if (tl.mode == T_WAIT && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
+                if (tl.mode == T_WAIT && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
                 continue;
             }
         }
@@ -292,7 +293,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
             if (KIND == RAY_SCATTER) scatter_quadric_batch(S, Q, reinterpret_cast<TravShared<RAY_SCATTER>&>(w), lane, nQ, nb);
             else shadow_quadric_batch(S, reinterpret_cast<TravShared<RAY_SHADOW>&>(w), lane, nQ, nb, nH);
             __syncwarp();
-            if (tl.mode == T_WAIT && w.pending[lane] == 0) { tl.mode = T_FETCH; tl.has_result = true; }
+            if (tl.mode == T_WAIT && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
             continue;
         }
         const unsigned mF = __ballot_sync(0xffffffffu, tl.mode == T_FETCH);
@@ -337,7 +338,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
                         w.ray[0][lane] = ro.x; w.ray[1][lane] = ro.y; w.ray[2][lane] = ro.z;
                         w.ray[3][lane] = rd.x; w.ray[4][lane] = rd.y; w.ray[5][lane] = rd.z;
                         w.ray[6][lane] = ro.w;
-                        w.pid[lane] = np; w.pending[lane] = 0;
+                        w.pid[lane] = np; w.pending[lane] = 0; tl.pushed = 0;
                         if (KIND == RAY_SCATTER) {
                             TravShared<RAY_SCATTER>& ws = reinterpret_cast<TravShared<RAY_SCATTER>&>(w);
                             ws.count[lane] = 0; ws.t_bound[lane] = 0x7f800000u;
