@@ -90,7 +90,25 @@ __device__ __forceinline__ int post_class(int K) { return K <= 1 ? 0 : K == 2 ? 
 // ------------------------------------------------------------------------------------------
 constexpr int kTravQueueCap = 32 + 64;    // < 32 left over + two leaf children per lane and round
 constexpr int kTravHitQueueCap = 64;      // shadow overlaps: < 32 left over + one quadric batch
-constexpr unsigned kFetchThreshold = 8;   // fetch new rays when this many lanes are free
+#ifndef VR_FETCH_S
+#define VR_FETCH_S 16
+#endif
+#ifndef VR_FETCH_H
+#define VR_FETCH_H 6
+#endif
+#ifdef VR_TRAV_MINBLOCKS
+#define VR_TRAV_BOUNDS __launch_bounds__(kBlockThreads, VR_TRAV_MINBLOCKS)
+#else
+#define VR_TRAV_BOUNDS __launch_bounds__(kBlockThreads)
+#endif
+#ifdef VR_POSTA_MINBLOCKS
+#define VR_POSTA_BOUNDS __launch_bounds__(128, VR_POSTA_MINBLOCKS)
+#else
+#define VR_POSTA_BOUNDS __launch_bounds__(128)
+#endif
+// fetch new rays when this many lanes are free: the free-flight kernel's flush step is long (escapes are finished
+// there), so it waits for more lanes than the shadow kernel (sweep in profiles/r01_tuning.md)
+template <int KIND> struct FetchThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_FETCH_S : VR_FETCH_H; };
 
 template <int KIND> struct TravShared;
 template <> struct TravShared<RAY_SCATTER> {
@@ -247,7 +265,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
         if (fin && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
         if (nQ >= 32) break;
         if (__ballot_sync(0xffffffffu, fin)) {
-            if (can_fetch && __popc(__ballot_sync(0xffffffffu, tl.mode == T_FETCH)) >= kFetchThreshold) break;
+            if (can_fetch && __popc(__ballot_sync(0xffffffffu, tl.mode == T_FETCH)) >= FetchThreshold<KIND>::value) break;
             if (__ballot_sync(0xffffffffu, tl.mode == T_TRAV) == 0) break;
         }
     }
@@ -255,7 +273,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
+__global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     __shared__ TravShared<KIND> wsh[kBlockThreads / 32];
     TravShared<KIND>& w = wsh[threadIdx.x >> 5];
     const SceneDev& S = A.scene;
@@ -297,7 +315,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_trav_kernel(const __grid_c
             continue;
         }
         const unsigned mF = __ballot_sync(0xffffffffu, tl.mode == T_FETCH);
-        if (mF && (__popc(mF) >= kFetchThreshold || mT == 0)) {
+        if (mF && (__popc(mF) >= FetchThreshold<KIND>::value || mT == 0)) {
             // ---- flush finished rays: result to the slot, slot to the list of its post kernel
             const bool flush = tl.mode == T_FETCH && tl.has_result;
             const unsigned int p = w.pid[lane];
@@ -431,57 +449,92 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
     }
 }
 
-// wave_post_a: integrator.h:593-678.  Slots arrive binned by overlap count (post_class); every class
-// starts at a multiple of 32 in the flattened index space, so a warp only ever holds slots of one class.
-// Class 0 (one overlap, the commonest case in sparse mixtures) has a register-only fast path that
-// performs the same operations in the same order as the general walk does for K = 1.
-__global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
+// wave_post_a: integrator.h:593-678.  Slots arrive binned by overlap count (post_class).
+//   wave_post_a_kernel<true>   class 0 only (one overlap, the commonest case in sparse mixtures): a register-only
+//       path that performs the same operations in the same order as the general walk does for K = 1.  Small code,
+//       so the warps of the launch share the instruction caches (profiles/r01_v5: the one-kernel version spent 40 %
+//       of its stall samples waiting for instructions).  A slot whose analytic inverse declines is handed to
+//       class 1 untouched.
+//   wave_post_a_kernel<false>  classes 1..4 (+ hand-overs): every class starts at a multiple of 32 in the flattened
+//       index space, so a warp only ever holds slots of one class.
+// environment / next-event part shared by both (integrator.h:652-678)
+__device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool& Q, unsigned int p, float4 s0, uint4 s1, f3 o, f3 d,
+                                             float target_tau, float t, float albedo, Pcg& rng, WaveCounters& cn) {
     const SceneDev& S = A.scene;
+    if (t < 0.0f) {
+        s0.x = __fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0]));
+        s0.y = __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1]));
+        s0.z = __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2]));
+        A.sampleL[s1.z] = make_float4(s0.x, s0.y, s0.z, (float)s1.w);
+        return DEST_REGEN;
+    }
+    const f3 pos = add3(o, scale3(t, d));
+    const bool is_env = rng.uniform() < __fdiv_rn(1.0f, (float)(S.nl + 1));
+    ++cn.shadow;
+    f3 wi; float dist; int light;
+    uint64_t stt;
+    if (!is_env) {
+        int li = (int)__fmul_rn(rng.uniform(), (float)S.nl);
+        li = min(li, S.nl - 1);
+        const f3 lp = mk3(__ldg(S.lpos + 3 * li), __ldg(S.lpos + 3 * li + 1), __ldg(S.lpos + 3 * li + 2));
+        const f3 to = sub3(lp, pos);
+        wi = normalized3(normalized3(to));
+        dist = __fsqrt_rn(sqnorm3(to));
+        light = li;
+        stt = rng.state;
+    } else {
+        stt = rng.state;
+        wi = sample_direction_ni(&stt);
+        dist = CUDART_INF_F;
+        light = -1;
+    }
+    Q.ray_o[p] = make_float4(pos.x, pos.y, pos.z, dist);
+    Q.ray_d[p] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW));
+    Q.ps1[p] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
+    Q.ps2[p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
+    return DEST_TRAV;
+}
+
+template <bool FAST>
+__global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
+    const SceneDev& S = A.scene;
+    constexpr int kFirst = FAST ? 0 : 1, kLast = FAST ? 1 : kPostClasses;   // classes [kFirst, kLast)
     unsigned int nA[kPostClasses], base[kPostClasses + 1];
-    base[0] = 0;
+    base[kFirst] = 0;
 #pragma unroll
-    for (int c = 0; c < kPostClasses; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
-    const unsigned int total = base[kPostClasses];
-    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
+    for (int c = kFirst; c < kLast; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
+    const unsigned int total = base[kLast];
+    if (!FAST && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (total + stride - 1) / stride;
     for (unsigned int r = 0; r < rounds; ++r) {
         const unsigned int i = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
         int dest = DEST_NONE;
+        bool hand_over = false;
         unsigned int p = 0;
-        int cls = 0;
+        int cls = kFirst;
 #pragma unroll
-        for (int c = 1; c < kPostClasses; ++c) cls += (i >= base[c]) ? 1 : 0;
-        unsigned int j = i, nc = nA[0];
+        for (int c = kFirst + 1; c < kLast; ++c) cls += (i >= base[c]) ? 1 : 0;
+        unsigned int j = i, nc = nA[kFirst];
 #pragma unroll
-        for (int c = 1; c < kPostClasses; ++c) if (cls == c) { j = i - base[c]; nc = nA[c]; }
+        for (int c = kFirst + 1; c < kLast; ++c) if (cls == c) { j = i - base[c]; nc = nA[c]; }
         if (i < total && j < nc) {
             p = Q.listA[(size_t)cls * Q.P + j];
             const int K = Q.hit_count[p];
-            float4 s0 = Q.ps0[p];
-            uint4 s1 = Q.ps1[p];
+            const float4 s0 = Q.ps0[p];
+            const uint4 s1 = Q.ps1[p];
             const float4 ro = Q.ray_o[p], rd = Q.ray_d[p];
             const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
             const float target_tau = ro.w;
-            dest = DEST_REGEN;
-            if (K > kWaveCap) {  // more overlaps than a slot holds: the whole sample is re-traced by the arena kernel
-                A.overflow_list[atomicAdd(A.overflow_count, 1u)] = s1.z;
-                ++cn.over;
-            } else if (K == 0) {  // nothing on the ray: environment, path ends, target draw not committed
-                s0.x = __fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0]));
-                s0.y = __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1]));
-                s0.z = __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2]));
-                A.sampleL[s1.z] = make_float4(s0.x, s0.y, s0.z, (float)s1.w);
-            } else {
-                cn.hits += (unsigned int)K;
-                Pcg rng; rng.state = (uint64_t)s1.x | ((uint64_t)s1.y << 32); rng.inc = 3;
-                rng.next_u32();  // commit the target draw
+            Pcg rng; rng.state = (uint64_t)s1.x | ((uint64_t)s1.y << 32); rng.inc = 3;
+            rng.next_u32();  // commit the target draw (every listed slot overlapped something)
+            if (FAST) {
+                // ---- one overlap: enter event (empty segment), exit event with the single active component,
+                //      analytic inverse when the target falls inside (integrator.h:422-498, distance_solvers.h:163-171)
                 float t = -1.0f, albedo = 0.0f;
                 bool solved = false;
                 if (K == 1 && A.solver <= 1) {
-                    // ---- one overlap: enter event (empty segment), exit event with the single active component,
-                    //      analytic inverse when the target falls inside (integrator.h:422-498, distance_solvers.h:163-171)
                     const uint32_t gi = Q.hit_gi[p];
                     const float t0 = Q.hit_t0[p], t1 = Q.hit_t1[p];
                     const GaussRec g = load_gauss(S.gauss, gi);
@@ -512,68 +565,48 @@ __global__ void __launch_bounds__(128) wave_post_a_kernel(const __grid_constant_
                         }
                     }
                 }
-                if (!solved) {
-                    LocalStore<kWaveCap> st;
-#pragma unroll 1
-                    for (int s = 0; s < K; ++s) {  // exact depth constants (gaussian.h:208-231) of the gathered overlaps
-                        const size_t at = (size_t)s * Q.P + p;
-                        const uint32_t gi = Q.hit_gi[at];
-                        const GaussRec g = load_gauss(S.gauss, gi);
-                        const DepthConst c = depth_const(g, ray_quad(g, o, d));
-                        st.F(F_T0, s) = Q.hit_t0[at]; st.F(F_T1, s) = Q.hit_t1[at];
-                        st.F(F_A, s) = c.A; st.F(F_B, s) = c.B; st.F(F_K, s) = c.K; st.F(F_DEN, s) = c.den;
-                        st.U(U_GI, s) = gi;
-                    }
-                    int na = 0;
-                    t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na);
-                    if (A.record_bits) {  // integrator.h:616-644
-                        int x, y, si;
-                        lane_xy(A, s1.z, &x, &y, &si);
-                        uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
-                        const float tlim = __fadd_rn(t, 1e-6f);
-                        for (int s = 0; s < K; ++s)
-                            if (t < 0.0f || st.F(F_T0, s) <= tlim) {
-                                const uint32_t orig = __ldg(S.orig + st.U(U_GI, s));
-                                const uint32_t bit = 1u << (orig & 31u);
-                                if (!(row[orig >> 5] & bit)) atomicOr(row + (orig >> 5), bit);
-                            }
-                    }
-                    if (t >= 0.0f) albedo = evaluate_albedo(S, st, na, add3(o, scale3(t, d)));
-                }
-                if (t < 0.0f) {
-                    s0.x = __fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0]));
-                    s0.y = __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1]));
-                    s0.z = __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2]));
-                    A.sampleL[s1.z] = make_float4(s0.x, s0.y, s0.z, (float)s1.w);
+                if (solved) {
+                    cn.hits += 1u;
+                    dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
                 } else {
-                    const f3 pos = add3(o, scale3(t, d));
-                    const bool is_env = rng.uniform() < __fdiv_rn(1.0f, (float)(S.nl + 1));
-                    ++cn.shadow;
-                    f3 wi; float dist; int light;
-                    uint64_t stt;
-                    if (!is_env) {
-                        int li = (int)__fmul_rn(rng.uniform(), (float)S.nl);
-                        li = min(li, S.nl - 1);
-                        const f3 lp = mk3(__ldg(S.lpos + 3 * li), __ldg(S.lpos + 3 * li + 1), __ldg(S.lpos + 3 * li + 2));
-                        const f3 to = sub3(lp, pos);
-                        wi = normalized3(normalized3(to));
-                        dist = __fsqrt_rn(sqnorm3(to));
-                        light = li;
-                        stt = rng.state;
-                    } else {
-                        stt = rng.state;
-                        wi = sample_direction_ni(&stt);
-                        dist = CUDART_INF_F;
-                        light = -1;
-                    }
-                    Q.ray_o[p] = make_float4(pos.x, pos.y, pos.z, dist);
-                    Q.ray_d[p] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW));
-                    Q.ps1[p] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
-                    Q.ps2[p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
-                    dest = DEST_TRAV;
+                    hand_over = true;   // untouched: the general kernel redoes it
                 }
+            } else if (K > kWaveCap) {  // more overlaps than a slot holds: the whole sample is re-traced by the arena kernel
+                A.overflow_list[atomicAdd(A.overflow_count, 1u)] = s1.z;
+                ++cn.over;
+                dest = DEST_REGEN;
+            } else {
+                cn.hits += (unsigned int)K;
+                LocalStore<kWaveCap> st;
+#pragma unroll 1
+                for (int s = 0; s < K; ++s) {  // exact depth constants (gaussian.h:208-231) of the gathered overlaps
+                    const size_t at = (size_t)s * Q.P + p;
+                    const uint32_t gi = Q.hit_gi[at];
+                    const GaussRec g = load_gauss(S.gauss, gi);
+                    const DepthConst c = depth_const(g, ray_quad(g, o, d));
+                    st.F(F_T0, s) = Q.hit_t0[at]; st.F(F_T1, s) = Q.hit_t1[at];
+                    st.F(F_A, s) = c.A; st.F(F_B, s) = c.B; st.F(F_K, s) = c.K; st.F(F_DEN, s) = c.den;
+                    st.U(U_GI, s) = gi;
+                }
+                int na = 0;
+                const float t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na);
+                if (A.record_bits) {  // integrator.h:616-644
+                    int x, y, si;
+                    lane_xy(A, s1.z, &x, &y, &si);
+                    uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
+                    const float tlim = __fadd_rn(t, 1e-6f);
+                    for (int s = 0; s < K; ++s)
+                        if (t < 0.0f || st.F(F_T0, s) <= tlim) {
+                            const uint32_t orig = __ldg(S.orig + st.U(U_GI, s));
+                            const uint32_t bit = 1u << (orig & 31u);
+                            if (!(row[orig >> 5] & bit)) atomicOr(row + (orig >> 5), bit);
+                        }
+                }
+                const float albedo = t >= 0.0f ? evaluate_albedo(S, st, na, add3(o, scale3(t, d))) : 0.0f;
+                dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
             }
         }
+        if (FAST) wave_append(Q.listA + (size_t)1 * Q.P, &Q.cnt[WC_NA + 1], hand_over, p);
         wave_append(Q.listTh, &Q.cnt[WC_NTH], dest == DEST_TRAV, p);
         wave_append(Q.listC, &Q.cnt[WC_NC], dest == DEST_REGEN, p);
     }
@@ -690,6 +723,7 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
     const bool prof = prof_env && prof_env[0] == '1';
     cudaEvent_t pe[6];
     double pt[5] = {0, 0, 0, 0, 0};
+    unsigned long long cls_total[kPostClasses] = {0, 0, 0, 0, 0};
     if (prof) for (auto& e : pe) cudaEventCreate(&e);
     while (true) {
         for (int b = 0; b < kBatch; ++b) {
@@ -699,8 +733,15 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
             if (prof) cudaEventRecord(pe[1], s);
             wave_trav_kernel<RAY_SCATTER><<<grid_s, kBlockThreads, 0, s>>>(a, q);
             if (prof) cudaEventRecord(pe[2], s);
-            wave_post_a_kernel<<<grid_post, 128, 0, s>>>(a, q);
-            if (prof) cudaEventRecord(pe[3], s);
+            wave_post_a_kernel<true><<<grid_post, 128, 0, s>>>(a, q);
+            wave_post_a_kernel<false><<<grid_post, 128, 0, s>>>(a, q);
+            if (prof) {
+                cudaEventRecord(pe[3], s);
+                unsigned int hc[kWaveCounters];
+                cudaMemcpyAsync(hc, q.cnt, sizeof(hc), cudaMemcpyDeviceToHost, s);
+                cudaStreamSynchronize(s);
+                for (int c = 0; c < kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
+            }
             wave_trav_kernel<RAY_SHADOW><<<grid_h, kBlockThreads, 0, s>>>(a, q);
             if (prof) cudaEventRecord(pe[4], s);
             wave_post_b_kernel<<<grid_post256, 256, 0, s>>>(a, q);
@@ -709,7 +750,7 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
                 cudaEventSynchronize(pe[5]);
                 for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); pt[k] += ms; }
             }
-            *launches += 5;
+            *launches += 6;
             ++iters;
         }
         if (cudaMemcpyAsync(h_cnt, q.cnt, sizeof(unsigned int) * kWaveCounters, cudaMemcpyDeviceToHost, s) != cudaSuccess ||
@@ -726,6 +767,8 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
     if (prof) {
         fprintf(stderr, "[wave] samples %u iters %d  regen %.3f  trav_scatter %.3f  post_a %.3f  trav_shadow %.3f  post_b %.3f ms\n",
                 a.work_count, iters, pt[0], pt[1], pt[2], pt[3], pt[4]);
+        fprintf(stderr, "[wave] post-A slots by overlap count: K=1 %llu  K=2 %llu  K=3..4 %llu  K=5..8 %llu  K>8 %llu\n", cls_total[0], cls_total[1],
+                cls_total[2], cls_total[3], cls_total[4]);
         for (auto& e : pe) cudaEventDestroy(e);
     }
     return iters;

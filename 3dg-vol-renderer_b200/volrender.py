@@ -13,7 +13,8 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvolrender_b200.so")
+# VR_LIB selects a tuning variant built by csrc/Makefile (VARIANT=...); tests and the bench use the default
+LIB_PATH = os.environ.get("VR_LIB") or os.path.join(HERE, "libvolrender_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
 INTEGRATOR_SS, INTEGRATOR_MS, INTEGRATOR_MARCH_SPHERES = 0, 1, 2
