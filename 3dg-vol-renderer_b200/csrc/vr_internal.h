@@ -43,13 +43,13 @@ enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_
 static_assert(WC_NA + kPostClasses <= kWaveCounters, "wave counters overflow");
 struct WavePool {
     int P;
-    float4* ray_o;        // o.xyz, lim (scatter: sampled optical depth, shadow: tmax)
-    float4* ray_d;        // d.xyz, kind bits
-    float4* ps0;          // L0 L1 L2 thr
-    uint4* ps1;           // rng state lo/hi, work (pass-local sample id), bounce
+    // fields that are read together share a 32-byte sector: slots are visited in arbitrary order, so every
+    // separately stored field costs a sector of its own
+    float4* ray;          // [2p]: o.xyz, lim (scatter: sampled optical depth, shadow: tmax); [2p+1]: d.xyz, kind bits
+    float4* ps01;         // [2p]: L0 L1 L2 thr; [2p+1] (as uint4): rng state lo/hi, work (pass-local sample id), bounce
     float4* ps2;          // target_tau, albedo, nee_dist, nee_light bits
-    int* hit_count;
-    float* hit_t0;        // [kWaveCap][P]
+    uint4* hit01;         // [2p]: overlap count, (t0, t1, index) of overlap 0; [2p+1]: (t0, t1, index) of overlap 1, pad
+    float* hit_t0;        // overlaps 2..kWaveCap-1: [k - 2][P]
     float* hit_t1;
     uint32_t* hit_gi;
     long long* tau_fixed; // shadow rays: sum of clipped optical depths in 2^-40 units

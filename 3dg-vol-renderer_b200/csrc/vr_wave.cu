@@ -32,7 +32,7 @@ namespace vr {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t wave_pool_bytes(int P) {
     const size_t p = (size_t)P;
-    return align256(p * 16) * 5 + align256(p * 4) + align256(p * 4 * kWaveCap) * 3 + align256(p * 8) + align256(p * 4) * 4 + align256(p * 4 * kPostClasses) +
+    return align256(p * 32) * 3 + align256(p * 16) + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 8) + align256(p * 4) * 4 + align256(p * 4 * kPostClasses) +
            align256(kWaveCounters * 4);
 }
 void wave_pool_carve(WavePool* q, int P, void* base) {
@@ -40,11 +40,10 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     const size_t p = (size_t)P;
     auto take = [&](size_t bytes) { char* r = b; b += align256(bytes); return (void*)r; };
     q->P = P;
-    q->ray_o = (float4*)take(p * 16); q->ray_d = (float4*)take(p * 16);
-    q->ps0 = (float4*)take(p * 16); q->ps1 = (uint4*)take(p * 16); q->ps2 = (float4*)take(p * 16);
-    q->hit_count = (int*)take(p * 4);
-    q->hit_t0 = (float*)take(p * 4 * kWaveCap); q->hit_t1 = (float*)take(p * 4 * kWaveCap);
-    q->hit_gi = (uint32_t*)take(p * 4 * kWaveCap);
+    q->ray = (float4*)take(p * 32); q->ps01 = (float4*)take(p * 32); q->ps2 = (float4*)take(p * 16);
+    q->hit01 = (uint4*)take(p * 32);
+    q->hit_t0 = (float*)take(p * 4 * (kWaveCap - 2)); q->hit_t1 = (float*)take(p * 4 * (kWaveCap - 2));
+    q->hit_gi = (uint32_t*)take(p * 4 * (kWaveCap - 2));
     q->tau_fixed = (long long*)take(p * 8);
     q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4);
     q->listA = (unsigned int*)take(p * 4 * kPostClasses); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
@@ -80,6 +79,27 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
     }
 }
 enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2 };
+// overlap records of a slot: the count and the first two records share one 32-byte sector (85 % of the free-flight
+// rays of a sparse mixture gather at most two components), the rest live in [k - 2][P] arrays
+__device__ __forceinline__ void pool_store_hit(const WavePool& Q, unsigned int p, int k, float t0, float t1, uint32_t gi) {
+    if (k < 2) {
+        uint32_t* r = reinterpret_cast<uint32_t*>(Q.hit01 + 2 * (size_t)p) + 1 + 3 * k;
+        r[0] = __float_as_uint(t0); r[1] = __float_as_uint(t1); r[2] = gi;
+    } else {
+        const size_t at = (size_t)(k - 2) * Q.P + p;
+        Q.hit_t0[at] = t0; Q.hit_t1[at] = t1; Q.hit_gi[at] = gi;
+    }
+}
+__device__ __forceinline__ void pool_load_hit(const WavePool& Q, unsigned int p, int k, const uint4& h0, float* t0, float* t1, uint32_t* gi) {
+    if (k == 0) { *t0 = __uint_as_float(h0.y); *t1 = __uint_as_float(h0.z); *gi = h0.w; }
+    else if (k == 1) {
+        const uint4 h1 = Q.hit01[2 * (size_t)p + 1];
+        *t0 = __uint_as_float(h1.x); *t1 = __uint_as_float(h1.y); *gi = h1.z;
+    } else {
+        const size_t at = (size_t)(k - 2) * Q.P + p;
+        *t0 = Q.hit_t0[at]; *t1 = Q.hit_t1[at]; *gi = Q.hit_gi[at];
+    }
+}
 __device__ __forceinline__ int post_class(int K) { return K <= 1 ? 0 : K == 2 ? 1 : K <= 4 ? 2 : K <= 8 ? 3 : 4; }
 
 
@@ -156,8 +176,7 @@ __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const W
             if (!(t0 > tb)) {
                 const int slot = atomicAdd(&w.count[owner], 1);
                 if (slot < kWaveCap) {
-                    const size_t at = (size_t)slot * Q.P + w.pid[owner];
-                    Q.hit_t0[at] = t0; Q.hit_t1[at] = t1; Q.hit_gi[at] = gi;
+                    pool_store_hit(Q, w.pid[owner], slot, t0, t1, gi);
                     if (t1 < tb) {
                         // pruning only: CONSERVATIVE estimate of this component's full optical depth
                         // (fast intrinsics; 1.5x margin covers the FP32 slack of the exact expression)
@@ -326,12 +345,12 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                 // slot back to the regeneration list (integrator.h:594-597; the target draw is not committed)
                 const bool esc = flush && K == 0;
                 if (esc) {
-                    const float4 s0 = Q.ps0[p];
-                    const uint4 s1 = Q.ps1[p];
+                    const float4 s0 = Q.ps01[2 * (size_t)p];
+                    const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
                     A.sampleL[s1.z] = make_float4(__fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0])), __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1])),
                                                   __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2])), (float)s1.w);
                 }
-                if (flush && K > 0) Q.hit_count[p] = K;
+                if (flush && K > 0) reinterpret_cast<int*>(Q.hit01 + 2 * (size_t)p)[0] = K;
                 wave_append(Q.listC, &Q.cnt[WC_NC], esc, p);
                 const int cls = post_class(K);
 #pragma unroll
@@ -352,7 +371,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                     const unsigned int idx = base + (unsigned int)__popc(mF & ((1u << lane) - 1u));
                     if (idx < nT) {
                         const unsigned int np = __ldg(list + idx);
-                        const float4 ro = Q.ray_o[np], rd = Q.ray_d[np];
+                        const float4 ro = Q.ray[2 * (size_t)np], rd = Q.ray[2 * (size_t)np + 1];
                         w.ray[0][lane] = ro.x; w.ray[1][lane] = ro.y; w.ray[2][lane] = ro.z;
                         w.ray[3][lane] = rd.x; w.ray[4][lane] = rd.y; w.ray[5][lane] = rd.z;
                         w.ray[6][lane] = ro.w;
@@ -395,8 +414,8 @@ __device__ __forceinline__ void publish_scatter_ray(const WavePool& Q, unsigned 
     Pcg peek; peek.state = rng_state; peek.inc = 3;
     const float t = -logf(__fsub_rn(1.0f, peek.uniform()));
     *target = t;
-    Q.ray_o[p] = make_float4(o.x, o.y, o.z, t);
-    Q.ray_d[p] = make_float4(d.x, d.y, d.z, __int_as_float(RAY_SCATTER));
+    Q.ray[2 * (size_t)p] = make_float4(o.x, o.y, o.z, t);
+    Q.ray[2 * (size_t)p + 1] = make_float4(d.x, d.y, d.z, __int_as_float(RAY_SCATTER));
 }
 
 // wave_regen: integrator.h:557-570
@@ -430,8 +449,8 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
             const RayOD ray = camera_ray(A.cam, u, v);
             float target;
             publish_scatter_ray(Q, p, ray.o, ray.d, rng.state, &target);
-            Q.ps0[p] = make_float4(0.f, 0.f, 0.f, 1.0f);
-            Q.ps1[p] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), idx, 0u);
+            Q.ps01[2 * (size_t)p] = make_float4(0.f, 0.f, 0.f, 1.0f);
+            reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), idx, 0u);
             Q.ps2[p] = make_float4(target, 0.f, 0.f, 0.f);
             ++cn.scatter;
             to_trav = true;
@@ -488,9 +507,9 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
         dist = CUDART_INF_F;
         light = -1;
     }
-    Q.ray_o[p] = make_float4(pos.x, pos.y, pos.z, dist);
-    Q.ray_d[p] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW));
-    Q.ps1[p] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
+    Q.ray[2 * (size_t)p] = make_float4(pos.x, pos.y, pos.z, dist);
+    Q.ray[2 * (size_t)p + 1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW));
+    reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
     Q.ps2[p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
     return DEST_TRAV;
 }
@@ -521,10 +540,11 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
         for (int c = kFirst + 1; c < kLast; ++c) if (cls == c) { j = i - base[c]; nc = nA[c]; }
         if (i < total && j < nc) {
             p = Q.listA[(size_t)cls * Q.P + j];
-            const int K = Q.hit_count[p];
-            const float4 s0 = Q.ps0[p];
-            const uint4 s1 = Q.ps1[p];
-            const float4 ro = Q.ray_o[p], rd = Q.ray_d[p];
+            const uint4 h0 = Q.hit01[2 * (size_t)p];   // overlap count + first overlap
+            const int K = (int)h0.x;
+            const float4 s0 = Q.ps01[2 * (size_t)p];
+            const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
+            const float4 ro = Q.ray[2 * (size_t)p], rd = Q.ray[2 * (size_t)p + 1];
             const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
             const float target_tau = ro.w;
             Pcg rng; rng.state = (uint64_t)s1.x | ((uint64_t)s1.y << 32); rng.inc = 3;
@@ -535,8 +555,8 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 float t = -1.0f, albedo = 0.0f;
                 bool solved = false;
                 if (K == 1 && A.solver <= 1) {
-                    const uint32_t gi = Q.hit_gi[p];
-                    const float t0 = Q.hit_t0[p], t1 = Q.hit_t1[p];
+                    const uint32_t gi = h0.w;
+                    const float t0 = __uint_as_float(h0.y), t1 = __uint_as_float(h0.z);
                     const GaussRec g = load_gauss(S.gauss, gi);
                     const RayQuad q = ray_quad(g, o, d);
                     const DepthConst c = depth_const(g, q);
@@ -580,11 +600,11 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 LocalStore<kWaveCap> st;
 #pragma unroll 1
                 for (int s = 0; s < K; ++s) {  // exact depth constants (gaussian.h:208-231) of the gathered overlaps
-                    const size_t at = (size_t)s * Q.P + p;
-                    const uint32_t gi = Q.hit_gi[at];
+                    float ht0, ht1; uint32_t gi;
+                    pool_load_hit(Q, p, s, h0, &ht0, &ht1, &gi);
                     const GaussRec g = load_gauss(S.gauss, gi);
                     const DepthConst c = depth_const(g, ray_quad(g, o, d));
-                    st.F(F_T0, s) = Q.hit_t0[at]; st.F(F_T1, s) = Q.hit_t1[at];
+                    st.F(F_T0, s) = ht0; st.F(F_T1, s) = ht1;
                     st.F(F_A, s) = c.A; st.F(F_B, s) = c.B; st.F(F_K, s) = c.K; st.F(F_DEN, s) = c.den;
                     st.U(U_GI, s) = gi;
                 }
@@ -629,8 +649,8 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
         unsigned int p = 0;
         if (i < nB) {
             p = Q.listB[i];
-            float4 s0 = Q.ps0[p];
-            uint4 s1 = Q.ps1[p];
+            float4 s0 = Q.ps01[2 * (size_t)p];
+            uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
             const float4 s2 = Q.ps2[p];
             const float albedo = s2.y, nee_dist = s2.z;
             const int light = __float_as_int(s2.w);
@@ -674,11 +694,11 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
                     A.sampleL[s1.z] = make_float4(s0.x, s0.y, s0.z, (float)s1.w);
                 } else {
                     const f3 nd = sample_direction_ni(&stt);
-                    const float4 ro = Q.ray_o[p];  // the scatter position is the shadow ray's origin
+                    const float4 ro = Q.ray[2 * (size_t)p];  // the scatter position is the shadow ray's origin
                     float target;
                     publish_scatter_ray(Q, p, mk3(ro.x, ro.y, ro.z), nd, stt, &target);
-                    Q.ps0[p] = s0;
-                    Q.ps1[p] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w + 1u);
+                    Q.ps01[2 * (size_t)p] = s0;
+                    reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w + 1u);
                     ++cn.scatter;
                     dest = DEST_TRAV;
                 }
