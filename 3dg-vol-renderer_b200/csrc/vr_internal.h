@@ -47,12 +47,11 @@ struct WavePool {
     // separately stored field costs a sector of its own
     float4* ray;          // [2p]: o.xyz, lim (scatter: sampled optical depth, shadow: tmax); [2p+1]: d.xyz, kind bits
     float4* ps01;         // [2p]: L0 L1 L2 thr; [2p+1] (as uint4): rng state lo/hi, work (pass-local sample id), bounce
-    float4* ps2;          // target_tau, albedo, nee_dist, nee_light bits
+    float4* ps2;          // [2p]: target_tau, albedo, nee_dist, nee_light bits; [2p+1]: shadow ray's optical depth sum (int64, 2^-40 units)
     uint4* hit01;         // [2p]: overlap count, (t0, t1, index) of overlap 0; [2p+1]: (t0, t1, index) of overlap 1, pad
     float* hit_t0;        // overlaps 2..kWaveCap-1: [k - 2][P]
     float* hit_t1;
     uint32_t* hit_gi;
-    long long* tau_fixed; // shadow rays: sum of clipped optical depths in 2^-40 units
     unsigned int* listTs;  // slots whose free-flight ray waits for traversal
     unsigned int* listTh;  // slots whose shadow ray waits for traversal
     unsigned int* listA;   // [kPostClasses][P]

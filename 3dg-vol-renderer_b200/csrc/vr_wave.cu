@@ -32,7 +32,7 @@ namespace vr {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t wave_pool_bytes(int P) {
     const size_t p = (size_t)P;
-    return align256(p * 32) * 3 + align256(p * 16) + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 8) + align256(p * 4) * 4 + align256(p * 4 * kPostClasses) +
+    return align256(p * 32) * 4 + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 4) * 4 + align256(p * 4 * kPostClasses) +
            align256(kWaveCounters * 4);
 }
 void wave_pool_carve(WavePool* q, int P, void* base) {
@@ -40,11 +40,10 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     const size_t p = (size_t)P;
     auto take = [&](size_t bytes) { char* r = b; b += align256(bytes); return (void*)r; };
     q->P = P;
-    q->ray = (float4*)take(p * 32); q->ps01 = (float4*)take(p * 32); q->ps2 = (float4*)take(p * 16);
+    q->ray = (float4*)take(p * 32); q->ps01 = (float4*)take(p * 32); q->ps2 = (float4*)take(p * 32);
     q->hit01 = (uint4*)take(p * 32);
     q->hit_t0 = (float*)take(p * 4 * (kWaveCap - 2)); q->hit_t1 = (float*)take(p * 4 * (kWaveCap - 2));
     q->hit_gi = (uint32_t*)take(p * 4 * (kWaveCap - 2));
-    q->tau_fixed = (long long*)take(p * 8);
     q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4);
     q->listA = (unsigned int*)take(p * 4 * kPostClasses); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
     q->cnt = (unsigned int*)take(kWaveCounters * 4);
@@ -265,7 +264,6 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
             l0 = h0 && c0 < 0 && ((~c0) & 7);   // leaf child with a Gaussian in it
             l1 = h1 && c1 < 0 && ((~c1) & 7);
             const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
-            tl.pushed += (int)l0 + (int)l1;
             if (i0 && i1) {
                 const bool swap = tn1 < tn0;
                 stack[tl.sp++] = swap ? c0 : c1;
@@ -274,6 +272,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
             else if (i1) tl.cur = c1;
             else if (tl.sp > 0) tl.cur = stack[--tl.sp];
             else { fin = true; tl.mode = T_WAIT; }   // resolved below once the pushes are counted
+            tl.pushed += (int)l0 + (int)l1;
         }
         const unsigned m0 = __ballot_sync(0xffffffffu, l0);
         if (l0) w.queue[nQ + __popc(m0 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | ((uint32_t)(~c0) >> 3);
@@ -358,7 +357,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                     wave_append(Q.listA + (size_t)c * Q.P, &Q.cnt[WC_NA + c], flush && K > 0 && cls == c, p);
             } else {
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
-                if (flush) Q.tau_fixed[p] = wh.tau[lane];
+                if (flush) reinterpret_cast<long long*>(Q.ps2 + 2 * (size_t)p + 1)[0] = wh.tau[lane];
                 wave_append(Q.listB, &Q.cnt[WC_NB], flush, p);
             }
             tl.has_result = false;
@@ -451,7 +450,6 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
             publish_scatter_ray(Q, p, ray.o, ray.d, rng.state, &target);
             Q.ps01[2 * (size_t)p] = make_float4(0.f, 0.f, 0.f, 1.0f);
             reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), idx, 0u);
-            Q.ps2[p] = make_float4(target, 0.f, 0.f, 0.f);
             ++cn.scatter;
             to_trav = true;
         }
@@ -510,7 +508,7 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
     Q.ray[2 * (size_t)p] = make_float4(pos.x, pos.y, pos.z, dist);
     Q.ray[2 * (size_t)p + 1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW));
     reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
-    Q.ps2[p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
+    Q.ps2[2 * (size_t)p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
     return DEST_TRAV;
 }
 
@@ -651,10 +649,10 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
             p = Q.listB[i];
             float4 s0 = Q.ps01[2 * (size_t)p];
             uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
-            const float4 s2 = Q.ps2[p];
+            const float4 s2 = Q.ps2[2 * (size_t)p];
             const float albedo = s2.y, nee_dist = s2.z;
             const int light = __float_as_int(s2.w);
-            const long long tf = Q.tau_fixed[p];
+            const long long tf = reinterpret_cast<const long long*>(Q.ps2 + 2 * (size_t)p + 1)[0];
             // exp(-float(sum)), sum = double sum of the clipped depths (gmm.h:577); exactly 0 beyond the cutoff
             const float Tr = tf > tau_cutoff_fixed() ? 0.0f : expf(-(float)((double)tf / kTauFixed));
             float Li0, Li1, Li2;
