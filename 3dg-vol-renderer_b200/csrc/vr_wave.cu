@@ -109,6 +109,12 @@ __device__ __forceinline__ int post_class(int K) { return K <= 1 ? 0 : K == 2 ? 
 // ------------------------------------------------------------------------------------------
 constexpr int kTravQueueCap = 32 + 64;    // < 32 left over + two leaf children per lane and round
 constexpr int kTravHitQueueCap = 64;      // shadow overlaps: < 32 left over + one quadric batch
+#ifndef VR_WAIT_S
+#define VR_WAIT_S 33   // > 32 = never (no gain for free-flight rays)
+#endif
+#ifndef VR_WAIT_H
+#define VR_WAIT_H 4
+#endif
 #ifndef VR_FETCH_S
 #define VR_FETCH_S 16
 #endif
@@ -127,6 +133,9 @@ constexpr int kTravHitQueueCap = 64;      // shadow overlaps: < 32 left over + o
 #endif
 // fetch new rays when this many lanes are free: the free-flight kernel's flush step is long (escapes are finished
 // there), so it waits for more lanes than the shadow kernel (sweep in profiles/r01_tuning.md)
+// candidate batches normally run full (32 entries); they run early once this many lanes have finished their traversal
+// and only wait for queued candidates (those lanes cannot take a new ray before their result is complete)
+template <int KIND> struct WaitThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_WAIT_S : VR_WAIT_H; };
 template <int KIND> struct FetchThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_FETCH_S : VR_FETCH_H; };
 
 template <int KIND> struct TravShared;
@@ -285,6 +294,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
         if (__ballot_sync(0xffffffffu, fin)) {
             if (can_fetch && __popc(__ballot_sync(0xffffffffu, tl.mode == T_FETCH)) >= FetchThreshold<KIND>::value) break;
             if (__ballot_sync(0xffffffffu, tl.mode == T_TRAV) == 0) break;
+            if (WaitThreshold<KIND>::value <= 32 && __popc(__ballot_sync(0xffffffffu, tl.mode == T_WAIT)) >= WaitThreshold<KIND>::value) break;
         }
     }
     __syncwarp();
@@ -312,8 +322,9 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
     bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
     while (true) {
         const unsigned mT = __ballot_sync(0xffffffffu, tl.mode == T_TRAV);
+        const bool drain = mT == 0 || (WaitThreshold<KIND>::value <= 32 && __popc(__ballot_sync(0xffffffffu, tl.mode == T_WAIT)) >= WaitThreshold<KIND>::value);
         if (KIND == RAY_SHADOW) {
-            if (nH >= 32 || (nH > 0 && mT == 0 && nQ == 0)) {
+            if (nH >= 32 || (nH > 0 && drain && nQ == 0)) {
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
                 const int nb = min(nH, 32);
                 nH -= nb;
@@ -323,7 +334,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                 continue;
             }
         }
-        if (nQ >= 32 || (nQ > 0 && mT == 0)) {
+        if (nQ >= 32 || (nQ > 0 && drain)) {
             const int nb = min(nQ, 32);
             nQ -= nb;
             if (KIND == RAY_SCATTER) scatter_quadric_batch(S, Q, reinterpret_cast<TravShared<RAY_SCATTER>&>(w), lane, nQ, nb);
