@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "vr_bvh.h"
+#include "vr_lightgrid.h"
 #include "vr_context.h"
 
 using namespace vr;
@@ -16,6 +17,8 @@ vr::SceneDev vr_context::scene_dev() const {
     S.nodes = nodes.as<float4>();
     S.qnodes = qnodes.as<uint4>();
     for (int k = 0; k < 3; ++k) { S.qorg[k] = qorg[k]; S.qcell[k] = qcell[k]; }
+    S.lg_start = lg_start.as<uint32_t>(); S.lg_gi = lg_gi.as<uint32_t>(); S.lg_dmin = lg_dmin.as<float>();
+    S.lg_res = lg_res; S.lg_mask = lg_valid ? lg_mask : 0u;
     S.orig = perm.as<uint32_t>();
     S.n = n;
     S.nl = nl;
@@ -97,6 +100,8 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
+    if (!strcmp(name, "light_grid")) { ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
+    if (!strcmp(name, "light_grid_res")) { ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "wave_slots")) { ctx->wave_slots = std::max(0, (int)value); ctx->wavepool.release(); return VR_OK; }
     return fail(ctx, VR_ERR_INVALID_ARGUMENT, std::string("unknown option ") + name);
 }
@@ -163,6 +168,8 @@ int vr_set_lights(vr_context* ctx, int nl, const float* pos3, const float* inten
         VR_CUDA(cudaMemcpyAsync(ctx->lint.p, intensity3, (size_t)nl * 12, cudaMemcpyHostToDevice, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
     }
+    ctx->h_lpos.assign(pos3, pos3 + (size_t)3 * std::max(nl, 0));
+    ctx->lg_valid = false;
     ctx->nl = nl;
     if (env_rgb) { ctx->env[0] = env_rgb[0]; ctx->env[1] = env_rgb[1]; ctx->env[2] = env_rgb[2]; }
     return VR_OK;
@@ -189,6 +196,8 @@ namespace vr {
 int set_gmm_from_device(vr_context* ctx, int n) {
     ctx->has_gmm = false;
     ctx->rec_valid = false;
+    ctx->lg_valid = false;
+    ctx->h_box_lo.clear(); ctx->h_box_hi.clear(); ctx->h_leaf_of_orig.clear();
     const size_t m = (size_t)std::max(n, 1);
     VR_CUDA(ctx->gauss_orig.ensure(m * 48)); VR_CUDA(ctx->gauss_leaf.ensure(m * 48));
     VR_CUDA(ctx->perm.ensure(m * 4)); VR_CUDA(ctx->leaf_of_orig.ensure(m * 4));
@@ -223,10 +232,41 @@ int set_gmm_from_device(vr_context* ctx, int n) {
                                  ctx->leaf_of_orig.as<uint32_t>(), ctx->stream);
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
         VR_CUDA(cudaGetLastError());
+        ctx->h_leaf_of_orig.resize((size_t)n);
+        for (int i = 0; i < n; ++i) ctx->h_leaf_of_orig[bvh.perm[(size_t)i]] = (uint32_t)i;
+        ctx->h_box_lo.swap(lo); ctx->h_box_hi.swap(hi);
         ctx->n_nodes = (int)bvh.nodes.size();
         ctx->bvh_depth = bvh.max_depth;
     }
     ctx->has_gmm = true;
+    return VR_OK;
+}
+
+// per-light direction grids for the wavefront engine's point-light shadow rays (vr_lightgrid.h); (re)built when the
+// mixture or the lights changed since the last render
+int ensure_light_grids(vr_context* ctx) {
+    if (ctx->lg_valid) return VR_OK;
+    ctx->lg_mask = 0;
+    VR_CUDA(ctx->lg_start.ensure(16)); VR_CUDA(ctx->lg_gi.ensure(16)); VR_CUDA(ctx->lg_dmin.ensure(16));
+    if (ctx->use_light_grid && ctx->n > 0 && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl &&
+        (int)ctx->h_leaf_of_orig.size() == ctx->n) {
+        LightGridHost g;
+        build_light_grids(ctx->n, ctx->h_box_lo.data(), ctx->h_box_hi.data(), ctx->h_leaf_of_orig.data(), ctx->nl, ctx->h_lpos.data(),
+                          ctx->lg_res, &g);
+        if (g.mask) {
+            VR_CUDA(ctx->lg_start.ensure(g.cell_start.size() * 4));
+            VR_CUDA(ctx->lg_gi.ensure(std::max<size_t>(g.entry_gi.size(), 1) * 4));
+            VR_CUDA(ctx->lg_dmin.ensure(std::max<size_t>(g.entry_dmin.size(), 1) * 4));
+            VR_CUDA(cudaMemcpyAsync(ctx->lg_start.p, g.cell_start.data(), g.cell_start.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+            if (!g.entry_gi.empty()) {
+                VR_CUDA(cudaMemcpyAsync(ctx->lg_gi.p, g.entry_gi.data(), g.entry_gi.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+                VR_CUDA(cudaMemcpyAsync(ctx->lg_dmin.p, g.entry_dmin.data(), g.entry_dmin.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+            }
+            VR_CUDA(cudaStreamSynchronize(ctx->stream));
+            ctx->lg_mask = g.mask;
+        }
+    }
+    ctx->lg_valid = true;
     return VR_OK;
 }
 }  // namespace vr

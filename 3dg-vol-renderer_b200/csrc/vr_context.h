@@ -42,6 +42,14 @@ struct vr_context {
     vr::DevBuf mean3, cov6, density, albedo;       // inputs as given (original order)
     vr::DevBuf gauss_orig, gauss_leaf, nodes, qnodes, perm, leaf_of_orig, box_lo, box_hi;
     float qorg[3] = {0.f, 0.f, 0.f}, qcell[3] = {1.f, 1.f, 1.f};   // grid of the compact tree (vr_bvh.h BvhQuantGrid)
+    // host copies kept for the per-light direction grids (vr_lightgrid.h), built lazily before a render
+    std::vector<float> h_box_lo, h_box_hi, h_lpos;
+    std::vector<uint32_t> h_leaf_of_orig;
+    vr::DevBuf lg_start, lg_gi, lg_dmin;
+    bool lg_valid = false;
+    int lg_res = 256;
+    uint32_t lg_mask = 0;
+    int use_light_grid = 1;
     // ---- sphere mixture
     bool has_smm = false;
     int n_spheres = 0;
@@ -75,7 +83,8 @@ namespace vr {
 int fail(vr_context* c, int code, const std::string& msg);
 int cuda_fail(vr_context* c, cudaError_t e, const char* what);
 int render_device_impl(vr_context* c, const vr_render_params* p, vr_render_stats* st);
-int set_gmm_from_device(vr_context* c, int n);  // mean3/cov6/density/albedo device buffers already filled
+int set_gmm_from_device(vr_context* c, int n);
+int ensure_light_grids(vr_context* c);  // vr_api.cu  // mean3/cov6/density/albedo device buffers already filled
 void sfd_destroy(vr_context* c);
 }  // namespace vr
 

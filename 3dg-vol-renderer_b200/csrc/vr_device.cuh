@@ -10,6 +10,12 @@ struct SceneDev {
     const float4* nodes;    // 4 x float4 per hierarchy node (vr_bvh.h BvhNode)
     const uint4* qnodes;    // 2 x uint4 per node: the same tree with 16-bit boxes (vr_bvh.h BvhNodeQ), wavefront kernels
     float qorg[3], qcell[3];
+    // per-light direction grids (vr_lightgrid.h): cell_start[light][6*R*R+1], entries sorted by distance from the light
+    const uint32_t* lg_start;
+    const uint32_t* lg_gi;
+    const float* lg_dmin;
+    int lg_res;
+    uint32_t lg_mask;       // bit l: light l has a grid
     const uint32_t* orig;   // leaf order -> original index
     int n;
     int nl;
@@ -122,6 +128,22 @@ __device__ __forceinline__ void node_slabs_q(const uint4* __restrict__ qnodes, i
                  fminf(fmaf(q_plane(v.y, fz), rs.s.z, rs.b.z), tlimit));
     *h1 = tmin <= tmax; *tn1 = tmin;
     *c0 = (int)v.z; *c1 = (int)v.w;
+}
+
+// cell of the direction v = (ray origin - light) in the light's cube map; same formula as light_grid_cell (vr_lightgrid.h)
+__device__ __forceinline__ uint32_t light_grid_cell_dev(f3 v, int res) {
+    const float ax = fabsf(v.x), ay = fabsf(v.y), az = fabsf(v.z);
+    int m = 0; float am = ax;
+    if (ay > am) { m = 1; am = ay; }
+    if (az > am) { m = 2; am = az; }
+    const float vm = m == 0 ? v.x : (m == 1 ? v.y : v.z);
+    const float va = m == 0 ? v.y : (m == 1 ? v.z : v.x);   // axis (m + 1) % 3
+    const float vb = m == 0 ? v.z : (m == 1 ? v.x : v.y);   // axis (m + 2) % 3
+    const int face = 2 * m + (vm < 0.0f ? 1 : 0);
+    const float half = 0.5f * (float)res;
+    int iu = (int)((va / am + 1.0f) * half), iw = (int)((vb / am + 1.0f) * half);
+    iu = min(res - 1, max(0, iu)); iw = min(res - 1, max(0, iw));
+    return (uint32_t)((face * res + iw) * res + iu);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -38,7 +38,8 @@ constexpr int kWaveCap = 16;         // free-flight overlaps kept per path slot 
 // post-A work is binned by overlap count so that the warps of wave_post_a_kernel run slots of similar
 // length: class 0: K = 1, 1: K = 2, 2: K = 3..4, 3: K = 5..8, 4: K > 8 (incl. overflow)
 constexpr int kPostClasses = 5;
-enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, WC_NA /* kPostClasses counters */,
+enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, WC_NTL, WC_CURSOR_L,
+       WC_NA /* kPostClasses counters */,
        kWaveCounters = 16 };
 static_assert(WC_NA + kPostClasses <= kWaveCounters, "wave counters overflow");
 struct WavePool {
@@ -53,7 +54,8 @@ struct WavePool {
     float* hit_t1;
     uint32_t* hit_gi;
     unsigned int* listTs;  // slots whose free-flight ray waits for traversal
-    unsigned int* listTh;  // slots whose shadow ray waits for traversal
+    unsigned int* listTh;  // slots whose shadow ray waits for traversal (environment rays, lights without a grid)
+    unsigned int* listTl;  // slots whose shadow ray goes to a point light that has a direction grid
     unsigned int* listA;   // [kPostClasses][P]
     unsigned int* listB;
     unsigned int* listC;

@@ -1,0 +1,116 @@
+// vr_lightgrid.cpp -- host builder of the per-light direction grids.  See vr_lightgrid.h.
+#include "vr_lightgrid.h"
+
+#include <algorithm>
+#include <cmath>
+#include <numeric>
+
+namespace vr {
+namespace {
+
+struct Rect { int face, u0, u1, w0, w1; };
+
+// cells of face (m, negative) that the box [lo, hi] (relative to the light) projects into; false = none
+bool face_rect(const double lo[3], const double hi[3], int m, bool negative, int res, Rect* r) {
+    const int a = (m + 1) % 3, b = (m + 2) % 3;
+    // s * x_m over the box, s = -1 for the negative face
+    const double xm0 = negative ? -hi[m] : lo[m], xm1 = negative ? -lo[m] : hi[m];
+    if (!(xm1 > 0.0)) return false;
+    double ulo = -1.0, uhi = 1.0, wlo = -1.0, whi = 1.0;
+    if (xm0 > 1e-9 && xm0 > 1e-6 * xm1) {   // the box is strictly in front of the face: exact perspective bounds
+        auto ratio = [&](int c, double* mn, double* mx) {
+            *mn = std::min(lo[c] / xm0, lo[c] / xm1);
+            *mx = std::max(hi[c] / xm0, hi[c] / xm1);
+        };
+        ratio(a, &ulo, &uhi); ratio(b, &wlo, &whi);
+        if (ulo > 1.0 || uhi < -1.0 || wlo > 1.0 || whi < -1.0) return false;
+    }   // else: the box reaches the plane through the light -> whole face (conservative)
+    auto cell = [&](double c, double slack) {
+        int i = (int)std::floor((c + 1.0) * 0.5 * res + slack);
+        return std::min(res - 1, std::max(0, i));
+    };
+    r->face = 2 * m + (negative ? 1 : 0);
+    r->u0 = cell(std::max(ulo, -1.0), -1e-3); r->u1 = cell(std::min(uhi, 1.0), 1e-3);
+    r->w0 = cell(std::max(wlo, -1.0), -1e-3); r->w1 = cell(std::min(whi, 1.0), 1e-3);
+    return true;
+}
+
+}  // namespace
+
+void build_light_grids(int n, const float* lo, const float* hi, const uint32_t* leaf_of_orig, int nl, const float* lpos, int res,
+                       LightGridHost* out) {
+    out->res = res; out->mask = 0;
+    const size_t cells = (size_t)6 * res * res;
+    out->cell_start.assign((size_t)std::max(nl, 0) * (cells + 1), 0u);
+    out->entry_gi.clear(); out->entry_dmin.clear();
+    if (n <= 0 || nl <= 0 || res <= 0) return;
+    const double pad = 1e-4;     // absolute slack around every box (scene units): rounding of ray origins / directions
+    const double near_limit = 0.05;
+    std::vector<Rect> rects;     // per component, up to 6
+    std::vector<uint32_t> rect_first((size_t)n + 1);
+    std::vector<float> dmin((size_t)n);
+    std::vector<uint32_t> count(cells + 1), order;
+    for (int l = 0; l < nl; ++l) {
+        uint32_t* start = out->cell_start.data() + (size_t)l * (cells + 1);
+        const uint32_t base = (uint32_t)out->entry_gi.size();
+        for (size_t c = 0; c <= cells; ++c) start[c] = base;   // a light without a grid has empty cells
+        if (l >= 32) continue;
+        const double L[3] = {lpos[3 * l], lpos[3 * l + 1], lpos[3 * l + 2]};
+        rects.clear();
+        bool usable = true;
+        for (int g = 0; g < n && usable; ++g) {
+            double blo[3], bhi[3], d2 = 0.0;
+            for (int k = 0; k < 3; ++k) {
+                blo[k] = (double)lo[3 * g + k] - pad - L[k]; bhi[k] = (double)hi[3 * g + k] + pad - L[k];
+                const double d = std::max(std::max(blo[k], -bhi[k]), 0.0);
+                d2 += d * d;
+            }
+            rect_first[(size_t)g] = (uint32_t)rects.size();
+            if (!(blo[0] <= bhi[0] && blo[1] <= bhi[1] && blo[2] <= bhi[2])) continue;   // degenerate / NaN box: never a candidate source
+            const double dist = std::sqrt(d2);
+            if (!(dist > near_limit)) { usable = false; break; }   // the light is inside or next to this component
+            dmin[(size_t)g] = (float)(dist * (1.0 - 1e-6));
+            for (int m = 0; m < 3; ++m)
+                for (int neg = 0; neg < 2; ++neg) {
+                    Rect r;
+                    if (face_rect(blo, bhi, m, neg != 0, res, &r)) rects.push_back(r);
+                }
+        }
+        if (!usable) continue;
+        rect_first[(size_t)n] = (uint32_t)rects.size();
+        // NaN boxes: components whose box is not finite cannot be culled by a grid -> no grid for this light
+        bool finite = true;
+        for (int g = 0; g < n && finite; ++g)
+            for (int k = 0; k < 3; ++k) if (!std::isfinite(lo[3 * g + k]) || !std::isfinite(hi[3 * g + k])) finite = false;
+        if (!finite) continue;
+        std::fill(count.begin(), count.end(), 0u);
+        for (int g = 0; g < n; ++g)
+            for (uint32_t ri = rect_first[(size_t)g]; ri < rect_first[(size_t)g + 1]; ++ri) {
+                const Rect& r = rects[ri];
+                for (int w = r.w0; w <= r.w1; ++w)
+                    for (int u = r.u0; u <= r.u1; ++u) ++count[((size_t)r.face * res + w) * res + u];
+            }
+        uint32_t total = 0;
+        for (size_t c = 0; c < cells; ++c) { const uint32_t k = count[c]; start[c] = base + total; count[c] = total; total += k; }
+        start[cells] = base + total;
+        out->entry_gi.resize((size_t)base + total);
+        out->entry_dmin.resize((size_t)base + total);
+        // fill in order of increasing distance, so every cell's list comes out sorted
+        order.resize((size_t)n);
+        std::iota(order.begin(), order.end(), 0u);
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return dmin[x] < dmin[y]; });
+        for (uint32_t g : order)
+            for (uint32_t ri = rect_first[g]; ri < rect_first[(size_t)g + 1]; ++ri) {
+                const Rect& r = rects[ri];
+                for (int w = r.w0; w <= r.w1; ++w)
+                    for (int u = r.u0; u <= r.u1; ++u) {
+                        const uint32_t at = base + count[((size_t)r.face * res + w) * res + u]++;
+                        out->entry_gi[at] = leaf_of_orig[g];
+                        out->entry_dmin[at] = dmin[g];
+                    }
+            }
+        out->mask |= 1u << l;
+    }
+}
+
+}  // namespace vr

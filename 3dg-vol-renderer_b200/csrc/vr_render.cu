@@ -45,6 +45,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
         VR_CUDA(cudaMemsetAsync(ctx->image.p, 0, (size_t)3 * W * H * sizeof(float), s));
         ctx->img_w = W; ctx->img_h = H;
     }
+    if (ctx->engine == 0) { rc = ensure_light_grids(ctx); if (rc) return rc; }
     RenderArgs A{};
     A.scene = ctx->scene_dev();
     A.cam = ctx->cam;

@@ -32,7 +32,7 @@ namespace vr {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t wave_pool_bytes(int P) {
     const size_t p = (size_t)P;
-    return align256(p * 32) * 4 + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 4) * 4 + align256(p * 4 * kPostClasses) +
+    return align256(p * 32) * 4 + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 4) * 5 + align256(p * 4 * kPostClasses) +
            align256(kWaveCounters * 4);
 }
 void wave_pool_carve(WavePool* q, int P, void* base) {
@@ -44,7 +44,7 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     q->hit01 = (uint4*)take(p * 32);
     q->hit_t0 = (float*)take(p * 4 * (kWaveCap - 2)); q->hit_t1 = (float*)take(p * 4 * (kWaveCap - 2));
     q->hit_gi = (uint32_t*)take(p * 4 * (kWaveCap - 2));
-    q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4);
+    q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4); q->listTl = (unsigned int*)take(p * 4);
     q->listA = (unsigned int*)take(p * 4 * kPostClasses); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
     q->cnt = (unsigned int*)take(kWaveCounters * 4);
 }
@@ -77,7 +77,7 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
         if (cn.over) atomicAdd(A.stats + ST_OVERFLOW, (unsigned long long)cn.over);
     }
 }
-enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2 };
+enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2, DEST_TRAV_LIGHT = 3 };
 // overlap records of a slot: the count and the first two records share one 32-byte sector (85 % of the free-flight
 // rays of a sparse mixture gather at most two components), the rest live in [k - 2][P] arrays
 __device__ __forceinline__ void pool_store_hit(const WavePool& Q, unsigned int p, int k, float t0, float t1, uint32_t gi) {
@@ -115,6 +115,12 @@ constexpr int kTravHitQueueCap = 64;      // shadow overlaps: < 32 left over + o
 #ifndef VR_WAIT_H
 #define VR_WAIT_H 4
 #endif
+#ifndef VR_FETCH_L
+#define VR_FETCH_L 8
+#endif
+#ifndef VR_WAIT_L
+#define VR_WAIT_L 4
+#endif
 #ifndef VR_FETCH_S
 #define VR_FETCH_S 16
 #endif
@@ -135,8 +141,8 @@ constexpr int kTravHitQueueCap = 64;      // shadow overlaps: < 32 left over + o
 // there), so it waits for more lanes than the shadow kernel (sweep in profiles/r01_tuning.md)
 // candidate batches normally run full (32 entries); they run early once this many lanes have finished their traversal
 // and only wait for queued candidates (those lanes cannot take a new ray before their result is complete)
-template <int KIND> struct WaitThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_WAIT_S : VR_WAIT_H; };
-template <int KIND> struct FetchThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_FETCH_S : VR_FETCH_H; };
+template <int KIND> struct WaitThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_WAIT_S : (KIND == RAY_SHADOW ? VR_WAIT_H : VR_WAIT_L); };
+template <int KIND> struct FetchThreshold { static constexpr unsigned value = KIND == RAY_SCATTER ? VR_FETCH_S : (KIND == RAY_SHADOW ? VR_FETCH_H : VR_FETCH_L); };
 
 template <int KIND> struct TravShared;
 template <> struct TravShared<RAY_SCATTER> {
@@ -156,6 +162,8 @@ template <> struct TravShared<RAY_SHADOW> {
     uint32_t hq_id[kTravHitQueueCap];
     float hq_a[kTravHitQueueCap], hq_b[kTravHitQueueCap];
 };
+
+template <> struct TravShared<RAY_LIGHT> : TravShared<RAY_SHADOW> {};   // same per-warp state; candidates come from the light's grid
 
 enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
 
@@ -256,38 +264,54 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
                                             int& nQ, bool can_fetch) {
     while (true) {
         bool l0 = false, l1 = false, fin = false;
-        int c0 = 0, c1 = 0;
+        uint32_t g0 = 0, g1 = 0;   // leaf-order indices of the candidates this lane queues in this round
         if (tl.mode == T_TRAV) {
-            float tlimit;
-            bool stop;
-            if (KIND == RAY_SCATTER) {
-                TravShared<RAY_SCATTER>& ws = reinterpret_cast<TravShared<RAY_SCATTER>&>(w);
-                tlimit = __uint_as_float(ws.t_bound[lane]); stop = ws.count[lane] > kWaveCap;
-            } else {
+            if constexpr (KIND == RAY_LIGHT) {
+                // candidates come from the cell list of the light's direction grid, nearest to the light first; the
+                // list ends for this ray at the first component that lies beyond the ray's origin (vr_lightgrid.h)
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
-                tlimit = tl.tmax; stop = wh.tau[lane] > tau_cutoff_fixed();
+                int pos = tl.cur;
+                const int end = tl.sp;
+                if (!(wh.tau[lane] > tau_cutoff_fixed()) && pos < end && __ldg(S.lg_dmin + pos) <= tl.tmax) {
+                    l0 = true; g0 = __ldg(S.lg_gi + pos); ++pos;
+                    if (pos < end && __ldg(S.lg_dmin + pos) <= tl.tmax) { l1 = true; g1 = __ldg(S.lg_gi + pos); ++pos; }
+                }
+                tl.cur = pos;
+                if (!l1) { fin = true; tl.mode = T_WAIT; }
+            } else {
+                float tlimit;
+                bool stop;
+                if (KIND == RAY_SCATTER) {
+                    TravShared<RAY_SCATTER>& ws = reinterpret_cast<TravShared<RAY_SCATTER>&>(w);
+                    tlimit = __uint_as_float(ws.t_bound[lane]); stop = ws.count[lane] > kWaveCap;
+                } else {
+                    TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
+                    tlimit = tl.tmax; stop = wh.tau[lane] > tau_cutoff_fixed();
+                }
+                bool h0, h1; float tn0, tn1;
+                int c0, c1;
+                node_slabs_q(S.qnodes, tl.cur, tl.rq, tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
+                if (stop) { h0 = h1 = false; tl.sp = 0; }
+                l0 = h0 && c0 < 0 && ((~c0) & 7);   // leaf child with a Gaussian in it
+                l1 = h1 && c1 < 0 && ((~c1) & 7);
+                g0 = (uint32_t)(~c0) >> 3; g1 = (uint32_t)(~c1) >> 3;
+                const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
+                if (i0 && i1) {
+                    const bool swap = tn1 < tn0;
+                    stack[tl.sp++] = swap ? c0 : c1;
+                    tl.cur = swap ? c1 : c0;
+                } else if (i0) tl.cur = c0;
+                else if (i1) tl.cur = c1;
+                else if (tl.sp > 0) tl.cur = stack[--tl.sp];
+                else { fin = true; tl.mode = T_WAIT; }   // resolved below once the pushes are counted
             }
-            bool h0, h1; float tn0, tn1;
-            node_slabs_q(S.qnodes, tl.cur, tl.rq, tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
-            if (stop) { h0 = h1 = false; tl.sp = 0; }
-            l0 = h0 && c0 < 0 && ((~c0) & 7);   // leaf child with a Gaussian in it
-            l1 = h1 && c1 < 0 && ((~c1) & 7);
-            const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
-            if (i0 && i1) {
-                const bool swap = tn1 < tn0;
-                stack[tl.sp++] = swap ? c0 : c1;
-                tl.cur = swap ? c1 : c0;
-            } else if (i0) tl.cur = c0;
-            else if (i1) tl.cur = c1;
-            else if (tl.sp > 0) tl.cur = stack[--tl.sp];
-            else { fin = true; tl.mode = T_WAIT; }   // resolved below once the pushes are counted
             tl.pushed += (int)l0 + (int)l1;
         }
         const unsigned m0 = __ballot_sync(0xffffffffu, l0);
-        if (l0) w.queue[nQ + __popc(m0 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | ((uint32_t)(~c0) >> 3);
+        if (l0) w.queue[nQ + __popc(m0 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | g0;
         nQ += __popc(m0);
         const unsigned m1 = __ballot_sync(0xffffffffu, l1);
-        if (l1) w.queue[nQ + __popc(m1 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | ((uint32_t)(~c1) >> 3);
+        if (l1) w.queue[nQ + __popc(m1 & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | g1;
         nQ += __popc(m1);
         if (fin && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
         if (nQ >= 32) break;
@@ -306,13 +330,13 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
     TravShared<KIND>& w = wsh[threadIdx.x >> 5];
     const SceneDev& S = A.scene;
     const int lane = threadIdx.x & 31;
-    const unsigned int nT = Q.cnt[KIND == RAY_SCATTER ? WC_NTS : WC_NTH];
-    const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : Q.listTh;
-    unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : WC_CURSOR_H];
+    const unsigned int nT = Q.cnt[KIND == RAY_SCATTER ? WC_NTS : (KIND == RAY_SHADOW ? WC_NTH : WC_NTL)];
+    const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : (KIND == RAY_SHADOW ? Q.listTh : Q.listTl);
+    unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : (KIND == RAY_SHADOW ? WC_CURSOR_H : WC_CURSOR_L)];
     // the list consumed by the previous kernel of the chain (regen -> travS -> postA -> travH -> postB) is free again
     if (blockIdx.x == 0 && threadIdx.x < kPostClasses) {
         if (KIND == RAY_SCATTER) { if (threadIdx.x == 0) Q.cnt[WC_NC] = 0; }
-        else Q.cnt[WC_NA + threadIdx.x] = 0;
+        else if (KIND == RAY_SHADOW) Q.cnt[WC_NA + threadIdx.x] = 0;
     }
     int stack[kStackDepth];
     TravLane tl;
@@ -323,7 +347,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
     while (true) {
         const unsigned mT = __ballot_sync(0xffffffffu, tl.mode == T_TRAV);
         const bool drain = mT == 0 || (WaitThreshold<KIND>::value <= 32 && __popc(__ballot_sync(0xffffffffu, tl.mode == T_WAIT)) >= WaitThreshold<KIND>::value);
-        if (KIND == RAY_SHADOW) {
+        if (KIND != RAY_SCATTER) {
             if (nH >= 32 || (nH > 0 && drain && nQ == 0)) {
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
                 const int nb = min(nH, 32);
@@ -392,9 +416,18 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                         } else {
                             reinterpret_cast<TravShared<RAY_SHADOW>&>(w).tau[lane] = 0LL;
                         }
-                        tl.rq = ray_setup_q(S, mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
-                        tl.tmax = ro.w; tl.sp = 0; tl.cur = 0;
-                        const bool nothing = S.n == 0 || (KIND == RAY_SHADOW && !(ro.w > 0.0f));
+                        if constexpr (KIND == RAY_LIGHT) {
+                            const int light = (__float_as_int(rd.w) >> 8) - 1;
+                            const f3 v = mk3(ro.x - __ldg(S.lpos + 3 * light), ro.y - __ldg(S.lpos + 3 * light + 1), ro.z - __ldg(S.lpos + 3 * light + 2));
+                            const size_t cells = (size_t)6 * S.lg_res * S.lg_res;
+                            const uint32_t* cs = S.lg_start + (size_t)light * (cells + 1) + light_grid_cell_dev(v, S.lg_res);
+                            tl.cur = (int)__ldg(cs); tl.sp = (int)__ldg(cs + 1);
+                            tl.tmax = __fmaf_rn(ro.w, 1.000001f, 1e-6f);   // entries farther from the light than the ray's origin cannot overlap it
+                        } else {
+                            tl.rq = ray_setup_q(S, mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
+                            tl.tmax = ro.w; tl.sp = 0; tl.cur = 0;
+                        }
+                        const bool nothing = S.n == 0 || (KIND != RAY_SCATTER && !(ro.w > 0.0f));
                         if (nothing) tl.has_result = true;   // stays in T_FETCH: flushed at the next fetch step
                         else tl.mode = T_TRAV;
                     } else {
@@ -517,10 +550,11 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
         light = -1;
     }
     Q.ray[2 * (size_t)p] = make_float4(pos.x, pos.y, pos.z, dist);
-    Q.ray[2 * (size_t)p + 1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW));
+    Q.ray[2 * (size_t)p + 1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW | ((light + 1) << 8)));
     reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
     Q.ps2[2 * (size_t)p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
-    return DEST_TRAV;
+    // a ray to a point light that has a direction grid takes its candidates from the grid (wave_trav_kernel<RAY_LIGHT>)
+    return (light >= 0 && light < 32 && ((S.lg_mask >> light) & 1u)) ? DEST_TRAV_LIGHT : DEST_TRAV;
 }
 
 template <bool FAST>
@@ -637,6 +671,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
         }
         if (FAST) wave_append(Q.listA + (size_t)1 * Q.P, &Q.cnt[WC_NA + 1], hand_over, p);
         wave_append(Q.listTh, &Q.cnt[WC_NTH], dest == DEST_TRAV, p);
+        wave_append(Q.listTl, &Q.cnt[WC_NTL], dest == DEST_TRAV_LIGHT, p);
         wave_append(Q.listC, &Q.cnt[WC_NC], dest == DEST_REGEN, p);
     }
     wave_flush_counters(A, cn);
@@ -647,7 +682,7 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
     const SceneDev& S = A.scene;
     const unsigned int nB = Q.cnt[WC_NB];
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // both traversal kernels of this iteration are over
-        Q.cnt[WC_NTH] = 0; Q.cnt[WC_CURSOR_S] = 0; Q.cnt[WC_CURSOR_H] = 0;
+        Q.cnt[WC_NTH] = 0; Q.cnt[WC_NTL] = 0; Q.cnt[WC_CURSOR_S] = 0; Q.cnt[WC_CURSOR_H] = 0; Q.cnt[WC_CURSOR_L] = 0;
     }
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
@@ -730,18 +765,20 @@ __global__ void wave_init_kernel(const __grid_constant__ WavePool Q, unsigned in
 // ------------------------------------------------------------------------------------------
 int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsigned int* h_cnt, cudaStream_t s,
                        unsigned int* launches) {
-    static int bps_s = 0, bps_h = 0;
+    static int bps_s = 0, bps_h = 0, bps_l = 0;
     if (!bps_s) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_h, wave_trav_kernel<RAY_SHADOW>, kBlockThreads, 0);
-        bps_s = std::max(bps_s, 1); bps_h = std::max(bps_h, 1);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_l, wave_trav_kernel<RAY_LIGHT>, kBlockThreads, 0);
+        bps_s = std::max(bps_s, 1); bps_h = std::max(bps_h, 1); bps_l = std::max(bps_l, 1);
     }
     const unsigned int slots = (unsigned int)std::min<unsigned long long>((unsigned long long)q.P, a.work_count);
     wave_init_kernel<<<(std::max(slots, (unsigned int)kWaveCounters) + 255) / 256, 256, 0, s>>>(q, slots);
     ++*launches;
     // persistent traversal grids, but never more warps than a wave of `slots` rays can keep busy
     const int need_blocks = (int)std::max(1u, (slots + kBlockThreads - 1) / kBlockThreads);
-    const int grid_s = std::min(num_sms * bps_s, need_blocks), grid_h = std::min(num_sms * bps_h, need_blocks);
+    const int grid_s = std::min(num_sms * bps_s, need_blocks), grid_h = std::min(num_sms * bps_h, need_blocks),
+              grid_l = std::min(num_sms * bps_l, need_blocks);
     const int grid_post = std::max(1, (int)std::min<unsigned int>((slots + 127) / 128, (unsigned int)num_sms * 16));
     const int grid_post256 = std::max(1, (grid_post + 1) / 2);
     int iters = 0;
@@ -750,8 +787,8 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return -1;
     const char* prof_env = getenv("VR_WAVE_PROFILE");
     const bool prof = prof_env && prof_env[0] == '1';
-    cudaEvent_t pe[6];
-    double pt[5] = {0, 0, 0, 0, 0};
+    cudaEvent_t pe[7];
+    double pt[5] = {0, 0, 0, 0, 0}, pt_light = 0;
     unsigned long long cls_total[kPostClasses] = {0, 0, 0, 0, 0};
     if (prof) for (auto& e : pe) cudaEventCreate(&e);
     while (true) {
@@ -772,12 +809,15 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
                 for (int c = 0; c < kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
             }
             wave_trav_kernel<RAY_SHADOW><<<grid_h, kBlockThreads, 0, s>>>(a, q);
+            if (prof) cudaEventRecord(pe[6], s);
+            if (a.scene.lg_mask) { wave_trav_kernel<RAY_LIGHT><<<grid_l, kBlockThreads, 0, s>>>(a, q); ++*launches; }
             if (prof) cudaEventRecord(pe[4], s);
             wave_post_b_kernel<<<grid_post256, 256, 0, s>>>(a, q);
             if (prof) {
                 cudaEventRecord(pe[5], s);
                 cudaEventSynchronize(pe[5]);
                 for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); pt[k] += ms; }
+                { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
             }
             *launches += 6;
             ++iters;
@@ -796,6 +836,7 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
     if (prof) {
         fprintf(stderr, "[wave] samples %u iters %d  regen %.3f  trav_scatter %.3f  post_a %.3f  trav_shadow %.3f  post_b %.3f ms\n",
                 a.work_count, iters, pt[0], pt[1], pt[2], pt[3], pt[4]);
+        fprintf(stderr, "[wave] of trav_shadow: %.3f ms in the light-grid kernel\n", pt_light);
         fprintf(stderr, "[wave] post-A slots by overlap count: K=1 %llu  K=2 %llu  K=3..4 %llu  K=5..8 %llu  K>8 %llu\n", cls_total[0], cls_total[1],
                 cls_total[2], cls_total[3], cls_total[4]);
         for (auto& e : pe) cudaEventDestroy(e);

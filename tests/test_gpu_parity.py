@@ -243,6 +243,32 @@ def test_recorded_sets_match_reference(ctx, ob, vr, golden, scenegen):
         assert same / len(ref) >= 0.98
 
 
+def test_light_grid_is_only_a_candidate_source(ctx, ob, vr, scenegen):
+    """Point-light shadow rays take their candidates from per-light direction grids instead of the hierarchy
+    (vr_lightgrid.h).  Shadow depths are summed in fixed point, so ANY superset of the overlapped components
+    gives the same bits: images with the grids on and off must be identical -- a missed component would show."""
+    for n, seed, nonuni, lights in [(3000, 11, True, None), (800, 12, False, [[0.2, 1.1, 0.1, 30, 30, 30], [0.0, 5.0, 0.1, 50, 0, 0]]),
+                                    (1500, 13, False, [[4.0, 1.0, 0.0, 40, 40, 40], [0.0, -3.0, 0.5, 0, 30, 0], [-0.7, 2.6, -0.9, 0, 0, 30],
+                                                       [0.0, 1.0, -5.0, 9, 9, 9]])]:
+        scene = scenegen.generate(n, seed, nonuniform=nonuni, diameter_range=(0.02, 0.09))
+        if lights is not None:
+            scene["lights"] = np.array(lights, np.float32)      # the second case puts a light INSIDE the cloud (no grid for it)
+        imgs = []
+        for cam in ("pin", "pin2"):
+            for grid, res in ((1, 256), (0, 256), (1, 32)):
+                ctx.set_option("light_grid", grid); ctx.set_option("light_grid_res", res)
+                setup(ctx, ob, vr, scenegen, None, cam, scene=scene)
+                img, st = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 96, 64, 16))
+                imgs.append(img)
+            assert np.array_equal(imgs[-3], imgs[-2]) and np.array_equal(imgs[-1], imgs[-2])
+        for grid in (1, 0):
+            ctx.set_option("light_grid", grid)
+            setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
+            imgs.append(ctx.render(vr.Context.params(vr.INTEGRATOR_SS, 64, 64, 16))[0])
+        assert np.array_equal(imgs[-1], imgs[-2])
+    ctx.set_option("light_grid", 1); ctx.set_option("light_grid_res", 256)
+
+
 # ------------------------------------------------------------------------------------------------
 # edge cases and size-independent properties
 # ------------------------------------------------------------------------------------------------

@@ -3,5 +3,5 @@
 for v in "$@"; do
   if [ "$v" = default ]; then lib=""; else lib="$PWD/3dg-vol-renderer_b200/libvolrender_b200_$v.so"; fi
   echo "== $v"
-  VR_LIB=$lib VR_WAVE_PROFILE=1 python bench.py --steps 1 --warmup 1 --spp 64 --no-cpu-baseline 2>&1 | grep -E "^\[wave\]" | tail -2
+  VR_LIB=$lib VR_WAVE_PROFILE=1 python bench.py --steps 1 --warmup 1 --spp 64 --no-cpu-baseline 2>&1 | grep -E "^\[wave\]" | tail -3
 done
