@@ -67,6 +67,7 @@ int vr_create(vr_context** out, int device_id) {
     for (auto& e : ctx->ev) VR_CUDA(cudaEventCreate(&e));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_stats, sizeof(unsigned long long) * kNumStats));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_counters, sizeof(unsigned int) * 32));
+    VR_CUDA(cudaMallocHost((void**)&ctx->h_wave_counters, sizeof(unsigned int) * kMaxWaveParts * kWaveCounters));
     VR_CUDA(ctx->stats.ensure(sizeof(unsigned long long) * kNumStats));
     VR_CUDA(ctx->counters.ensure(sizeof(unsigned int) * 4));
     ctx->blocks_per_sm_main = std::max(1, path_kernel_blocks_per_sm(false));
@@ -86,6 +87,8 @@ void vr_destroy(vr_context* ctx) {
         b->release();
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+    if (ctx->h_wave_counters) cudaFreeHost(ctx->h_wave_counters);
+    for (cudaStream_t ws : ctx->wave_streams) if (ws) cudaStreamDestroy(ws);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -102,6 +105,7 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
     if (!strcmp(name, "light_grid")) { ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "light_grid_res")) { ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
+    if (!strcmp(name, "wave_parts")) { ctx->wave_parts = std::max(1, std::min(kMaxWaveParts, (int)value)); ctx->wavepool.release(); return VR_OK; }
     if (!strcmp(name, "wave_slots")) { ctx->wave_slots = std::max(0, (int)value); ctx->wavepool.release(); return VR_OK; }
     return fail(ctx, VR_ERR_INVALID_ARGUMENT, std::string("unknown option ") + name);
 }

@@ -73,6 +73,9 @@ struct vr_context {
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
     int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
     int wave_slots = 0;                            // 0 = 8192 per SM
+    int wave_parts = 2;                            // independent parts (own pool + stream) a big pass is cut into
+    cudaStream_t wave_streams[vr::kMaxWaveParts] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned int* h_wave_counters = nullptr;       // pinned, kMaxWaveParts * kWaveCounters
     // ---- inverse
     vr::SfdState* sfd = nullptr;
 

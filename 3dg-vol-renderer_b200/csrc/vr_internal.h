@@ -18,7 +18,8 @@ struct RenderArgs {
     int solver, min_bounces;
     int x0, y0, win_w;     // owned pixel p -> x = x0 + p % win_w, y = y0 + (p / win_w) * part_count + part_rank
     int part_rank, part_count;
-    unsigned int pixel_base;      // first owned pixel of this pass
+    unsigned int pixel_base;      // first owned pixel of this pass (of this part of the pass, wavefront engine)
+    unsigned int work_base;       // wavefront engine: id of this part's first sample within the pass (0 otherwise)
     unsigned int work_count;      // samples in this pass = pass pixels * spp
     unsigned int* counter;        // work-fetch counter of this pass
     const unsigned int* worklist; // nullptr: work ids 0..work_count-1; else ids taken from this list (re-trace kernel)
@@ -64,8 +65,9 @@ struct WavePool {
 size_t wave_pool_bytes(int P);
 void wave_pool_carve(WavePool* q, int P, void* base);
 // runs the whole pass (a.work_count samples) ; returns the number of iterations enqueued, < 0 on CUDA error
-int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsigned int* h_cnt_pinned, cudaStream_t s,
-                       unsigned int* launches);
+constexpr int kMaxWaveParts = 4;
+int run_wavefront_pass(const RenderArgs& a, void* pool_mem, int P_total, int parts, int num_sms, unsigned int* h_cnt_pinned /* parts * kWaveCounters */,
+                       cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches);
 
 constexpr int kBlockThreads = 128;
 constexpr int kLocalCap = 32;        // overlaps kept in local memory by the main kernel

@@ -96,10 +96,16 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             VR_CUDA(cudaEventRecord(ctx->ev[2], s));
             if (ctx->engine == 0) {
                 const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 8192;
-                VR_CUDA(ctx->wavepool.ensure(wave_pool_bytes(P)));
-                WavePool Q;
-                wave_pool_carve(&Q, P, ctx->wavepool.p);
-                if (run_wavefront_pass(A, Q, ctx->num_sms, ctx->h_counters + 8, s, &launches) < 0) VR_CUDA(cudaGetLastError());
+                // big passes are cut into independent parts on their own streams so that kernel tails overlap
+                int parts = (unsigned long long)A.work_count >= 4ULL * (unsigned long long)P ? ctx->wave_parts : 1;
+                parts = std::max(1, std::min(parts, kMaxWaveParts));
+                VR_CUDA(ctx->wavepool.ensure(wave_pool_bytes(P / parts) * parts));
+                for (int i = 0; i < parts; ++i)
+                    if (!ctx->wave_streams[i]) VR_CUDA(cudaStreamCreateWithFlags(&ctx->wave_streams[i], cudaStreamNonBlocking));
+                if (run_wavefront_pass(A, ctx->wavepool.p, P, parts, ctx->num_sms, ctx->h_wave_counters, s, ctx->wave_streams, &launches) < 0) {
+                    VR_CUDA(cudaGetLastError());
+                    return fail(ctx, VR_ERR_CUDA, "wavefront pass failed");
+                }
             } else {
                 launch_path_kernel(A, grid_main, false, s); ++launches;
             }

@@ -635,7 +635,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     hand_over = true;   // untouched: the general kernel redoes it
                 }
             } else if (K > kWaveCap) {  // more overlaps than a slot holds: the whole sample is re-traced by the arena kernel
-                A.overflow_list[atomicAdd(A.overflow_count, 1u)] = s1.z;
+                A.overflow_list[atomicAdd(A.overflow_count, 1u)] = s1.z + A.work_base;
                 ++cn.over;
                 dest = DEST_REGEN;
             } else {
@@ -763,8 +763,11 @@ __global__ void wave_init_kernel(const __grid_constant__ WavePool Q, unsigned in
 // ------------------------------------------------------------------------------------------
 // host driver of one pass
 // ------------------------------------------------------------------------------------------
-int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsigned int* h_cnt, cudaStream_t s,
-                       unsigned int* launches) {
+// One pass = a.work_count samples.  The pass is cut into `parts` pixel ranges, each with its own pool of slots, counters
+// and stream; the kernel chains of the parts are independent, so the tail of one part's kernel (persistent warps waiting
+// for the last rays, 9-15 % of SM cycles per kernel in profiles/r01_v7) is filled by the other part's kernels.
+int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int parts, int num_sms, unsigned int* h_cnt_all,
+                       cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches) {
     static int bps_s = 0, bps_h = 0, bps_l = 0;
     if (!bps_s) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
@@ -772,76 +775,120 @@ int run_wavefront_pass(const RenderArgs& a, const WavePool& q, int num_sms, unsi
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_l, wave_trav_kernel<RAY_LIGHT>, kBlockThreads, 0);
         bps_s = std::max(bps_s, 1); bps_h = std::max(bps_h, 1); bps_l = std::max(bps_l, 1);
     }
-    const unsigned int slots = (unsigned int)std::min<unsigned long long>((unsigned long long)q.P, a.work_count);
-    wave_init_kernel<<<(std::max(slots, (unsigned int)kWaveCounters) + 255) / 256, 256, 0, s>>>(q, slots);
-    ++*launches;
-    // persistent traversal grids, but never more warps than a wave of `slots` rays can keep busy
-    const int need_blocks = (int)std::max(1u, (slots + kBlockThreads - 1) / kBlockThreads);
-    const int grid_s = std::min(num_sms * bps_s, need_blocks), grid_h = std::min(num_sms * bps_h, need_blocks),
-              grid_l = std::min(num_sms * bps_l, need_blocks);
-    const int grid_post = std::max(1, (int)std::min<unsigned int>((slots + 127) / 128, (unsigned int)num_sms * 16));
-    const int grid_post256 = std::max(1, (grid_post + 1) / 2);
-    int iters = 0;
-    const int kBatch = 8;
-    cudaEvent_t ev;
-    if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return -1;
     const char* prof_env = getenv("VR_WAVE_PROFILE");
     const bool prof = prof_env && prof_env[0] == '1';
+    const unsigned int pass_pixels = a_all.work_count / (unsigned int)a_all.spp;
+    parts = std::max(1, std::min(parts, kMaxWaveParts));
+    if (prof || pass_pixels < (unsigned int)parts) parts = 1;
+    struct Part {
+        RenderArgs a; WavePool q; cudaStream_t st; cudaEvent_t ev; unsigned int* h; bool done;
+        int grid_s, grid_h, grid_l, grid_post, grid_post256;
+    } part[kMaxWaveParts];
+    const int P_part = P_total / parts;
+    const size_t pool_stride = wave_pool_bytes(P_part);
+    cudaEvent_t fork;
+    if (cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) != cudaSuccess) return -1;
+    if (parts > 1) cudaEventRecord(fork, s);
+    for (int i = 0; i < parts; ++i) {
+        Part& pt = part[i];
+        const unsigned int px0 = (unsigned int)((unsigned long long)pass_pixels * i / parts), px1 = (unsigned int)((unsigned long long)pass_pixels * (i + 1) / parts);
+        pt.a = a_all;
+        pt.a.pixel_base = a_all.pixel_base + px0;
+        pt.a.work_base = px0 * (unsigned int)a_all.spp;
+        pt.a.work_count = (px1 - px0) * (unsigned int)a_all.spp;
+        pt.a.sampleL = a_all.sampleL + (size_t)px0 * a_all.spp;
+        wave_pool_carve(&pt.q, P_part, (char*)pool_mem + pool_stride * i);
+        pt.st = parts > 1 ? part_streams[i] : s;
+        pt.h = h_cnt_all + kWaveCounters * i;
+        pt.done = false;
+        if (cudaEventCreateWithFlags(&pt.ev, cudaEventDisableTiming) != cudaSuccess) return -1;
+        if (parts > 1) cudaStreamWaitEvent(pt.st, fork, 0);
+        const unsigned int slots = (unsigned int)std::min<unsigned long long>((unsigned long long)pt.q.P, pt.a.work_count);
+        wave_init_kernel<<<(std::max(slots, (unsigned int)kWaveCounters) + 255) / 256, 256, 0, pt.st>>>(pt.q, slots);
+        ++*launches;
+        // persistent traversal grids, but never more warps than a wave of `slots` rays can keep busy
+        const int need_blocks = (int)std::max(1u, (slots + kBlockThreads - 1) / kBlockThreads);
+        pt.grid_s = std::min(num_sms * bps_s, need_blocks); pt.grid_h = std::min(num_sms * bps_h, need_blocks);
+        pt.grid_l = std::min(num_sms * bps_l, need_blocks);
+        pt.grid_post = std::max(1, (int)std::min<unsigned int>((slots + 127) / 128, (unsigned int)num_sms * 16));
+        pt.grid_post256 = std::max(1, (pt.grid_post + 1) / 2);
+    }
+    int iters = 0;
+    const int kBatch = 8;
     cudaEvent_t pe[7];
-    double pt[5] = {0, 0, 0, 0, 0}, pt_light = 0;
+    double ptm[5] = {0, 0, 0, 0, 0}, pt_light = 0;
     unsigned long long cls_total[kPostClasses] = {0, 0, 0, 0, 0};
     if (prof) for (auto& e : pe) cudaEventCreate(&e);
-    while (true) {
+    bool failed = false;
+    while (!failed) {
+        bool any = false;
         for (int b = 0; b < kBatch; ++b) {
-            // chain: every kernel consumes the list the previous one filled
-            if (prof) cudaEventRecord(pe[0], s);
-            wave_regen_kernel<<<grid_post256, 256, 0, s>>>(a, q);
-            if (prof) cudaEventRecord(pe[1], s);
-            wave_trav_kernel<RAY_SCATTER><<<grid_s, kBlockThreads, 0, s>>>(a, q);
-            if (prof) cudaEventRecord(pe[2], s);
-            wave_post_a_kernel<true><<<grid_post, 128, 0, s>>>(a, q);
-            wave_post_a_kernel<false><<<grid_post, 128, 0, s>>>(a, q);
-            if (prof) {
-                cudaEventRecord(pe[3], s);
-                unsigned int hc[kWaveCounters];
-                cudaMemcpyAsync(hc, q.cnt, sizeof(hc), cudaMemcpyDeviceToHost, s);
-                cudaStreamSynchronize(s);
-                for (int c = 0; c < kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
+            for (int i = 0; i < parts; ++i) {
+                Part& pt = part[i];
+                if (pt.done) continue;
+                any = true;
+                const RenderArgs& a = pt.a; const WavePool& q = pt.q; cudaStream_t st = pt.st;
+                // chain: every kernel consumes the list the previous one filled
+                if (prof) cudaEventRecord(pe[0], st);
+                wave_regen_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
+                if (prof) cudaEventRecord(pe[1], st);
+                wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
+                if (prof) cudaEventRecord(pe[2], st);
+                wave_post_a_kernel<true><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<false><<<pt.grid_post, 128, 0, st>>>(a, q);
+                if (prof) {
+                    cudaEventRecord(pe[3], st);
+                    unsigned int hc[kWaveCounters];
+                    cudaMemcpyAsync(hc, q.cnt, sizeof(hc), cudaMemcpyDeviceToHost, st);
+                    cudaStreamSynchronize(st);
+                    for (int c = 0; c < kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
+                }
+                wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
+                if (prof) cudaEventRecord(pe[6], st);
+                if (a.scene.lg_mask) { wave_trav_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q); ++*launches; }
+                if (prof) cudaEventRecord(pe[4], st);
+                wave_post_b_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
+                if (prof) {
+                    cudaEventRecord(pe[5], st);
+                    cudaEventSynchronize(pe[5]);
+                    for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); ptm[k] += ms; }
+                    { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
+                }
+                *launches += 6;
             }
-            wave_trav_kernel<RAY_SHADOW><<<grid_h, kBlockThreads, 0, s>>>(a, q);
-            if (prof) cudaEventRecord(pe[6], s);
-            if (a.scene.lg_mask) { wave_trav_kernel<RAY_LIGHT><<<grid_l, kBlockThreads, 0, s>>>(a, q); ++*launches; }
-            if (prof) cudaEventRecord(pe[4], s);
-            wave_post_b_kernel<<<grid_post256, 256, 0, s>>>(a, q);
-            if (prof) {
-                cudaEventRecord(pe[5], s);
-                cudaEventSynchronize(pe[5]);
-                for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); pt[k] += ms; }
-                { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
-            }
-            *launches += 6;
             ++iters;
         }
-        if (cudaMemcpyAsync(h_cnt, q.cnt, sizeof(unsigned int) * kWaveCounters, cudaMemcpyDeviceToHost, s) != cudaSuccess ||
-            cudaEventRecord(ev, s) != cudaSuccess || cudaEventSynchronize(ev) != cudaSuccess) {
-            cudaEventDestroy(ev);
-            return -1;
+        if (!any) break;
+        for (int i = 0; i < parts; ++i) {
+            Part& pt = part[i];
+            if (pt.done) continue;
+            if (cudaMemcpyAsync(pt.h, pt.q.cnt, sizeof(unsigned int) * kWaveCounters, cudaMemcpyDeviceToHost, pt.st) != cudaSuccess ||
+                cudaEventRecord(pt.ev, pt.st) != cudaSuccess) failed = true;
         }
-        // after wave_post_b: rays left = listTs + slots waiting for a new sample
-        const bool more_samples = h_cnt[WC_NEXT_SAMPLE] < a.work_count;
-        if (h_cnt[WC_NTS] == 0 && (h_cnt[WC_NC] == 0 || !more_samples)) break;
+        for (int i = 0; i < parts && !failed; ++i) {
+            Part& pt = part[i];
+            if (pt.done) continue;
+            if (cudaEventSynchronize(pt.ev) != cudaSuccess) { failed = true; break; }
+            // after wave_post_b: rays left = listTs + slots waiting for a new sample
+            const bool more_samples = pt.h[WC_NEXT_SAMPLE] < pt.a.work_count;
+            if (pt.h[WC_NTS] == 0 && (pt.h[WC_NC] == 0 || !more_samples)) pt.done = true;
+        }
         if (iters > (1 << 24)) break;
     }
-    cudaEventDestroy(ev);
+    for (int i = 0; i < parts; ++i) {
+        if (parts > 1) { cudaEventRecord(part[i].ev, part[i].st); cudaStreamWaitEvent(s, part[i].ev, 0); }   // join
+        cudaEventDestroy(part[i].ev);
+    }
+    cudaEventDestroy(fork);
     if (prof) {
         fprintf(stderr, "[wave] samples %u iters %d  regen %.3f  trav_scatter %.3f  post_a %.3f  trav_shadow %.3f  post_b %.3f ms\n",
-                a.work_count, iters, pt[0], pt[1], pt[2], pt[3], pt[4]);
+                a_all.work_count, iters, ptm[0], ptm[1], ptm[2], ptm[3], ptm[4]);
         fprintf(stderr, "[wave] of trav_shadow: %.3f ms in the light-grid kernel\n", pt_light);
         fprintf(stderr, "[wave] post-A slots by overlap count: K=1 %llu  K=2 %llu  K=3..4 %llu  K=5..8 %llu  K>8 %llu\n", cls_total[0], cls_total[1],
                 cls_total[2], cls_total[3], cls_total[4]);
         for (auto& e : pe) cudaEventDestroy(e);
     }
-    return iters;
+    return failed ? -1 : iters;
 }
 
 }  // namespace vr

@@ -279,6 +279,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
     ap.add_argument("--wave-slots", type=int, default=0)
+    ap.add_argument("--wave-parts", type=int, default=0)
     a = ap.parse_args()
     cfg = dict(CONFIGS[a.config])
     if a.spp:
@@ -322,6 +323,8 @@ def main():
     ctx.set_option("engine", a.engine)
     if a.wave_slots:
         ctx.set_option("wave_slots", a.wave_slots)
+    if a.wave_parts:
+        ctx.set_option("wave_parts", a.wave_parts)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
     ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cam); ctx.set_gmm(scene)
     integ = vr.INTEGRATOR_SS if cfg["integrator"] == "ss" else vr.INTEGRATOR_MS
