@@ -104,6 +104,7 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
     if (!strcmp(name, "light_grid")) { ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
+    if (!strcmp(name, "light_grid_min_samples")) { ctx->light_grid_min_samples = value; return VR_OK; }
     if (!strcmp(name, "light_grid_res")) { ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "wave_parts")) { ctx->wave_parts = std::max(1, std::min(kMaxWaveParts, (int)value)); ctx->wavepool.release(); return VR_OK; }
     if (!strcmp(name, "wave_slots")) { ctx->wave_slots = std::max(0, (int)value); ctx->wavepool.release(); return VR_OK; }

@@ -50,6 +50,7 @@ struct vr_context {
     int lg_res = 256;
     uint32_t lg_mask = 0;
     int use_light_grid = 1;
+    double light_grid_min_samples = 16.0e6;       // renders smaller than this skip the grids (build cost > gain)
     // ---- sphere mixture
     bool has_smm = false;
     int n_spheres = 0;
@@ -72,7 +73,7 @@ struct vr_context {
     double max_pass_samples = 268435456.0;         // 2^28 samples = 4 GiB of per-sample radiance
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
     int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
-    int wave_slots = 0;                            // 0 = 8192 per SM
+    int wave_slots = 0;                            // 0 = 24576 per SM (sweep in profiles/r01_tuning.md)
     int wave_parts = 2;                            // independent parts (own pool + stream) a big pass is cut into
     cudaStream_t wave_streams[vr::kMaxWaveParts] = {nullptr, nullptr, nullptr, nullptr};
     unsigned int* h_wave_counters = nullptr;       // pinned, kMaxWaveParts * kWaveCounters

@@ -14,17 +14,23 @@ struct Rect { int face, u0, u1, w0, w1; };
 bool face_rect(const double lo[3], const double hi[3], int m, bool negative, int res, Rect* r) {
     const int a = (m + 1) % 3, b = (m + 2) % 3;
     // s * x_m over the box, s = -1 for the negative face
-    const double xm0 = negative ? -hi[m] : lo[m], xm1 = negative ? -lo[m] : hi[m];
+    double xm0 = negative ? -hi[m] : lo[m];
+    const double xm1 = negative ? -lo[m] : hi[m];
     if (!(xm1 > 0.0)) return false;
+    // a direction belongs to this face only if |v_a| <= v_m and |v_b| <= v_m: the part of the box that can project
+    // into the face has v_m >= the smallest |v_a| and |v_b| of the box
+    auto min_abs = [&](int c) { return lo[c] > 0.0 ? lo[c] : (hi[c] < 0.0 ? -hi[c] : 0.0); };
+    xm0 = std::max(xm0, std::max(min_abs(a), min_abs(b)));
+    if (xm0 > xm1) return false;
     double ulo = -1.0, uhi = 1.0, wlo = -1.0, whi = 1.0;
-    if (xm0 > 1e-9 && xm0 > 1e-6 * xm1) {   // the box is strictly in front of the face: exact perspective bounds
+    if (xm0 > 1e-9 && xm0 > 1e-6 * xm1) {   // strictly in front of the face: exact perspective bounds of the clipped box
         auto ratio = [&](int c, double* mn, double* mx) {
             *mn = std::min(lo[c] / xm0, lo[c] / xm1);
             *mx = std::max(hi[c] / xm0, hi[c] / xm1);
         };
         ratio(a, &ulo, &uhi); ratio(b, &wlo, &whi);
         if (ulo > 1.0 || uhi < -1.0 || wlo > 1.0 || whi < -1.0) return false;
-    }   // else: the box reaches the plane through the light -> whole face (conservative)
+    }   // else: the box reaches the light along this axis -> whole face (conservative; such lights normally get no grid)
     auto cell = [&](double c, double slack) {
         int i = (int)std::floor((c + 1.0) * 0.5 * res + slack);
         return std::min(res - 1, std::max(0, i));
@@ -83,6 +89,10 @@ void build_light_grids(int n, const float* lo, const float* hi, const uint32_t* 
         for (int g = 0; g < n && finite; ++g)
             for (int k = 0; k < 3; ++k) if (!std::isfinite(lo[3 * g + k]) || !std::isfinite(hi[3 * g + k])) finite = false;
         if (!finite) continue;
+        // bound the table: a light whose footprints add up to more than ~200 cells per component gets no grid
+        unsigned long long area = 0;
+        for (const Rect& r : rects) area += (unsigned long long)(r.u1 - r.u0 + 1) * (unsigned long long)(r.w1 - r.w0 + 1);
+        if (area > 200ULL * (unsigned long long)n + (1ULL << 20)) continue;
         std::fill(count.begin(), count.end(), 0u);
         for (int g = 0; g < n; ++g)
             for (uint32_t ri = rect_first[(size_t)g]; ri < rect_first[(size_t)g + 1]; ++ri) {

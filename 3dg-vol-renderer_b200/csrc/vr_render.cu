@@ -45,9 +45,13 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
         VR_CUDA(cudaMemsetAsync(ctx->image.p, 0, (size_t)3 * W * H * sizeof(float), s));
         ctx->img_w = W; ctx->img_h = H;
     }
-    if (ctx->engine == 0) { rc = ensure_light_grids(ctx); if (rc) return rc; }
+    // the per-light grids cost ~1 ms per 1000 components to build on the host: worth it from ~16 M samples on
+    const unsigned long long render_samples = (unsigned long long)(p->x1 - p->x0) * (unsigned long long)owned_rows(p) * (unsigned long long)p->spp;
+    const bool use_grids = ctx->engine == 0 && ctx->use_light_grid && (double)render_samples >= ctx->light_grid_min_samples;
+    if (use_grids) { rc = ensure_light_grids(ctx); if (rc) return rc; }
     RenderArgs A{};
     A.scene = ctx->scene_dev();
+    if (!use_grids) A.scene.lg_mask = 0;
     A.cam = ctx->cam;
     A.W = W; A.H = H; A.spp = p->spp;
     A.nsq = (int)std::sqrt((double)p->spp);  // integrator.h:562
@@ -95,7 +99,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             VR_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(unsigned int) * 4, s));
             VR_CUDA(cudaEventRecord(ctx->ev[2], s));
             if (ctx->engine == 0) {
-                const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 8192;
+                const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 24576;
                 // big passes are cut into independent parts on their own streams so that kernel tails overlap
                 int parts = (unsigned long long)A.work_count >= 4ULL * (unsigned long long)P ? ctx->wave_parts : 1;
                 parts = std::max(1, std::min(parts, kMaxWaveParts));

@@ -254,6 +254,7 @@ def test_light_grid_is_only_a_candidate_source(ctx, ob, vr, scenegen):
         if lights is not None:
             scene["lights"] = np.array(lights, np.float32)      # the second case puts a light INSIDE the cloud (no grid for it)
         imgs = []
+        ctx.set_option("light_grid_min_samples", 0)      # these renders are small: force the grids on
         for cam in ("pin", "pin2"):
             for grid, res in ((1, 256), (0, 256), (1, 32)):
                 ctx.set_option("light_grid", grid); ctx.set_option("light_grid_res", res)
@@ -266,7 +267,7 @@ def test_light_grid_is_only_a_candidate_source(ctx, ob, vr, scenegen):
             setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
             imgs.append(ctx.render(vr.Context.params(vr.INTEGRATOR_SS, 64, 64, 16))[0])
         assert np.array_equal(imgs[-1], imgs[-2])
-    ctx.set_option("light_grid", 1); ctx.set_option("light_grid_res", 256)
+    ctx.set_option("light_grid", 1); ctx.set_option("light_grid_res", 256); ctx.set_option("light_grid_min_samples", 16e6)
 
 
 # ------------------------------------------------------------------------------------------------
