@@ -290,6 +290,13 @@ __device__ __noinline__ float solve_newton(St& st, int na, float ta, float tb, f
 template <class St>
 __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, float ta, float tb, float remaining,
                                 int solver) {  // :150-187
+    if (solver == 4) {  // UNIFORM (:131-137): t = ta + u (tb - ta); the reference's u comes from a random_device-seeded
+                        // generator (parity unpinned), ours is hashed from the segment like the oracle's solve_uniform
+        const uint64_t h = splitmix64((((uint64_t)__float_as_uint(ta) << 32) | (uint64_t)__float_as_uint(tb)) ^
+                                      ((uint64_t)__float_as_uint(remaining) * 0x9E3779B97F4A7C15ULL));
+        const float u = __fmul_rn((float)(uint32_t)(h >> 40), 1.0f / 16777216.0f);
+        return __fadd_rn(ta, __fmul_rn(u, __fsub_rn(tb, ta)));
+    }
     if ((solver == 0 || solver == 1) && na == 1) {
         const int s = (int)st.U(U_ACT, 0);
         const GaussRec g = load_gauss(S.gauss, st.U(U_GI, s));

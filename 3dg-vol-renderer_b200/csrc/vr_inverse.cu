@@ -294,6 +294,33 @@ int vr_sfd_apply(vr_context* ctx, int S, const int8_t* signs, const double* F_di
     return VR_OK;
 }
 
+// checkpoint / resume of the optimiser: parameters, Adam moments and step count
+int vr_sfd_get_state(vr_context* ctx, float* params11, float* m, float* v, int* t) {
+    if (!ctx || !ctx->sfd || !params11 || !m || !v || !t) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_get_state: bad arguments");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    SfdState* s = ctx->sfd;
+    const size_t bytes = (size_t)11 * s->n * 4;
+    VR_CUDA(cudaMemcpyAsync(params11, s->params.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(m, s->m.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(v, s->v.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    *t = s->t;
+    return VR_OK;
+}
+
+int vr_sfd_set_state(vr_context* ctx, const float* params11, const float* m, const float* v, int t) {
+    if (!ctx || !ctx->sfd || !params11 || !m || !v || t < 0) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_set_state: bad arguments (vr_sfd_begin first)");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    SfdState* s = ctx->sfd;
+    const size_t bytes = (size_t)11 * s->n * 4;
+    VR_CUDA(cudaMemcpyAsync(s->params.p, params11, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(s->m.p, m, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(s->v.p, v, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    s->t = t;
+    return VR_OK;
+}
+
 int vr_sfd_get_params(vr_context* ctx, float* params11) {
     if (!ctx || !ctx->sfd || !params11) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_get_params: bad arguments");
     VR_CUDA(cudaSetDevice(ctx->device));

@@ -24,7 +24,7 @@ static int validate(vr_context* ctx, const vr_render_params* p) {
         return fail(ctx, VR_ERR_INVALID_ARGUMENT, "render: bad pixel window");
     if (p->part_count < 1 || p->part_rank < 0 || p->part_rank >= p->part_count)
         return fail(ctx, VR_ERR_INVALID_ARGUMENT, "render: bad row partition");
-    if (p->solver < 0 || p->solver > 3) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "render: unknown solver");
+    if (p->solver < 0 || p->solver > 4) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "render: unknown solver");
     if (!ctx->has_camera) return fail(ctx, VR_ERR_NO_SCENE, "render: no camera set");
     return VR_OK;
 }

@@ -6,7 +6,7 @@
 //
 // The reference picks its distance solver with a #define (distance_solvers.h:143-147); here it is a
 // runtime property: set_solver(), default ANALYTIC_PLUS_NEWTON (the shipped mode), and the same macros
-// (-DBISECTION, -DNEWTON, -DANALYTIC_PLUS_BISECTION) select the default when user code defines them.
+// (-DUNIFORM, -DBISECTION, -DNEWTON, -DANALYTIC_PLUS_BISECTION) select the default when user code defines them.
 #pragma once
 #include <cstdint>
 #include <memory>
@@ -22,7 +22,9 @@
 namespace vrhost {
 
 inline int default_solver() {
-#if defined(BISECTION)
+#if defined(UNIFORM)
+    return VR_SOLVER_UNIFORM;
+#elif defined(BISECTION)
     return VR_SOLVER_BISECTION;
 #elif defined(NEWTON)
     return VR_SOLVER_NEWTON;

@@ -63,7 +63,45 @@ struct SFDDConfig {
     std::string output_dir = "./sfd_output";
     int final_samples = 16384;             // inverse_integrator.h:231
     bool verbose = true;
+    // checkpoint / resume: every checkpoint_every iterations the optimiser state (iteration,
+    // parameters, Adam moments, sign-vector generator) is written to checkpoint_path; a non-empty resume_from continues
+    // a run from such a file and reproduces the uninterrupted run bit for bit
+    std::string checkpoint_path;
+    int checkpoint_every = 0;
+    std::string resume_from;
 };
+
+namespace vrhost {
+struct SfdCheckpoint {
+    int iteration = 0, adam_t = 0;
+    std::vector<float> params, m, v;
+    std::string rng_state;   // std::mt19937 text form
+
+    bool save(const std::string& path) const {
+        std::ofstream f(path, std::ios::binary);
+        if (!f) return false;
+        const uint64_t n = params.size(), r = rng_state.size();
+        f.write("VRSFD001", 8);
+        f.write((const char*)&iteration, 4); f.write((const char*)&adam_t, 4);
+        f.write((const char*)&n, 8); f.write((const char*)&r, 8);
+        f.write((const char*)params.data(), std::streamsize(n * 4)); f.write((const char*)m.data(), std::streamsize(n * 4));
+        f.write((const char*)v.data(), std::streamsize(n * 4)); f.write(rng_state.data(), std::streamsize(r));
+        return bool(f);
+    }
+    bool load(const std::string& path) {
+        std::ifstream f(path, std::ios::binary);
+        char magic[8];
+        uint64_t n = 0, r = 0;
+        if (!f || !f.read(magic, 8) || std::string(magic, 8) != "VRSFD001") return false;
+        f.read((char*)&iteration, 4); f.read((char*)&adam_t, 4); f.read((char*)&n, 8); f.read((char*)&r, 8);
+        if (!f || n > (1ull << 32) || r > (1ull << 20)) return false;
+        params.resize(n); m.resize(n); v.resize(n); rng_state.resize(r);
+        f.read((char*)params.data(), std::streamsize(n * 4)); f.read((char*)m.data(), std::streamsize(n * 4));
+        f.read((char*)v.data(), std::streamsize(n * 4)); f.read(&rng_state[0], std::streamsize(r));
+        return bool(f);
+    }
+};
+}  // namespace vrhost
 
 class StochasticFiniteDiffInverseIntegrator : public InverseIntegrator {
     std::shared_ptr<MultiScatterGaussians> forward_integrator;
@@ -114,12 +152,23 @@ public:
             dev.check(i, vr_sfd_set_target(dev.ctx(i), W, H, I_ref.data()));
         }
         std::mt19937 rng(cfg.seed);
+        int first_iter = 0;
+        if (!cfg.resume_from.empty()) {
+            vrhost::SfdCheckpoint ck;
+            if (!ck.load(cfg.resume_from) || int(ck.params.size()) != D) {
+                std::cerr << "Cannot resume from " << cfg.resume_from << std::endl;
+                return false;
+            }
+            for (int i = 0; i < nd; ++i) dev.check(i, vr_sfd_set_state(dev.ctx(i), ck.params.data(), ck.m.data(), ck.v.data(), ck.adam_t));
+            std::istringstream(ck.rng_state) >> rng;
+            first_iter = ck.iteration;
+        }
         std::vector<int8_t> signs(size_t(S) * D);
         std::vector<double> F(size_t(S) * n), Fpart(size_t(S) * n);
         Image I_base(W, H);
         const auto t0 = clock::now();
 
-        for (int iter = 0; iter < cfg.max_iters; ++iter) {
+        for (int iter = first_iter; iter < cfg.max_iters; ++iter) {
             for (int8_t& s : signs) s = (rng() & 1u) ? 1 : -1;
             vrhost::for_each_device(dev, [&](int i) {
                 vr_render_params rp{};
@@ -138,6 +187,14 @@ public:
                     for (size_t k = 0; k < F.size(); ++k) F[k] += Fpart[k];
                 }
                 for (int i = 0; i < nd; ++i) dev.check(i, vr_sfd_apply(dev.ctx(i), S, signs.data(), F.data(), nullptr));
+            }
+            if (cfg.checkpoint_every > 0 && !cfg.checkpoint_path.empty() && (iter + 1) % cfg.checkpoint_every == 0) {
+                vrhost::SfdCheckpoint ck;
+                ck.iteration = iter + 1;
+                ck.params.resize(size_t(D)); ck.m.resize(size_t(D)); ck.v.resize(size_t(D));
+                dev.check(0, vr_sfd_get_state(dev.ctx(0), ck.params.data(), ck.m.data(), ck.v.data(), &ck.adam_t));
+                std::ostringstream os; os << rng; ck.rng_state = os.str();
+                if (!ck.save(cfg.checkpoint_path)) std::cerr << "Cannot write checkpoint " << cfg.checkpoint_path << std::endl;
             }
             if (iter % cfg.save_every == 0) {
                 dev.check(0, vr_sfd_get_params(dev.ctx(0), params.data()));

@@ -10,7 +10,8 @@
 //              [--step 0.01 --env-samples 5] [--out output.ppm] [--raw image.f32] [--record lists.u32]
 //              [--repeat 1]
 //   vol_render --scene S.txt --inverse target.ppm [--iters 1000 --save-every 25 --sfd-samples 4 --lr 0.01
-//              --seed N --final-spp 16384 --out-dir ./sfd_output --save-scene fitted.txt]
+//              --seed N --final-spp 16384 --out-dir ./sfd_output --save-scene fitted.txt
+//              --checkpoint state.bin --checkpoint-every 50 --resume state.bin --save-params params.f32]
 // Devices: VR_DEVICES="0,1,..." (default "0").
 #include <chrono>
 #include <cstdio>
@@ -111,12 +112,18 @@ int main(int argc, char** argv) {
             cfg.num_stoch_samples = a.i("sfd-samples", cfg.num_stoch_samples); cfg.lr = a.f("lr", cfg.lr);
             cfg.seed = uint32_t(a.i("seed", int(cfg.seed))); cfg.final_samples = a.i("final-spp", cfg.final_samples);
             cfg.output_dir = a.str("out-dir", cfg.output_dir);
+            cfg.checkpoint_path = a.str("checkpoint", ""); cfg.checkpoint_every = a.i("checkpoint-every", 0);
+            cfg.resume_from = a.str("resume", ""); cfg.verbose = !a.has("quiet");
             StochasticFiniteDiffInverseIntegrator inv(camera, fwd, cfg);
             const auto t0 = std::chrono::high_resolution_clock::now();
             const bool ok = inv.optimize(scene, target);
             const std::chrono::duration<double> el = std::chrono::high_resolution_clock::now() - t0;
             std::printf("Inverse optimization time: %.6f seconds (%.3f iterations/s)\n", el.count(), cfg.max_iters / el.count());
             if (ok && a.has("save-scene")) write_scene_txt(a.str("save-scene", ""), inv.optimized_scene());
+            if (ok && a.has("save-params")) {
+                std::ofstream pf(a.str("save-params", ""), std::ios::binary);
+                pf.write((const char*)inv.optimized_params().data(), std::streamsize(inv.optimized_params().size() * 4));
+            }
             return ok ? 0 : 1;
         }
 

@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("VR_LIB") or os.path.join(HERE, "libvolrender_b200.so"
 CSRC = os.path.join(HERE, "csrc")
 
 INTEGRATOR_SS, INTEGRATOR_MS, INTEGRATOR_MARCH_SPHERES = 0, 1, 2
-SOLVER_ANALYTIC_NEWTON, SOLVER_ANALYTIC_BISECTION, SOLVER_NEWTON, SOLVER_BISECTION = 0, 1, 2, 3
+SOLVER_ANALYTIC_NEWTON, SOLVER_ANALYTIC_BISECTION, SOLVER_NEWTON, SOLVER_BISECTION, SOLVER_UNIFORM = 0, 1, 2, 3, 4
 CAMERA_PINHOLE, CAMERA_ORTHO = 0, 1
 
 STATUS = {0: "VR_OK", 1: "VR_ERR_INVALID_ARGUMENT", 2: "VR_ERR_CUDA", 3: "VR_ERR_NO_DEVICE", 4: "VR_ERR_NO_SCENE",
@@ -29,7 +29,7 @@ SYMBOLS = ["vr_create", "vr_destroy", "vr_last_error", "vr_version", "vr_device_
            "vr_set_gmm_params", "vr_set_smm", "vr_set_lights", "vr_set_camera", "vr_render", "vr_render_device",
            "vr_image_dev", "vr_get_recorded", "vr_transmittance", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
            "vr_sfd_apply", "vr_sfd_reset_fdiff", "vr_sfd_accumulate", "vr_sfd_read", "vr_sfd_fdiff_dev",
-           "vr_sfd_get_params", "vr_adam_step", "vr_unpack_params", "vr_set_option", "vr_kat_pcg", "vr_kat_gaussian",
+           "vr_sfd_get_params", "vr_sfd_get_state", "vr_sfd_set_state", "vr_adam_step", "vr_unpack_params", "vr_set_option", "vr_kat_pcg", "vr_kat_gaussian",
            "vr_kat_camera_rays", "vr_kat_events", "vr_kat_libm", "vr_kat_erfinv"]
 
 
@@ -101,6 +101,8 @@ def lib():
     L.vr_sfd_read.argtypes = [vp, fp, fp]
     L.vr_sfd_fdiff_dev.argtypes = [vp]; L.vr_sfd_fdiff_dev.restype = vp
     L.vr_sfd_get_params.argtypes = [vp, fp]
+    L.vr_sfd_get_state.argtypes = [vp, fp, fp, fp, C.POINTER(ci)]
+    L.vr_sfd_set_state.argtypes = [vp, fp, fp, fp, ci]
     L.vr_adam_step.argtypes = [vp, ci, fp, fp, fp, fp, C.POINTER(ci), C.c_float, C.c_float, C.c_float, C.c_float]
     L.vr_unpack_params.argtypes = [vp, ci, fp, fp, fp, fp, fp]
     L.vr_set_option.argtypes = [vp, C.c_char_p, C.c_double]
@@ -286,6 +288,15 @@ class Context:
         p = np.zeros(self._sfd_n * 11, np.float32)
         self._ck(self.L.vr_sfd_get_params(self.h, _ptr(p)))
         return p
+
+    def sfd_get_state(self):
+        D = self._sfd_n * 11
+        p, m, v = (np.zeros(D, np.float32) for _ in range(3)); t = C.c_int(0)
+        self._ck(self.L.vr_sfd_get_state(self.h, _ptr(p), _ptr(m), _ptr(v), C.byref(t)))
+        return p, m, v, t.value
+
+    def sfd_set_state(self, p, m, v, t):
+        self._ck(self.L.vr_sfd_set_state(self.h, _ptr(_f32(p)), _ptr(_f32(m)), _ptr(_f32(v)), int(t)))
 
     def adam_step(self, params, grads, m, v, t, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8):
         tt = C.c_int(t)

@@ -38,6 +38,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ENV = (0.53, 0.81, 0.92)
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, profiles/r01_v8_wave_all_kernels.md
+DOMINANT_KERNEL_DRAM_BYTES = None
 CONFIGS = {
     # name: (n_gaussians, seed, nonuniform, W, H, spp, integrator)
     "c1": dict(n=1000, seed=1, nonuniform=False, W=512, H=512, spp=64, integrator="ss",
@@ -116,6 +118,8 @@ def algorithmic_flop_per_sample(cfg, scene):
     n = max(c["paths"], 1)
     per = {k: v / n for k, v in c.items()}
     flop = 74 * per["hits"] + 44 * per["optical_depth"] + 28 * per["mu_t"] + 40 * per["analytic"] + 40 * per["scatter_rays"]
+    mufu = 5 * per["hits"] + 2 * per["optical_depth"] + per["mu_t"] + 4 * per["analytic"] + 5 * per["scatter_rays"]
+    per["mufu_per_sample"] = mufu
     return flop, per
 
 
@@ -401,15 +405,30 @@ def main():
     sm_clock = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
     n_sms = 148
     peak_tflops = n_sms * 128 * 2 * sm_clock * 1e6 * 1e-12
-    samples_per_launch = total_samples / world          # this rank's share; one path-kernel launch per pass
+    peak_mufu = n_sms * 16 * sm_clock * 1e6 * 1e-12      # Tops/s: 16 MUFU lanes per SM
+    samples_per_launch = total_samples / world          # this rank's share of the step (the step's chain of wave kernels)
     launch_ms = kern_ms_max / a.steps
     achieved = flop_per_sample * samples_per_launch / (launch_ms * 1e-3) * 1e-12
-    roof = dict(bound="fp32", achieved=achieved, peak=peak_tflops, unit="TFLOP/s", frac=achieved / peak_tflops, traffic=None,
-                note=f"algorithmic FP32 FLOP/sample {flop_per_sample:.0f} (oracle counters: " +
+    mufu_per_sample = per.pop("mufu_per_sample")
+    achieved_mufu = mufu_per_sample * samples_per_launch / (launch_ms * 1e-3) * 1e-12
+    frac_f, frac_m = achieved / peak_tflops, achieved_mufu / peak_mufu
+    # roofline.achieved = max(F_alg*rate/peak_FP32, M_alg*rate/peak_MUFU); neither "hbm" nor "tensor"
+    # bounds this path (no dense contraction, ~0 compulsory bytes per sample), which the hbm entry below documents
+    hbm_gbs = (3 * 4 * W * H + 112 * cfg["n"]) / world / (launch_ms * 1e-3) * 1e-9
+    roof = dict(bound="fp32" if frac_f >= frac_m else "mufu",
+                achieved=achieved if frac_f >= frac_m else achieved_mufu, peak=peak_tflops if frac_f >= frac_m else peak_mufu,
+                unit="TFLOP/s" if frac_f >= frac_m else "Tops/s", frac=max(frac_f, frac_m),
+                # DRAM bytes of the dominant kernel (wave_trav_kernel<free-flight>) per launch, ncu --set full capture of this command
+                traffic=DOMINANT_KERNEL_DRAM_BYTES,
+                fp32=dict(achieved=achieved, peak=peak_tflops, unit="TFLOP/s", frac=frac_f, flop_per_sample=flop_per_sample),
+                mufu=dict(achieved=achieved_mufu, peak=peak_mufu, unit="Tops/s", frac=frac_m, ops_per_sample=mufu_per_sample),
+                hbm=dict(achieved=hbm_gbs, peak=peaks.get("hbm_gbs", 6650.0), unit="GB/s", frac=hbm_gbs / peaks.get("hbm_gbs", 6650.0),
+                         note="compulsory bytes only: 12*W*H image + 112 B per Gaussian"),
+                note="algorithmic work per sample from the oracle's counters on this scene (unpruned walk of the reference): " +
                      ", ".join(f"{k} {v:.2f}" for k, v in per.items() if k != "paths") +
-                     f"); peak = {n_sms} SMs x 128 x 2 x {sm_clock:.0f} MHz (clock sampled under load); "
-                     f"hbm for context: {3 * 4 * W * H / world / (launch_ms * 1e-3) * 1e-9:.2f} GB/s compulsory vs "
-                     f"{peaks.get('hbm_gbs', 6650.0)} GB/s measured peak")
+                     f"; FP32 peak = {n_sms} SMs x 128 x 2 x {sm_clock:.0f} MHz, MUFU peak = {n_sms} x 16 x clock (clock sampled under load); "
+                     "time = device time of the step's wave kernels (CUDA events on the context's stream); hierarchy / grid "
+                     "traversal is implementation overhead and is NOT counted as achieved work (see profiles/ for raw pipe utilisation)")
     cpu = None
     if not a.no_cpu_baseline:
         cpu = cpu_render_sample(cfg, scene)

@@ -48,7 +48,8 @@ typedef enum vr_solver {
     VR_SOLVER_ANALYTIC_PLUS_NEWTON = 0, /* shipped default */
     VR_SOLVER_ANALYTIC_PLUS_BISECTION = 1,
     VR_SOLVER_NEWTON = 2,
-    VR_SOLVER_BISECTION = 3
+    VR_SOLVER_BISECTION = 3,
+    VR_SOLVER_UNIFORM = 4               /* distance_solvers.h:131-137; u is hashed from the segment (the reference's is unseeded) */
 } vr_solver;
 
 typedef enum vr_camera_kind { VR_CAMERA_PINHOLE = 0, VR_CAMERA_ORTHOGRAPHIC = 1 } vr_camera_kind;
@@ -145,6 +146,9 @@ int vr_sfd_accumulate(vr_context* ctx, const vr_render_params* rp, int S, const 
 int vr_sfd_read(vr_context* ctx, double* F_diff /* S*n or NULL */, double* loss_sum /* or NULL */);
 int64_t* vr_sfd_fdiff_dev(vr_context* ctx);
 int vr_sfd_get_params(vr_context* ctx, float* params11);
+/* optimiser state for checkpoint / resume: current parameters, Adam moments m and v (11n floats each), step count t */
+int vr_sfd_get_state(vr_context* ctx, float* params11, float* m, float* v, int* t);
+int vr_sfd_set_state(vr_context* ctx, const float* params11, const float* m, const float* v, int t);
 /* stand-alone AdamOptimizer::step on host arrays (state m, v, t owned by the caller) */
 int vr_adam_step(vr_context* ctx, int D, float* params, const float* grads, float* m, float* v, int* t, float lr,
                  float beta1, float beta2, float eps);

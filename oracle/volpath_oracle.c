@@ -528,9 +528,21 @@ static float solve_newton(const vo_gmm* m, const vo_ray* ray, float ta, float tb
     return solve_bisection(m, ray, ta, tb, act, na, target);
 }
 /* solver selector (runtime form of the #define block, distance_solvers.h:143-147) */
-enum { VO_SOLVER_ANALYTIC_NEWTON = 0, VO_SOLVER_ANALYTIC_BISECTION = 1, VO_SOLVER_NEWTON = 2, VO_SOLVER_BISECTION = 3 };
+enum { VO_SOLVER_ANALYTIC_NEWTON = 0, VO_SOLVER_ANALYTIC_BISECTION = 1, VO_SOLVER_NEWTON = 2, VO_SOLVER_BISECTION = 3,
+       VO_SOLVER_UNIFORM = 4 };
+/* distance_solvers.h:131-137: t = ta + u (tb - ta).  The reference draws u from a random_device-seeded mt19937
+ * (rng.h:6-10), i.e. it is not reproducible: PARITY UNPINNED for this mode.  Here u is a counter-based value hashed from
+ * the segment itself, so oracle and device agree bit for bit and the path's own PCG stream is left untouched. */
+static float solve_uniform(float ta, float tb, float remaining) {
+    uint32_t a, b, r;
+    memcpy(&a, &ta, 4); memcpy(&b, &tb, 4); memcpy(&r, &remaining, 4);
+    const uint64_t h = vo_splitmix64((((uint64_t)a << 32) | (uint64_t)b) ^ ((uint64_t)r * 0x9E3779B97F4A7C15ULL));
+    const float u = (float)(uint32_t)(h >> 40) * (1.0f / 16777216.0f);
+    return ta + u * (tb - ta);
+}
 static float solve_distance(const vo_gmm* m, const vo_ray* ray, float ta, float tb, const uint32_t* act, int na,
                             float remaining, int solver) { /* distance_solvers.h:150-187 */
+    if (solver == VO_SOLVER_UNIFORM) return solve_uniform(ta, tb, remaining);
     if ((solver == VO_SOLVER_ANALYTIC_NEWTON || solver == VO_SOLVER_ANALYTIC_BISECTION) && na == 1) {
         float t_an = 0.0f;
         if (gauss_solve_t(&m->g[act[0]], ray, ta, tb, remaining, &t_an)) return clampf(t_an, ta, tb);

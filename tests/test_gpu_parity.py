@@ -197,7 +197,7 @@ def test_render_min_bounces(ctx, ob, vr, golden, scenegen):
     assert frac_within(img, golden["render/rand50/pin/ms/16/minb1"], 1e-4) >= 0.98
 
 
-@pytest.mark.parametrize("solver", [0, 1, 2, 3])
+@pytest.mark.parametrize("solver", [0, 1, 2, 3, 4])
 def test_render_all_solvers_vs_oracle(ctx, ob, vr, scenegen, solver):
     """runtime form of the solver #define block (distance_solvers.h:143-147)"""
     scene, oc = setup(ctx, ob, vr, scenegen, "rand300", "pin2")

@@ -156,3 +156,24 @@ def test_vol_render_inverse_reduces_loss(host_bins, tmp_path):
     assert len(losses) >= 4 and losses[-1] < losses[0], losses
     assert (out_dir / "iter_0000.ppm").exists() and (out_dir / "iter_0030.ppm").exists()
     assert sum(1 for l in open(tmp_path / "fit.txt") if l.startswith("g ")) == 50
+
+
+@pytest.mark.gpu
+def test_inverse_checkpoint_resume_is_bit_exact(host_bins, tmp_path):
+    """12 iterations in one go == 6 iterations, checkpoint, resume for 6 more: identical final parameters
+    (state = parameters + Adam moments + step count + sign-vector generator)."""
+    exe = os.path.join(host_bins, "vol_render")
+    cam = _cam_args("pin")
+    tgt = tmp_path / "target.ppm"
+    scene = os.path.join(SCENES, "rand50.txt")
+    assert run([exe, "--scene", scene, "--spp", "16", "--width", "24", "--height", "24", "--out", str(tgt)] + cam).returncode == 0
+    common = [exe, "--scene", scene, "--inverse", str(tgt), "--spp", "16", "--save-every", "1000", "--final-spp", "16", "--quiet"] + cam
+    r = run(common + ["--iters", "12", "--out-dir", str(tmp_path / "a"), "--save-params", str(tmp_path / "a.f32")])
+    assert r.returncode == 0, r.stdout + r.stderr
+    ck = tmp_path / "state.bin"
+    r = run(common + ["--iters", "6", "--out-dir", str(tmp_path / "b"), "--checkpoint", str(ck), "--checkpoint-every", "6"])
+    assert r.returncode == 0 and ck.exists(), r.stdout + r.stderr
+    r = run(common + ["--iters", "12", "--out-dir", str(tmp_path / "c"), "--resume", str(ck), "--save-params", str(tmp_path / "c.f32")])
+    assert r.returncode == 0, r.stdout + r.stderr
+    a = np.fromfile(tmp_path / "a.f32", np.float32); c = np.fromfile(tmp_path / "c.f32", np.float32)
+    assert a.size == 550 and np.array_equal(a, c)

@@ -219,6 +219,20 @@ def test_sfd_iterations(ob, golden, scenegen):
         np.testing.assert_allclose(params, golden[f"sfd/iter{it}/13"], rtol=0, atol=1e-6)
 
 
+def test_uniform_solver_is_statistically_consistent(ob, scenegen):
+    """UNIFORM distance solver (distance_solvers.h:131-137): parity UNPINNED -- the reference draws u from a
+    random_device-seeded generator, the oracle hashes it from the segment.  The mode replaces the root solve by a
+    uniform pick inside the collision segment, so images must agree with the exact solver in the mean."""
+    scene = _scene(scenegen, "rand50")
+    cam = _cam(ob, "pin")
+    exact = ob.render(ob.Gmm(scene), scene["lights"], ENV, cam, ob.INTEGRATOR_MS, 32, 32, 16, solver=0)
+    uni = ob.render(ob.Gmm(scene), scene["lights"], ENV, cam, ob.INTEGRATOR_MS, 32, 32, 16, solver=4)
+    assert np.isfinite(uni).all() and not np.array_equal(uni, exact)
+    assert abs(float(uni.mean()) - float(exact.mean())) < 0.03 * float(exact.mean())
+    bg = (exact == np.array(ENV, np.float32)).all(axis=-1)
+    assert np.array_equal(uni[bg], exact[bg])        # rays that miss everything never reach a solver
+
+
 @pytest.mark.parametrize("name", ["one_sphere", "three_spheres"])
 def test_spheres_statistical(ob, golden, scenegen, name):
     """RayMarchingSpheres (test_integrators.h:23-135).  The reference's environment directions are
