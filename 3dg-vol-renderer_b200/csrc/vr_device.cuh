@@ -289,12 +289,11 @@ __device__ __noinline__ float solve_newton(St& st, int na, float ta, float tb, f
 }
 template <class St>
 __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, float ta, float tb, float remaining,
-                                int solver) {  // :150-187
+                                int solver, uint64_t key) {  // :150-187
     if (solver == 4) {  // UNIFORM (:131-137): t = ta + u (tb - ta); the reference's u comes from a random_device-seeded
-                        // generator (parity unpinned), ours is hashed from the segment like the oracle's solve_uniform
-        const uint64_t h = splitmix64((((uint64_t)__float_as_uint(ta) << 32) | (uint64_t)__float_as_uint(tb)) ^
-                                      ((uint64_t)__float_as_uint(remaining) * 0x9E3779B97F4A7C15ULL));
-        const float u = __fmul_rn((float)(uint32_t)(h >> 40), 1.0f / 16777216.0f);
+                        // generator (parity unpinned), ours is hashed from the path's PCG state after the target draw,
+                        // like the oracle's solve_uniform
+        const float u = __fmul_rn((float)(uint32_t)(splitmix64(key) >> 40), 1.0f / 16777216.0f);
         return __fadd_rn(ta, __fmul_rn(u, __fsub_rn(tb, ta)));
     }
     if ((solver == 0 || solver == 1) && na == 1) {
@@ -373,7 +372,7 @@ __device__ __forceinline__ bool next_event(const SceneDev& S, St& st, int K, int
 
 template <class St>
 __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float target_tau, int solver, bool ss,
-                             int* na_out) {
+                             int* na_out, uint64_t key) {
     sort_entries(S, st, K);
     double acc = 0.0;
     float accf = 0.0f;
@@ -412,7 +411,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
             for (int k = 0; k < na; ++k)  // restore erf(arg(t_prev)) for the solver
                 st.F(F_ACTF, k) = erff_ni(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
             *na_out = na;
-            return solve_distance(S, st, na, o, d, t_prev, t_evt, remaining, solver);
+            return solve_distance(S, st, na, o, d, t_prev, t_evt, remaining, solver, key);
         }
         if (take_enter) {
             const float F0 = erff_ni(erf_arg(hit_const(st, se), t_evt));

@@ -104,7 +104,7 @@ __device__ __forceinline__ int path_vertex(const RenderArgs& A, PathState& ps, S
     rng = peek;
     int na = 0;
     const bool ss = A.integrator == 0;
-    const float t = free_flight(S, st, K, ps.o, ps.d, target_tau, A.solver, ss, &na);
+    const float t = free_flight(S, st, K, ps.o, ps.d, target_tau, A.solver, ss, &na, rng.state);
     if (A.record_bits) {  // integrator.h:616-644
         const float tlim = __fadd_rn(t, 1e-6f);
         for (int s = 0; s < K; ++s)

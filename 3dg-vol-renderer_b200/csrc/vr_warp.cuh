@@ -229,7 +229,7 @@ static __device__ __noinline__ void lane_post_a(const RenderArgs& A, WarpShared&
     }
     int na = 0;
     const bool ss = A.integrator == 0;
-    const float t = free_flight(S, st, K, ls.o, ls.d, ls.target_tau, A.solver, ss, &na);
+    const float t = free_flight(S, st, K, ls.o, ls.d, ls.target_tau, A.solver, ss, &na, rng.state);
     if (A.record_bits) {  // integrator.h:616-644
         int x, y, si;
         lane_xy(A, ls.work, &x, &y, &si);

@@ -652,7 +652,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     st.U(U_GI, s) = gi;
                 }
                 int na = 0;
-                const float t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na);
+                const float t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state);
                 if (A.record_bits) {  // integrator.h:616-644
                     int x, y, si;
                     lane_xy(A, s1.z, &x, &y, &si);

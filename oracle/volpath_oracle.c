@@ -532,17 +532,16 @@ enum { VO_SOLVER_ANALYTIC_NEWTON = 0, VO_SOLVER_ANALYTIC_BISECTION = 1, VO_SOLVE
        VO_SOLVER_UNIFORM = 4 };
 /* distance_solvers.h:131-137: t = ta + u (tb - ta).  The reference draws u from a random_device-seeded mt19937
  * (rng.h:6-10), i.e. it is not reproducible: PARITY UNPINNED for this mode.  Here u is a counter-based value hashed from
- * the segment itself, so oracle and device agree bit for bit and the path's own PCG stream is left untouched. */
-static float solve_uniform(float ta, float tb, float remaining) {
-    uint32_t a, b, r;
-    memcpy(&a, &ta, 4); memcpy(&b, &tb, 4); memcpy(&r, &remaining, 4);
-    const uint64_t h = vo_splitmix64((((uint64_t)a << 32) | (uint64_t)b) ^ ((uint64_t)r * 0x9E3779B97F4A7C15ULL));
+ * the state of the path's PCG stream right after the target draw (an integer, identical on every implementation; one
+ * solve per draw), so oracle and device agree and the path's own stream is left untouched. */
+static float solve_uniform(float ta, float tb, uint64_t key) {
+    const uint64_t h = vo_splitmix64(key);
     const float u = (float)(uint32_t)(h >> 40) * (1.0f / 16777216.0f);
     return ta + u * (tb - ta);
 }
 static float solve_distance(const vo_gmm* m, const vo_ray* ray, float ta, float tb, const uint32_t* act, int na,
-                            float remaining, int solver) { /* distance_solvers.h:150-187 */
-    if (solver == VO_SOLVER_UNIFORM) return solve_uniform(ta, tb, remaining);
+                            float remaining, int solver, uint64_t key) { /* distance_solvers.h:150-187 */
+    if (solver == VO_SOLVER_UNIFORM) return solve_uniform(ta, tb, key);
     if ((solver == VO_SOLVER_ANALYTIC_NEWTON || solver == VO_SOLVER_ANALYTIC_BISECTION) && na == 1) {
         float t_an = 0.0f;
         if (gauss_solve_t(&m->g[act[0]], ray, ta, tb, remaining, &t_an)) return clampf(t_an, ta, tb);
@@ -689,7 +688,7 @@ static void pix_list_add(vo_scratch* s, uint32_t g) { /* linear-search dedupe, i
 }
 
 /* MultiScatterGaussians::get_free_flight_distance, integrator.h:422-498 */
-static float ms_free_flight(const vo_gmm* m, const vo_ray* ray, vo_scratch* s, float target_tau, int solver) {
+static float ms_free_flight(const vo_gmm* m, const vo_ray* ray, vo_scratch* s, float target_tau, int solver, uint64_t key) {
     int cur_epoch = ++s->epoch_counter;
     if (cur_epoch == 0) { memset(s->idx_epoch, 0, (size_t)m->n * sizeof(int)); cur_epoch = ++s->epoch_counter; }
     double acc_tau = 0.0;
@@ -700,7 +699,7 @@ static float ms_free_flight(const vo_gmm* m, const vo_ray* ray, vo_scratch* s, f
         for (int k = 0; k < s->na; ++k) seg_tau += (double)gauss_optical_depth(&m->g[s->active[k]], ray, t_prev, t_evt);
         if (acc_tau + seg_tau > (double)target_tau) {
             float remaining = (float)((double)target_tau - acc_tau);
-            return solve_distance(m, ray, t_prev, t_evt, s->active, s->na, remaining, solver);
+            return solve_distance(m, ray, t_prev, t_evt, s->active, s->na, remaining, solver, key);
         }
         acc_tau += seg_tau;
         uint32_t gidx = s->ev.e[ei].index;
@@ -776,7 +775,7 @@ static void ms_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
         if (s->ev.n == 0) { for (int c = 0; c < 3; ++c) Lacc[c] += thr[c] * L->env[c]; break; }
         float target_tau = -logf(1.0f - pcg_uniform(&rng));
         s->na = 0;
-        float t_scatter = ms_free_flight(m, &ray, s, target_tau, solver);
+        float t_scatter = ms_free_flight(m, &ray, s, target_tau, solver, rng.state);
         if (record) {
             const float tol = 1e-6f;
             if (t_scatter >= 0.0f) {
@@ -829,7 +828,7 @@ static void ss_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
         float seg_tau = 0.0f;
         for (int k = 0; k < s->na; ++k) seg_tau += gauss_optical_depth(&m->g[s->active[k]], &ray, t_prev, t_evt);
         if (acc_tau + seg_tau > target_tau) {
-            t_scatter = solve_distance(m, &ray, t_prev, t_evt, s->active, s->na, target_tau - acc_tau, solver);
+            t_scatter = solve_distance(m, &ray, t_prev, t_evt, s->active, s->na, target_tau - acc_tau, solver, rng.state);
             break;
         }
         acc_tau += seg_tau;
