@@ -287,9 +287,11 @@ __device__ __noinline__ float solve_newton(St& st, int na, float ta, float tb, f
     }
     return solve_bisection(st, na, ta, tb, target);
 }
-template <class St>
+// DEFER: the iterative solvers are not run here; *deferred is set instead and the caller redoes the whole walk later
+// among other deferred paths (wave_post_a_kernel<2>), where a warp's lanes iterate together
+template <bool DEFER, class St>
 __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, float ta, float tb, float remaining,
-                                int solver, uint64_t key) {  // :150-187
+                                int solver, uint64_t key, bool* deferred) {  // :150-187
     if (solver == 4) {  // UNIFORM (:131-137): t = ta + u (tb - ta); the reference's u comes from a random_device-seeded
                         // generator (parity unpinned), ours is hashed from the path's PCG state after the target draw,
                         // like the oracle's solve_uniform
@@ -303,6 +305,7 @@ __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, f
         float t_an;
         if (solve_t_given_tau(g, q, ta, tb, remaining, &t_an)) return clampf(t_an, ta, tb);
     }
+    if (DEFER) { *deferred = true; return ta; }
     if (solver == 0 || solver == 2) return solve_newton(st, na, ta, tb, remaining);
     return solve_bisection(st, na, ta, tb, remaining);
 }
@@ -370,9 +373,9 @@ __device__ __forceinline__ bool next_event(const SceneDev& S, St& st, int K, int
     return true;
 }
 
-template <class St>
+template <bool DEFER = false, class St>
 __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float target_tau, int solver, bool ss,
-                             int* na_out, uint64_t key) {
+                             int* na_out, uint64_t key, bool* deferred = nullptr) {
     sort_entries(S, st, K);
     double acc = 0.0;
     float accf = 0.0f;
@@ -411,7 +414,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
             for (int k = 0; k < na; ++k)  // restore erf(arg(t_prev)) for the solver
                 st.F(F_ACTF, k) = erff_ni(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
             *na_out = na;
-            return solve_distance(S, st, na, o, d, t_prev, t_evt, remaining, solver, key);
+            return solve_distance<DEFER>(S, st, na, o, d, t_prev, t_evt, remaining, solver, key, deferred);
         }
         if (take_enter) {
             const float F0 = erff_ni(erf_arg(hit_const(st, se), t_evt));

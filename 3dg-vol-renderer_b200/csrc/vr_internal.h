@@ -42,7 +42,7 @@ constexpr int kPostClasses = 5;
 enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, WC_NTL, WC_CURSOR_L,
        WC_NA /* kPostClasses counters */,
        kWaveCounters = 16 };
-static_assert(WC_NA + kPostClasses <= kWaveCounters, "wave counters overflow");
+static_assert(WC_NA + kPostClasses + 1 <= kWaveCounters, "wave counters overflow");
 struct WavePool {
     int P;
     // fields that are read together share a 32-byte sector: slots are visited in arbitrary order, so every

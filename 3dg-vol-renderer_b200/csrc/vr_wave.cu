@@ -32,7 +32,7 @@ namespace vr {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t wave_pool_bytes(int P) {
     const size_t p = (size_t)P;
-    return align256(p * 32) * 4 + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 4) * 5 + align256(p * 4 * kPostClasses) +
+    return align256(p * 32) * 4 + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 4) * 5 + align256(p * 4 * (kPostClasses + 1)) +
            align256(kWaveCounters * 4);
 }
 void wave_pool_carve(WavePool* q, int P, void* base) {
@@ -45,7 +45,7 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     q->hit_t0 = (float*)take(p * 4 * (kWaveCap - 2)); q->hit_t1 = (float*)take(p * 4 * (kWaveCap - 2));
     q->hit_gi = (uint32_t*)take(p * 4 * (kWaveCap - 2));
     q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4); q->listTl = (unsigned int*)take(p * 4);
-    q->listA = (unsigned int*)take(p * 4 * kPostClasses); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
+    q->listA = (unsigned int*)take(p * 4 * (kPostClasses + 1)); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
     q->cnt = (unsigned int*)take(kWaveCounters * 4);
 }
 
@@ -334,7 +334,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
     const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : (KIND == RAY_SHADOW ? Q.listTh : Q.listTl);
     unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : (KIND == RAY_SHADOW ? WC_CURSOR_H : WC_CURSOR_L)];
     // the list consumed by the previous kernel of the chain (regen -> travS -> postA -> travH -> postB) is free again
-    if (blockIdx.x == 0 && threadIdx.x < kPostClasses) {
+    if (blockIdx.x == 0 && threadIdx.x < kPostClasses + 1) {
         if (KIND == RAY_SCATTER) { if (threadIdx.x == 0) Q.cnt[WC_NC] = 0; }
         else if (KIND == RAY_SHADOW) Q.cnt[WC_NA + threadIdx.x] = 0;
     }
@@ -511,13 +511,16 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
 }
 
 // wave_post_a: integrator.h:593-678.  Slots arrive binned by overlap count (post_class).
-//   wave_post_a_kernel<true>   class 0 only (one overlap, the commonest case in sparse mixtures): a register-only
+//   wave_post_a_kernel<1>      class 0 only (one overlap, the commonest case in sparse mixtures): a register-only
 //       path that performs the same operations in the same order as the general walk does for K = 1.  Small code,
 //       so the warps of the launch share the instruction caches (profiles/r01_v5: the one-kernel version spent 40 %
 //       of its stall samples waiting for instructions).  A slot whose analytic inverse declines is handed to
 //       class 1 untouched.
-//   wave_post_a_kernel<false>  classes 1..4 (+ hand-overs): every class starts at a multiple of 32 in the flattened
-//       index space, so a warp only ever holds slots of one class.
+//   wave_post_a_kernel<0>      classes 1..4 (+ hand-overs): every class starts at a multiple of 32 in the flattened
+//       index space, so a warp only ever holds slots of one class.  A slot whose walk ends in an ITERATIVE solve
+//       (Newton / bisection, distance_solvers.h:15-129: ~3 % of the slots, but 40 % of this kernel's warp instructions
+//       at 2-5 active lanes when solved in place, profiles/r01_v8) is left untouched and listed in class kPostClasses.
+//   wave_post_a_kernel<2>      the deferred slots: the same walk again, now in warps whose lanes all iterate.
 // environment / next-event part shared by both (integrator.h:652-678)
 __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool& Q, unsigned int p, float4 s0, uint4 s1, f3 o, f3 d,
                                              float target_tau, float t, float albedo, Pcg& rng, WaveCounters& cn) {
@@ -557,23 +560,25 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
     return (light >= 0 && light < 32 && ((S.lg_mask >> light) & 1u)) ? DEST_TRAV_LIGHT : DEST_TRAV;
 }
 
-template <bool FAST>
+template <int MODE>   // 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots
 __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
-    constexpr int kFirst = FAST ? 0 : 1, kLast = FAST ? 1 : kPostClasses;   // classes [kFirst, kLast)
-    unsigned int nA[kPostClasses], base[kPostClasses + 1];
+    constexpr bool FAST = MODE == 1;
+    constexpr int kFirst = MODE == 1 ? 0 : (MODE == 0 ? 1 : kPostClasses);              // classes [kFirst, kLast)
+    constexpr int kLast = MODE == 1 ? 1 : (MODE == 0 ? kPostClasses : kPostClasses + 1);
+    unsigned int nA[kPostClasses + 1], base[kPostClasses + 2];
     base[kFirst] = 0;
 #pragma unroll
     for (int c = kFirst; c < kLast; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
     const unsigned int total = base[kLast];
-    if (!FAST && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
+    if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (total + stride - 1) / stride;
     for (unsigned int r = 0; r < rounds; ++r) {
         const unsigned int i = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
         int dest = DEST_NONE;
-        bool hand_over = false;
+        bool hand_over = false, deferred = false;
         unsigned int p = 0;
         int cls = kFirst;
 #pragma unroll
@@ -652,7 +657,10 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     st.U(U_GI, s) = gi;
                 }
                 int na = 0;
-                const float t = free_flight(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state);
+                const float t = free_flight<MODE == 0>(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state, &deferred);
+                if (deferred) {
+                    cn.hits -= (unsigned int)K;   // counted when the slot is redone
+                } else {
                 if (A.record_bits) {  // integrator.h:616-644
                     int x, y, si;
                     lane_xy(A, s1.z, &x, &y, &si);
@@ -667,9 +675,11 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 }
                 const float albedo = t >= 0.0f ? evaluate_albedo(S, st, na, add3(o, scale3(t, d))) : 0.0f;
                 dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
+                }
             }
         }
         if (FAST) wave_append(Q.listA + (size_t)1 * Q.P, &Q.cnt[WC_NA + 1], hand_over, p);
+        if (MODE == 0) wave_append(Q.listA + (size_t)kPostClasses * Q.P, &Q.cnt[WC_NA + kPostClasses], deferred, p);
         wave_append(Q.listTh, &Q.cnt[WC_NTH], dest == DEST_TRAV, p);
         wave_append(Q.listTl, &Q.cnt[WC_NTL], dest == DEST_TRAV_LIGHT, p);
         wave_append(Q.listC, &Q.cnt[WC_NC], dest == DEST_REGEN, p);
@@ -817,7 +827,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     const int kBatch = 8;
     cudaEvent_t pe[7];
     double ptm[5] = {0, 0, 0, 0, 0}, pt_light = 0;
-    unsigned long long cls_total[kPostClasses] = {0, 0, 0, 0, 0};
+    unsigned long long cls_total[kPostClasses + 1] = {0, 0, 0, 0, 0, 0};
     if (prof) for (auto& e : pe) cudaEventCreate(&e);
     bool failed = false;
     while (!failed) {
@@ -834,14 +844,15 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
                 if (prof) cudaEventRecord(pe[1], st);
                 wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
                 if (prof) cudaEventRecord(pe[2], st);
-                wave_post_a_kernel<true><<<pt.grid_post, 128, 0, st>>>(a, q);
-                wave_post_a_kernel<false><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<1><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
                 if (prof) {
                     cudaEventRecord(pe[3], st);
                     unsigned int hc[kWaveCounters];
                     cudaMemcpyAsync(hc, q.cnt, sizeof(hc), cudaMemcpyDeviceToHost, st);
                     cudaStreamSynchronize(st);
-                    for (int c = 0; c < kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
+                    for (int c = 0; c <= kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
                 }
                 wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
                 if (prof) cudaEventRecord(pe[6], st);
@@ -854,7 +865,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
                     for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); ptm[k] += ms; }
                     { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
                 }
-                *launches += 6;
+                *launches += 7;
             }
             ++iters;
         }
@@ -884,8 +895,8 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         fprintf(stderr, "[wave] samples %u iters %d  regen %.3f  trav_scatter %.3f  post_a %.3f  trav_shadow %.3f  post_b %.3f ms\n",
                 a_all.work_count, iters, ptm[0], ptm[1], ptm[2], ptm[3], ptm[4]);
         fprintf(stderr, "[wave] of trav_shadow: %.3f ms in the light-grid kernel\n", pt_light);
-        fprintf(stderr, "[wave] post-A slots by overlap count: K=1 %llu  K=2 %llu  K=3..4 %llu  K=5..8 %llu  K>8 %llu\n", cls_total[0], cls_total[1],
-                cls_total[2], cls_total[3], cls_total[4]);
+        fprintf(stderr, "[wave] post-A slots by overlap count: K=1 %llu  K=2 %llu  K=3..4 %llu  K=5..8 %llu  K>8 %llu  deferred (iterative solve) %llu\n", cls_total[0], cls_total[1],
+                cls_total[2], cls_total[3], cls_total[4], cls_total[5]);
         for (auto& e : pe) cudaEventDestroy(e);
     }
     return failed ? -1 : iters;
