@@ -9,6 +9,7 @@ using namespace vr;
 
 namespace vr {
 int render_spheres_impl(vr_context* ctx, const vr_render_params* p, vr_render_stats* st);  // vr_spheres.cu
+int render_march_impl(vr_context* ctx, const vr_render_params* p, vr_render_stats* st);    // vr_march.cu
 
 static int owned_rows(const vr_render_params* p) {
     const int rows = p->y1 - p->y0;
@@ -35,6 +36,8 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     if (st) memset(st, 0, sizeof(*st));
     VR_CUDA(cudaSetDevice(ctx->device));
     if (p->integrator == VR_INTEGRATOR_MARCH_SPHERES) return render_spheres_impl(ctx, p, st);
+    if (p->integrator == VR_INTEGRATOR_TEST || p->integrator == VR_INTEGRATOR_PURE_MARCH || p->integrator == VR_INTEGRATOR_MARCH_GAUSSIANS)
+        return render_march_impl(ctx, p, st);
     if (p->integrator != VR_INTEGRATOR_FREE_FLIGHT_SS && p->integrator != VR_INTEGRATOR_MULTI_SCATTER)
         return fail(ctx, VR_ERR_INVALID_ARGUMENT, "render: unknown integrator");
     if (!ctx->has_gmm) return fail(ctx, VR_ERR_NO_SCENE, "render: no Gaussian mixture set (vr_set_gmm)");

@@ -66,7 +66,7 @@ inline void for_each_device(Session& S, F fn) {
 
 // One Integrator::render over Gaussians: kind = VR_INTEGRATOR_FREE_FLIGHT_SS / VR_INTEGRATOR_MULTI_SCATTER.
 inline RenderTotals render_gaussians(int kind, int solver, const Scene& scene, const Camera& camera, Image& image, int spp, int min_bounces,
-                                     std::vector<std::vector<uint32_t>>* per_pixel_gaussians) {
+                                     std::vector<std::vector<uint32_t>>* per_pixel_gaussians, float march_step = 0.01f, int env_samples = 5) {
     if (scene.volume_type != Scene::VolumeType::GAUSSIANS) throw std::runtime_error("Trying to intersect with uninitialized medium");
     static const GaussianMixtureModel empty_model;
     const GaussianMixtureModel& model = scene.gmm && !scene.gmm->empty() ? scene.gmm->at(0) : empty_model;
@@ -84,7 +84,7 @@ inline RenderTotals render_gaussians(int kind, int solver, const Scene& scene, c
         p.integrator = kind; p.solver = solver; p.width = W; p.height = H; p.spp = spp; p.min_bounces = min_bounces;
         p.x0 = 0; p.y0 = 0; p.x1 = W; p.y1 = H; p.part_rank = i; p.part_count = nd;
         p.record = per_pixel_gaussians ? 1 : 0;
-        p.march_step = 0.01f; p.env_samples = 5;
+        p.march_step = march_step; p.env_samples = env_samples;
         S.check(i, vr_render(S.ctx(i), &p, image.data(), &stats[(size_t)i]));
     });
     if (per_pixel_gaussians) {  // integrator.h:540-545,709-714: one de-duplicated index list per pixel

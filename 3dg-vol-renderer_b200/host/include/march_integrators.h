@@ -5,7 +5,7 @@
 // RayMarchingSpheres runs on the device (vr_set_smm + VR_INTEGRATOR_MARCH_SPHERES).  The reference
 // seeds its environment directions from std::random_device; the device marcher uses
 // the PCG stream seeded per (x, y, step, sample) instead, so images agree statistically, not bit-wise.
-// The other three are not on the device yet: their render() throws.
+// The other three run on the device for Gaussian scenes (vr_march.cu, same substitution for the environment directions).
 #pragma once
 
 class RayMarchingSpheres : public Integrator {
@@ -43,10 +43,13 @@ public:
     }
 };
 
+// The three validation integrators over a Gaussian scene run on the device (vr_march.cu): one ray per pixel through
+// the pixel centre, fixed-step march.  Sphere scenes are served by RayMarchingSpheres only.
 namespace vrhost {
-[[noreturn]] inline void not_on_device(const char* what) {
-    throw std::runtime_error(std::string(what) + ": not implemented on the device (the hot path is FreeFlightGaussians / MultiScatterGaussians / "
-                             "RayMarchingSpheres); there is no CPU fallback");
+inline void render_validation(int kind, const char* what, const Scene& scene, const Camera& camera, Image& image, float step, int env_samples) {
+    if (scene.volume_type != Scene::VolumeType::GAUSSIANS)
+        throw std::runtime_error(std::string(what) + ": only Gaussian scenes run on the device (use RayMarchingSpheres for spheres); there is no CPU fallback");
+    render_gaussians(kind, VR_SOLVER_ANALYTIC_PLUS_NEWTON, scene, camera, image, 1, 0, nullptr, step, env_samples);
 }
 }  // namespace vrhost
 
@@ -56,7 +59,9 @@ class RayMarchingGaussians : public Integrator {
 public:
     RayMarchingGaussians(const std::shared_ptr<Camera>& cam, float step_size_in = 0.01f, int env_samples_in = 20)
         : Integrator(cam), step_size(step_size_in), env_samples(env_samples_in) {}
-    void render(const Scene&, Image&) override { (void)step_size; (void)env_samples; vrhost::not_on_device("RayMarchingGaussians"); }
+    void render(const Scene& scene, Image& image) override {
+        vrhost::render_validation(VR_INTEGRATOR_MARCH_GAUSSIANS, "RayMarchingGaussians", scene, *camera, image, step_size, env_samples);
+    }
 };
 
 class PureRayMarching : public Integrator {
@@ -65,11 +70,15 @@ class PureRayMarching : public Integrator {
 public:
     PureRayMarching(const std::shared_ptr<Camera>& cam, float step_size_in = 0.01f, int env_samples_in = 20)
         : Integrator(cam), step_size(step_size_in), env_samples(env_samples_in) {}
-    void render(const Scene&, Image&) override { (void)step_size; (void)env_samples; vrhost::not_on_device("PureRayMarching"); }
+    void render(const Scene& scene, Image& image) override {
+        vrhost::render_validation(VR_INTEGRATOR_PURE_MARCH, "PureRayMarching", scene, *camera, image, step_size, env_samples);
+    }
 };
 
 class TestIntegrator : public Integrator {
 public:
     TestIntegrator(const std::shared_ptr<Camera>& cam) : Integrator(cam) {}
-    void render(const Scene&, Image&) override { vrhost::not_on_device("TestIntegrator"); }
+    void render(const Scene& scene, Image& image) override {
+        vrhost::render_validation(VR_INTEGRATOR_TEST, "TestIntegrator", scene, *camera, image, 0.01f, 1);
+    }
 };

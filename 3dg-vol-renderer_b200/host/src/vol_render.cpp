@@ -4,7 +4,7 @@
 // count are compile-time edits, by runtime flags; output is the same 8-bit PPM (Image::make_PPM)
 // and, optionally, the raw float image and the recorded per-pixel Gaussian lists.
 //
-//   vol_render --scene S.txt [--type gmm|smm|xml] [--integrator ms|ss|spheres] [--solver 0..3]
+//   vol_render --scene S.txt [--type gmm|smm|xml] [--integrator ms|ss|spheres|march|pure|test] [--solver 0..4]
 //              [--spp 256] [--min-bounces 5] [--width 512 --height 512]
 //              [--camera pinhole|ortho] [--pos 0,1,6] [--look 0,1,0] [--fov 0.785398]
 //              [--step 0.01 --env-samples 5] [--out output.ppm] [--raw image.f32] [--record lists.u32]
@@ -145,6 +145,15 @@ int main(int argc, char** argv) {
                 MultiScatterGaussians ms(camera, spp, a.i("min-bounces", 5));
                 ms.set_solver(solver);
                 if (record) ms.render(scene, image, &lists); else ms.render(scene, image);
+            } else if (integ == "march") {
+                RayMarchingGaussians rm(camera, a.f("step", 0.01f), a.i("env-samples", 20));
+                rm.render(scene, image);
+            } else if (integ == "pure") {
+                PureRayMarching pm(camera, a.f("step", 0.01f), a.i("env-samples", 20));
+                pm.render(scene, image);
+            } else if (integ == "test") {
+                TestIntegrator ti(camera);
+                ti.render(scene, image);
             } else {
                 throw std::runtime_error("unknown integrator '" + integ + "'");
             }
@@ -152,7 +161,7 @@ int main(int argc, char** argv) {
             best = std::min(best, el.count());
             std::printf("Render time: %.6f seconds\n", el.count());
         }
-        const double samples = double(W) * H * (integ == "spheres" ? 1 : spp);
+        const double samples = double(W) * H * (integ == "ss" || integ == "ms" ? spp : 1);
         std::printf("best %.6f s, %.3f Msamples/s\n", best, samples / best * 1e-6);
         image.make_PPM(a.str("out", "output.ppm"));
         if (a.has("raw")) image.write_raw(a.str("raw", ""));

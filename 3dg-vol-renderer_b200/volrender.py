@@ -18,6 +18,7 @@ LIB_PATH = os.environ.get("VR_LIB") or os.path.join(HERE, "libvolrender_b200.so"
 CSRC = os.path.join(HERE, "csrc")
 
 INTEGRATOR_SS, INTEGRATOR_MS, INTEGRATOR_MARCH_SPHERES = 0, 1, 2
+INTEGRATOR_TEST, INTEGRATOR_PURE_MARCH, INTEGRATOR_MARCH_GAUSSIANS = 3, 4, 5
 SOLVER_ANALYTIC_NEWTON, SOLVER_ANALYTIC_BISECTION, SOLVER_NEWTON, SOLVER_BISECTION, SOLVER_UNIFORM = 0, 1, 2, 3, 4
 CAMERA_PINHOLE, CAMERA_ORTHO = 0, 1
 

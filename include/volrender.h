@@ -40,7 +40,11 @@ typedef enum vr_status {
 typedef enum vr_integrator {
     VR_INTEGRATOR_FREE_FLIGHT_SS = 0,  /* FreeFlightGaussians::render      integrator.h:300-408 */
     VR_INTEGRATOR_MULTI_SCATTER = 1,   /* MultiScatterGaussians::render    integrator.h:524-717 */
-    VR_INTEGRATOR_MARCH_SPHERES = 2    /* RayMarchingSpheres::render       test_integrators.h:23-135 */
+    VR_INTEGRATOR_MARCH_SPHERES = 2,   /* RayMarchingSpheres::render       test_integrators.h:23-135 */
+    /* validation integrators over the Gaussian mixture: one ray per pixel, march_step / env_samples as below */
+    VR_INTEGRATOR_TEST = 3,            /* TestIntegrator::render           integrator.h:65-94 */
+    VR_INTEGRATOR_PURE_MARCH = 4,      /* PureRayMarching::render          integrator.h:100-267 */
+    VR_INTEGRATOR_MARCH_GAUSSIANS = 5  /* RayMarchingGaussians::render     test_integrators.h:143-297 */
 } vr_integrator;
 
 /* runtime form of the #define selector distance_solvers.h:143-147 */
@@ -66,8 +70,8 @@ typedef struct vr_render_params {
     /* row partition for multi-GPU: this context renders rows y with (y - y0) % part_count == part_rank */
     int32_t part_rank, part_count;
     int32_t record;        /* != 0: keep per-pixel contributing-Gaussian sets (integrator.h:616-644) */
-    float march_step;      /* RayMarchingSpheres step_size (0.01) */
-    int32_t env_samples;   /* RayMarchingSpheres env_samples (5) */
+    float march_step;      /* marchers: step_size (0.01) */
+    int32_t env_samples;   /* marchers: env_samples (RayMarchingSpheres 5, the Gaussian marchers 20) */
     int32_t reserved[4];
 } vr_render_params;
 

@@ -195,6 +195,24 @@ def render_spheres(smm: dict, env, cam, W, H, step=0.01, env_samples=5):
     return out
 
 
+MARCH_TEST, MARCH_PURE, MARCH_GAUSS = 0, 1, 2
+
+
+def render_march(gmm: Gmm, lights, env, cam, W, H, mode, step=0.01, env_samples=20):
+    """TestIntegrator / PureRayMarching / RayMarchingGaussians restated (vo_render_march)."""
+    lights = _c(lights).reshape(-1, 6)
+    lpos = _c(lights[:, 0:3]); lint = _c(lights[:, 3:6])
+    if lpos.size == 0:
+        lpos = np.zeros(3, np.float32); lint = np.zeros(3, np.float32)
+    out = np.zeros((H, W, 3), np.float32)
+    f = lib().vo_render_march
+    f.restype = None
+    f(C.c_void_p(gmm.h) if not isinstance(gmm.h, C.c_void_p) else gmm.h, C.c_int(lights.shape[0]), lpos.ctypes.data_as(C.c_void_p),
+      lint.ctypes.data_as(C.c_void_p), _c(env).ctypes.data_as(C.c_void_p), C.byref(cam), C.c_int(W), C.c_int(H), C.c_int(mode),
+      C.c_float(step), C.c_int(env_samples), out.ctypes.data_as(C.c_void_p))
+    return out
+
+
 # ------------------------------------------------------------------------------------------
 # the compiled reference (oracle/_ref/ref_driver)
 # ------------------------------------------------------------------------------------------

@@ -16,6 +16,7 @@
 //            pos=x,y,z look=x,y,z fov=rad out=img.f32 [record=lists.bin] [repeat=K]
 //   kat      scene=F n=N seed=S out=kat.bin       known-answer vectors
 //   sfd      scene=F target=img.f32 signs=signs.i8 S=s iters=k w= h= spp= ... out=prefix
+//   march    scene=F integrator=test|march_pure|march_gauss w= h= step= env= envcolor=r,g,b cam... out=img.f32
 //   spheres  scene=F w= h= step= env= cam... out=img.f32   (RayMarchingSpheres; env part is
 //            random_device-seeded in the reference -> statistical use only)
 #include "integrator.h"
@@ -399,8 +400,31 @@ static int cmd_spheres(const Args& a) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------
+// validation integrators over a Gaussian scene: integrator=test|march_pure|march_gauss, envcolor=r,g,b overrides
+// Scene::env_color (0,0,0 makes the random_device-seeded environment term vanish, so the image is deterministic)
+static int cmd_march(const Args& a) {
+    Scene scene = Scene::load_GMM(get(a, "scene"));
+    if (!get(a, "envcolor").empty()) scene.env_color = vec3(get(a, "envcolor"));
+    int W = std::stoi(get(a, "w", "16")), H = std::stoi(get(a, "h", "16"));
+    auto cam = make_camera(a);
+    Image image(W, H);
+    std::string integ = get(a, "integrator", "march_gauss");
+    float step = std::stof(get(a, "step", "0.01"));
+    int env = std::stoi(get(a, "env", "20"));
+    auto t0 = std::chrono::high_resolution_clock::now();
+    if (integ == "test") { TestIntegrator ti(cam); ti.render(scene, image); }
+    else if (integ == "march_pure") { PureRayMarching pm(cam, step, env); pm.render(scene, image); }
+    else { RayMarchingGaussians rm(cam, step, env); rm.render(scene, image); }
+    auto t1 = std::chrono::high_resolution_clock::now();
+    dump_image(image, get(a, "out"));
+    printf("{\"cmd\": \"march\", \"integrator\": \"%s\", \"w\": %d, \"h\": %d, \"time_s\": %.6f, \"threads\": %d}\n", integ.c_str(), W, H,
+           std::chrono::duration<double>(t1 - t0).count(), omp_get_max_threads());
+    return 0;
+}
+
 int main(int argc, char** argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|kat|sfd|pack|spheres key=value...\n"); return 1; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|kat|sfd|pack|spheres|march key=value...\n"); return 1; }
     Args a = parse_args(argc, argv, 2);
     std::string c(argv[1]);
     // the reference prints banners on stdout; keep our JSON line last.
@@ -410,6 +434,7 @@ int main(int argc, char** argv) {
         if (c == "sfd") return cmd_sfd(a);
         if (c == "pack") return cmd_pack(a);
         if (c == "spheres") return cmd_spheres(a);
+        if (c == "march") return cmd_march(a);
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());
         return 2;

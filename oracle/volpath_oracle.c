@@ -1131,3 +1131,148 @@ VO_EXPORT void vo_render_spheres(int n, const float* center, const float* radius
         free(ev.e); free(sev.e); free(active); free(act2);
     }
 }
+
+/* ------------------------------------------------------------------------- */
+/* Validation integrators over Gaussians               */
+/*   TestIntegrator        integrator.h:65-94                                */
+/*   PureRayMarching       integrator.h:100-267                              */
+/*   RayMarchingGaussians  test_integrators.h:143-297                        */
+/* The reference draws the environment directions from a random_device-seeded */
+/* generator (sample_uniform_direction_old, rng.h:6-10): PARITY UNPINNED for  */
+/* that term.  Here, as in vo_render_spheres, they come from the PCG stream   */
+/* seeded with (x, y, step index), sequence 2.                                */
+/* ------------------------------------------------------------------------- */
+static void evaluate_sigma_mask(const vo_gmm* m, const unsigned char* active, v3 pos, float* sigma_a, float* sigma_s) { /* gmm.h:98-126 */
+    float sum = 0.0f, sum_alb = 0.0f;
+    for (int i = 0; i < m->n; ++i) {
+        if (!active[i]) continue;
+        float mu = gauss_mu_t(&m->g[i], pos);
+        sum += mu;
+        sum_alb += mu * m->g[i].albedo;
+    }
+    if (sum <= 0.0f) { *sigma_s = *sigma_a = 0.0f; return; }
+    float a_mix = sum_alb / sum;
+    *sigma_s = a_mix * sum;
+    *sigma_a = (1.0f - a_mix) * sum;
+}
+static float transmittance_over_segment_mask(const vo_gmm* m, const vo_ray* ray, float t0, float t1, const unsigned char* mask) { /* gmm.h:146-157 */
+    float sum = 0.0f;
+    for (int i = 0; i < m->n; ++i) if (mask[i]) sum += gauss_optical_depth(&m->g[i], ray, t0, t1);
+    return expf(-sum);
+}
+/* events of `ray` with {0, entering, i} put in front for every active i (integrator.h:200-208, test_integrators.h:204-207) */
+static void shadow_events(const vo_gmm* m, const vo_ray* ray, const unsigned char* active, vo_events* ev, vo_events* tmp, vo_stack* st) {
+    gmm_intersect_events(m, ray, tmp, st);
+    ev->n = 0;
+    for (int i = m->n - 1; i >= 0; --i) if (active[i]) events_push(ev, 0.0f, 1, (uint32_t)i); /* repeated insert at begin() reverses */
+    for (int k = 0; k < tmp->n; ++k) events_push(ev, tmp->e[k].t, tmp->e[k].entering, tmp->e[k].index);
+}
+/* PureRayMarching::march_transmittance, integrator.h:105-135 */
+static float march_transmittance(const vo_gmm* m, const vo_ray* ray, float t_max, const vo_events* ev, const unsigned char* active0,
+                                 float step, unsigned char* act) {
+    memcpy(act, active0, (size_t)m->n);
+    float T = 1.0f;
+    int k = 0;
+    for (float t = 0.0f; t < t_max; t += step) {
+        while (k < ev->n && ev->e[k].t <= t) { act[ev->e[k].index] = (unsigned char)ev->e[k].entering; ++k; }
+        v3 pos = v3_add(ray->o, v3_scale(t, ray->d));
+        float sa, ss;
+        evaluate_sigma_mask(m, act, pos, &sa, &ss);
+        T *= expf(-(sa + ss) * step);
+    }
+    return T;
+}
+/* mode 0 TestIntegrator, 1 PureRayMarching, 2 RayMarchingGaussians */
+VO_EXPORT void vo_render_march(const vo_gmm* m, int nl, const float* lpos, const float* lint, const float* env, const vo_camera* cam,
+                               int W, int H, int mode, float step_size, int env_samples, float* out_rgb) {
+    const int n = m->n;
+#pragma omp parallel
+    {
+        vo_events ev = {0, 0, 0}, sev = {0, 0, 0}, tmp = {0, 0, 0};
+        vo_stack st = {0, 0};
+        unsigned char* active = (unsigned char*)calloc((size_t)(n > 0 ? n : 1), 1);
+        unsigned char* mask = (unsigned char*)calloc((size_t)(n > 0 ? n : 1), 1);
+#pragma omp for collapse(2) schedule(dynamic, 1)
+        for (int y = 0; y < H; ++y) {
+            for (int x = 0; x < W; ++x) {
+                float u = ((float)x + 0.5f) / (float)W, v = ((float)y + 0.5f) / (float)H;
+                vo_ray ray = camera_sample_ray(cam, u, v);
+                float* dst = out_rgb + 3 * ((size_t)y * W + x);
+                gmm_intersect_events(m, &ray, &ev, &st);
+                if (mode == 0) { /* magenta where the primary ray overlaps anything */
+                    dst[0] = ev.n ? 1.0f : env[0]; dst[1] = ev.n ? 0.0f : env[1]; dst[2] = ev.n ? 1.0f : env[2];
+                    continue;
+                }
+                if (ev.n == 0) { for (int c = 0; c < 3; ++c) dst[c] = env[c]; continue; }
+                const float t_end = ev.e[ev.n - 1].t;
+                memset(active, 0, (size_t)n);
+                if (mode == 1) for (int k = 0; k < ev.n; ++k) if (ev.e[k].t == 0.0f && ev.e[k].entering) active[ev.e[k].index] = 1;
+                int cur = 0, stepi = 0;
+                float T = 1.0f, L[3] = {0, 0, 0};
+                const float four_pi = (float)(4.0f * VO_PI), inv4pi = (float)(1.0f / (4.0f * VO_PI));
+                for (float t = 0.0f; t < t_end; t += step_size, ++stepi) {
+                    while (cur < ev.n && ev.e[cur].t <= t) { active[ev.e[cur].index] = (unsigned char)ev.e[cur].entering; ++cur; }
+                    v3 pos = v3_add(ray.o, v3_scale(t, ray.d));
+                    float sa, ss;
+                    evaluate_sigma_mask(m, active, pos, &sa, &ss);
+                    if (ss > 0.0f) {
+                        float Li[3] = {0, 0, 0}, Le[3] = {0, 0, 0};
+                        for (int l = 0; l < nl; ++l) {
+                            v3 to = v3_sub(v3_make(lpos[3 * l], lpos[3 * l + 1], lpos[3 * l + 2]), pos);
+                            v3 wi = v3_normalized(to);
+                            float dist = sqrtf(v3_sqnorm(to));
+                            vo_ray sh = ray_make(pos, wi);
+                            shadow_events(m, &sh, active, &sev, &tmp, &st);
+                            float Tr = 1.0f;
+                            if (mode == 1) {
+                                Tr = march_transmittance(m, &sh, dist, &sev, active, step_size, mask);
+                            } else { /* test_integrators.h:209-231: no clipping of the last segment to dist */
+                                memcpy(mask, active, (size_t)n);
+                                float t_prev = 0.0f;
+                                int k = 0;
+                                while (t_prev < dist) {
+                                    float t_next = k < sev.n ? sev.e[k].t : dist;
+                                    Tr *= transmittance_over_segment_mask(m, &sh, t_prev, t_next, mask);
+                                    if (k < sev.n) { mask[sev.e[k].index] = (unsigned char)sev.e[k].entering; ++k; }
+                                    t_prev = t_next;
+                                }
+                            }
+                            for (int c = 0; c < 3; ++c) Li[c] += (Tr * lint[3 * l + c]) / (dist * dist);
+                        }
+                        vo_pcg rng;
+                        pcg_seed(&rng, vo_derive_path_seed(x, y, stepi), 2);
+                        for (int e = 0; e < env_samples; ++e) {
+                            v3 wi = sample_uniform_direction(&rng);
+                            vo_ray sh = ray_make(pos, wi);
+                            shadow_events(m, &sh, active, &sev, &tmp, &st);
+                            float Tr = 1.0f;
+                            if (mode == 1) {
+                                float t_env_end = sev.n ? sev.e[sev.n - 1].t : 0.0f;
+                                Tr = march_transmittance(m, &sh, t_env_end, &sev, active, step_size, mask);
+                            } else { /* test_integrators.h:247-263 */
+                                memcpy(mask, active, (size_t)n);
+                                float t_prev = 0.0f;
+                                for (int k = 0; k < sev.n; ++k) {
+                                    float t_next = sev.e[k].t;
+                                    Tr *= transmittance_over_segment_mask(m, &sh, t_prev, t_next, mask);
+                                    mask[sev.e[k].index] = (unsigned char)sev.e[k].entering;
+                                    t_prev = t_next;
+                                }
+                            }
+                            for (int c = 0; c < 3; ++c) Le[c] += Tr * env[c];
+                        }
+                        for (int c = 0; c < 3; ++c) {
+                            Le[c] /= (float)env_samples;
+                            Le[c] *= four_pi;
+                            L[c] += (((T * ss) * (Li[c] + Le[c])) * step_size) * inv4pi;
+                        }
+                    }
+                    if (mode == 1) T *= expf(-(sa + ss) * step_size);
+                    else T *= transmittance_over_segment_mask(m, &ray, t, t + step_size, active);
+                }
+                for (int c = 0; c < 3; ++c) dst[c] = L[c] + T * env[c];
+            }
+        }
+        free(ev.e); free(sev.e); free(tmp.e); free(st.s); free(active); free(mask);
+    }
+}

@@ -39,6 +39,12 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def golden_march():
+    """reference images of the validation integrators (oracle/make_golden_march.py)"""
+    return np.load(os.path.join(GOLD, "golden_march_v1.npz"))
+
+
+@pytest.fixture(scope="session")
 def scenegen():
     return load_pkg_module("scenegen")
 

@@ -447,3 +447,35 @@ def test_spheres_vs_oracle(ctx, ob, vr, golden, scenegen, name):
     assert frac_within(img, ref, 1e-4) >= 0.99
     gold = golden[f"spheres/{name}/ortho"]
     assert abs(float(img.mean()) - float(gold.mean())) < 0.01 * float(gold.mean())
+
+
+@pytest.mark.parametrize("sc", ["two_gauss", "rand50", "rand300"])
+@pytest.mark.parametrize("integ,mode", [("test", 3), ("march_pure", 4), ("march_gauss", 5)])
+def test_validation_integrators(ctx, ob, vr, scenegen, golden_march, sc, integ, mode):
+    """TestIntegrator / PureRayMarching / RayMarchingGaussians on the device.
+    Black environment: against the REFERENCE's images (deterministic there), 1e-4 relative on >= 98 % of the pixels.
+    Sky colour: against the oracle, which draws the same environment directions (PCG per pixel and step)."""
+    wh, step, env_samples = golden_march[f"meta/{sc}"]
+    wh, env_samples = int(wh), int(env_samples)
+    scene, oc = setup(ctx, ob, vr, scenegen, sc, "pin")
+    ctx.set_lights(scene["lights"], (0.0, 0.0, 0.0))
+    p = vr.Context.params(mode, wh, wh, 1, march_step=float(step), env_samples=env_samples)
+    img, st = ctx.render(p)
+    ref = golden_march[f"env0/{sc}/{integ}"]
+    if integ == "test":
+        assert np.array_equal(img, ref)
+    else:
+        assert frac_within(img, ref, 1e-4, atol=1e-7) >= 0.98
+    ctx.set_lights(scene["lights"], ENV)
+    img, st = ctx.render(p)
+    orc = ob.render_march(ob.Gmm(scene), scene["lights"], ENV, oc, wh, wh, mode - 3, float(step), env_samples)
+    if integ == "test":
+        assert np.array_equal(img, orc)
+    else:
+        assert frac_within(img, orc, 1e-4) >= 0.98
+        assert st["kernel_launches"] == 1
+    # row partition: the two halves of an interleaved split reproduce the whole image
+    parts = np.zeros_like(img)
+    for r in range(2):
+        ctx.render(vr.Context.params(mode, wh, wh, 1, march_step=float(step), env_samples=env_samples, part=(r, 2)), out=parts)
+    assert np.array_equal(parts, img)
