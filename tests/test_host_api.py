@@ -177,3 +177,18 @@ def test_inverse_checkpoint_resume_is_bit_exact(host_bins, tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     a = np.fromfile(tmp_path / "a.f32", np.float32); c = np.fromfile(tmp_path / "c.f32", np.float32)
     assert a.size == 550 and np.array_equal(a, c)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("integ,key", [("test", "test"), ("pure", "march_pure"), ("march", "march_gauss")])
+def test_vol_render_validation_integrators(host_bins, golden_march, tmp_path, integ, key):
+    """TestIntegrator / PureRayMarching / RayMarchingGaussians classes of the drop-in API against the reference's images
+    (black environment: the reference's random_device-seeded term vanishes, per-pixel comparison)."""
+    wh, step, env_samples = golden_march["meta/rand50"]
+    raw = tmp_path / "img.f32"
+    r = run([os.path.join(host_bins, "vol_render"), "--scene", os.path.join(SCENES, "rand50.txt"), "--integrator", integ,
+             "--width", str(int(wh)), "--height", str(int(wh)), "--step", repr(float(step)), "--env-samples", str(int(env_samples)),
+             "--env", "0,0,0", "--raw", str(raw), "--out", str(tmp_path / "o.ppm")] + _cam_args("pin"))
+    assert r.returncode == 0, r.stdout + r.stderr
+    img = np.fromfile(raw, np.float32).reshape(int(wh), int(wh), 3)
+    assert frac_within(img, golden_march[f"env0/rand50/{key}"], 1e-4, atol=1e-7) >= 0.98
