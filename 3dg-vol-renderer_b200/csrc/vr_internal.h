@@ -40,9 +40,10 @@ constexpr int kWaveCap = 16;         // free-flight overlaps kept per path slot 
 // length: class 0: K = 1, 1: K = 2, 2: K = 3..4, 3: K = 5..8, 4: K > 8 (incl. overflow)
 constexpr int kPostClasses = 5;
 enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, WC_NTL, WC_CURSOR_L,
-       WC_NA /* kPostClasses counters */,
-       kWaveCounters = 16 };
-static_assert(WC_NA + kPostClasses + 1 <= kWaveCounters, "wave counters overflow");
+       WC_NA /* kPostClasses + 1 counters */,
+       WC_SUM_GENERAL = WC_NA + kPostClasses + 1, WC_SUM_DEFERRED,   // running totals of the pass (general-kernel slots, deferred slots)
+       kWaveCounters = 24 };
+static_assert(WC_SUM_DEFERRED < kWaveCounters, "wave counters overflow");
 struct WavePool {
     int P;
     // fields that are read together share a 32-byte sector: slots are visited in arbitrary order, so every

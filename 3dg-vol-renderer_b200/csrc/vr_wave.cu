@@ -560,18 +560,24 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
     return (light >= 0 && light < 32 && ((S.lg_mask >> light) & 1u)) ? DEST_TRAV_LIGHT : DEST_TRAV;
 }
 
-template <int MODE>   // 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots
+template <int MODE>   // 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots, 3 general, solves in place
 __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
     constexpr bool FAST = MODE == 1;
-    constexpr int kFirst = MODE == 1 ? 0 : (MODE == 0 ? 1 : kPostClasses);              // classes [kFirst, kLast)
-    constexpr int kLast = MODE == 1 ? 1 : (MODE == 0 ? kPostClasses : kPostClasses + 1);
+    constexpr int kFirst = MODE == 1 ? 0 : (MODE == 2 ? kPostClasses : 1);              // classes [kFirst, kLast)
+    constexpr int kLast = MODE == 1 ? 1 : (MODE == 2 ? kPostClasses + 1 : kPostClasses);
     unsigned int nA[kPostClasses + 1], base[kPostClasses + 2];
     base[kFirst] = 0;
 #pragma unroll
     for (int c = kFirst; c < kLast; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
     const unsigned int total = base[kLast];
-    if (MODE == 0 && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;  // consumed by wave_trav<scatter>
+    if ((MODE == 0 || MODE == 3) && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;
+    if (MODE != 1 && blockIdx.x == 0 && threadIdx.x == 0) {   // the host decides from these whether deferring pays (run_wavefront_pass)
+        unsigned int sum = 0;
+#pragma unroll
+        for (int c = kFirst; c < kLast; ++c) sum += nA[c];
+        Q.cnt[MODE == 2 ? WC_SUM_DEFERRED : WC_SUM_GENERAL] += sum;
+    }  // consumed by wave_trav<scatter>
     WaveCounters cn = {0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (total + stride - 1) / stride;
@@ -791,9 +797,10 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     parts = std::max(1, std::min(parts, kMaxWaveParts));
     if (prof || pass_pixels < (unsigned int)parts) parts = 1;
     struct Part {
-        RenderArgs a; WavePool q; cudaStream_t st; cudaEvent_t ev; unsigned int* h; bool done;
+        RenderArgs a; WavePool q; cudaStream_t st; cudaEvent_t ev; unsigned int* h; bool done, defer;
         int grid_s, grid_h, grid_l, grid_post, grid_post256;
     } part[kMaxWaveParts];
+    static const int defer_env = getenv("VR_WAVE_DEFER") ? atoi(getenv("VR_WAVE_DEFER")) : -1;   // 0 / 1 force, default adaptive
     const int P_part = P_total / parts;
     const size_t pool_stride = wave_pool_bytes(P_part);
     cudaEvent_t fork;
@@ -803,6 +810,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         Part& pt = part[i];
         const unsigned int px0 = (unsigned int)((unsigned long long)pass_pixels * i / parts), px1 = (unsigned int)((unsigned long long)pass_pixels * (i + 1) / parts);
         pt.a = a_all;
+        pt.defer = defer_env != 0;
         pt.a.pixel_base = a_all.pixel_base + px0;
         pt.a.work_base = px0 * (unsigned int)a_all.spp;
         pt.a.work_count = (px1 - px0) * (unsigned int)a_all.spp;
@@ -845,8 +853,12 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
                 wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
                 if (prof) cudaEventRecord(pe[2], st);
                 wave_post_a_kernel<1><<<pt.grid_post, 128, 0, st>>>(a, q);
-                wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
-                wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
+                if (pt.defer) {
+                    wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
+                    wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
+                } else {
+                    wave_post_a_kernel<3><<<pt.grid_post, 128, 0, st>>>(a, q);
+                }
                 if (prof) {
                     cudaEventRecord(pe[3], st);
                     unsigned int hc[kWaveCounters];
@@ -881,6 +893,9 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             if (pt.done) continue;
             if (cudaEventSynchronize(pt.ev) != cudaSuccess) { failed = true; break; }
             // after wave_post_b: rays left = listTs + slots waiting for a new sample
+            // deferring the iterative solves redoes those slots' walk: it pays while they are few (sparse mixtures: 8 % of the
+            // general slots at C2), not when a third of all slots need one (C3, heavy overlap)
+            if (defer_env < 0 && pt.defer && pt.h[WC_SUM_GENERAL] > 4096u && 5ull * pt.h[WC_SUM_DEFERRED] > pt.h[WC_SUM_GENERAL]) pt.defer = false;
             const bool more_samples = pt.h[WC_NEXT_SAMPLE] < pt.a.work_count;
             if (pt.h[WC_NTS] == 0 && (pt.h[WC_NC] == 0 || !more_samples)) pt.done = true;
         }

@@ -80,17 +80,20 @@ def cpu_render_sample(cfg, scene, seconds_target=15.0):
     from oracle import oracle_binding as ob
     ob.build()
     integ = cfg["integrator"]
-    cores = os.cpu_count() or 1
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+    # silently make the CPU arm single-threaded at N > 1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     if ob.have_ref():
         sg = _pkg("scenegen")
         tmp = tempfile.mkdtemp()
         path = os.path.join(tmp, "scene.txt")
         sg.write_gmm(path, scene)
         kw = dict(scene=path, integrator=integ, cam="pinhole", pos="0,1,6", look="0,1,0", fov="0.78539816339")
-        probe = ob.run_ref("render", w=64, h=64, spp=4, **kw)
+        probe = ob.run_ref("render", threads=cores, w=64, h=64, spp=4, **kw)
         rate = max(probe["msamples_per_s"], 1e-6) * 1e6
         side = int(min(cfg["W"], max(64, (seconds_target * rate / 16) ** 0.5)))
-        r = ob.run_ref("render", w=side, h=side, spp=16, repeat=1, **kw)
+        r = ob.run_ref("render", threads=cores, w=side, h=side, spp=16, repeat=1, **kw)
         return dict(value=r["msamples_per_s"], unit="Msamples/s", cores=int(r["threads"]), kind="reference",
                     sample=f"same scene and camera at {side}x{side}, 16 spp ({side * side * 16} samples, "
                            f"{r['time_s']:.1f} s), unmodified reference headers via oracle/_ref/ref_driver")
