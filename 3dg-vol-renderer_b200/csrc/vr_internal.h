@@ -44,14 +44,18 @@ enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_
        WC_SUM_GENERAL = WC_NA + kPostClasses + 1, WC_SUM_DEFERRED,   // running totals of the pass (general-kernel slots, deferred slots)
        kWaveCounters = 24 };
 static_assert(WC_SUM_DEFERRED < kWaveCounters, "wave counters overflow");
+constexpr int kSlotF4 = 8;           // float4s per slot record
 struct WavePool {
     int P;
-    // fields that are read together share a 32-byte sector: slots are visited in arbitrary order, so every
-    // separately stored field costs a sector of its own
-    float4* ray;          // [2p]: o.xyz, lim (scatter: sampled optical depth, shadow: tmax); [2p+1]: d.xyz, kind bits
-    float4* ps01;         // [2p]: L0 L1 L2 thr; [2p+1] (as uint4): rng state lo/hi, work (pass-local sample id), bounce
-    float4* ps2;          // [2p]: target_tau, albedo, nee_dist, nee_light bits; [2p+1]: shadow ray's optical depth sum (int64, 2^-40 units)
-    uint4* hit01;         // [2p]: overlap count, (t0, t1, index) of overlap 0; [2p+1]: (t0, t1, index) of overlap 1, pad
+    // One 128-byte record per slot (kSlotF4 = 8 float4s; the four pointers below are views into it at +0, +2, +4, +6):
+    // slots are visited in arbitrary order and DRAM moves 64 bytes at a time, so separate arrays cost a burst per field
+    // (profiles/r01_v8: the post kernels moved 2.2x their useful bytes).  Order ray | ps2 | ps01 | hit01: the shadow
+    // traversal reads ray and writes the depth sum next to it, post A reads ray + the adjacent ps01 | hit01 pair, post B
+    // reads the first three sectors.
+    float4* ray;          // [8p]: o.xyz, lim (scatter: sampled optical depth, shadow: tmax); [8p+1]: d.xyz, kind bits
+    float4* ps2;          // [8p]: target_tau, albedo, nee_dist, nee_light bits; [8p+1]: shadow ray's optical depth sum (int64, 2^-40 units)
+    float4* ps01;         // [8p]: L0 L1 L2 thr; [8p+1] (as uint4): rng state lo/hi, work (pass-local sample id), bounce
+    uint4* hit01;         // [8p]: overlap count, (t0, t1, index) of overlap 0; [8p+1]: (t0, t1, index) of overlap 1, pad
     float* hit_t0;        // overlaps 2..kWaveCap-1: [k - 2][P]
     float* hit_t1;
     uint32_t* hit_gi;

@@ -40,8 +40,9 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     const size_t p = (size_t)P;
     auto take = [&](size_t bytes) { char* r = b; b += align256(bytes); return (void*)r; };
     q->P = P;
-    q->ray = (float4*)take(p * 32); q->ps01 = (float4*)take(p * 32); q->ps2 = (float4*)take(p * 32);
-    q->hit01 = (uint4*)take(p * 32);
+    // one 128-byte record per slot (kSlotF4 float4s): ray | ps2 | ps01 | hit01, see vr_internal.h
+    float4* slab = (float4*)take(p * 128);
+    q->ray = slab; q->ps2 = slab + 2; q->ps01 = slab + 4; q->hit01 = (uint4*)(slab + 6);
     q->hit_t0 = (float*)take(p * 4 * (kWaveCap - 2)); q->hit_t1 = (float*)take(p * 4 * (kWaveCap - 2));
     q->hit_gi = (uint32_t*)take(p * 4 * (kWaveCap - 2));
     q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4); q->listTl = (unsigned int*)take(p * 4);
@@ -82,7 +83,7 @@ enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2, DEST_TRAV_LIGHT = 3 };
 // rays of a sparse mixture gather at most two components), the rest live in [k - 2][P] arrays
 __device__ __forceinline__ void pool_store_hit(const WavePool& Q, unsigned int p, int k, float t0, float t1, uint32_t gi) {
     if (k < 2) {
-        uint32_t* r = reinterpret_cast<uint32_t*>(Q.hit01 + 2 * (size_t)p) + 1 + 3 * k;
+        uint32_t* r = reinterpret_cast<uint32_t*>(Q.hit01 + kSlotF4 * (size_t)p) + 1 + 3 * k;
         r[0] = __float_as_uint(t0); r[1] = __float_as_uint(t1); r[2] = gi;
     } else {
         const size_t at = (size_t)(k - 2) * Q.P + p;
@@ -92,7 +93,7 @@ __device__ __forceinline__ void pool_store_hit(const WavePool& Q, unsigned int p
 __device__ __forceinline__ void pool_load_hit(const WavePool& Q, unsigned int p, int k, const uint4& h0, float* t0, float* t1, uint32_t* gi) {
     if (k == 0) { *t0 = __uint_as_float(h0.y); *t1 = __uint_as_float(h0.z); *gi = h0.w; }
     else if (k == 1) {
-        const uint4 h1 = Q.hit01[2 * (size_t)p + 1];
+        const uint4 h1 = Q.hit01[kSlotF4 * (size_t)p + 1];
         *t0 = __uint_as_float(h1.x); *t1 = __uint_as_float(h1.y); *gi = h1.z;
     } else {
         const size_t at = (size_t)(k - 2) * Q.P + p;
@@ -379,12 +380,12 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                 // slot back to the regeneration list (integrator.h:594-597; the target draw is not committed)
                 const bool esc = flush && K == 0;
                 if (esc) {
-                    const float4 s0 = Q.ps01[2 * (size_t)p];
-                    const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
+                    const float4 s0 = Q.ps01[kSlotF4 * (size_t)p];
+                    const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1];
                     A.sampleL[s1.z] = make_float4(__fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0])), __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1])),
                                                   __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2])), (float)s1.w);
                 }
-                if (flush && K > 0) reinterpret_cast<int*>(Q.hit01 + 2 * (size_t)p)[0] = K;
+                if (flush && K > 0) reinterpret_cast<int*>(Q.hit01 + kSlotF4 * (size_t)p)[0] = K;
                 wave_append(Q.listC, &Q.cnt[WC_NC], esc, p);
                 const int cls = post_class(K);
 #pragma unroll
@@ -392,7 +393,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                     wave_append(Q.listA + (size_t)c * Q.P, &Q.cnt[WC_NA + c], flush && K > 0 && cls == c, p);
             } else {
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
-                if (flush) reinterpret_cast<long long*>(Q.ps2 + 2 * (size_t)p + 1)[0] = wh.tau[lane];
+                if (flush) reinterpret_cast<long long*>(Q.ps2 + kSlotF4 * (size_t)p + 1)[0] = wh.tau[lane];
                 wave_append(Q.listB, &Q.cnt[WC_NB], flush, p);
             }
             tl.has_result = false;
@@ -405,7 +406,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                     const unsigned int idx = base + (unsigned int)__popc(mF & ((1u << lane) - 1u));
                     if (idx < nT) {
                         const unsigned int np = __ldg(list + idx);
-                        const float4 ro = Q.ray[2 * (size_t)np], rd = Q.ray[2 * (size_t)np + 1];
+                        const float4 ro = Q.ray[kSlotF4 * (size_t)np], rd = Q.ray[kSlotF4 * (size_t)np + 1];
                         w.ray[0][lane] = ro.x; w.ray[1][lane] = ro.y; w.ray[2][lane] = ro.z;
                         w.ray[3][lane] = rd.x; w.ray[4][lane] = rd.y; w.ray[5][lane] = rd.z;
                         w.ray[6][lane] = ro.w;
@@ -457,8 +458,8 @@ __device__ __forceinline__ void publish_scatter_ray(const WavePool& Q, unsigned 
     Pcg peek; peek.state = rng_state; peek.inc = 3;
     const float t = -logf(__fsub_rn(1.0f, peek.uniform()));
     *target = t;
-    Q.ray[2 * (size_t)p] = make_float4(o.x, o.y, o.z, t);
-    Q.ray[2 * (size_t)p + 1] = make_float4(d.x, d.y, d.z, __int_as_float(RAY_SCATTER));
+    Q.ray[kSlotF4 * (size_t)p] = make_float4(o.x, o.y, o.z, t);
+    Q.ray[kSlotF4 * (size_t)p + 1] = make_float4(d.x, d.y, d.z, __int_as_float(RAY_SCATTER));
 }
 
 // wave_regen: integrator.h:557-570
@@ -492,8 +493,8 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
             const RayOD ray = camera_ray(A.cam, u, v);
             float target;
             publish_scatter_ray(Q, p, ray.o, ray.d, rng.state, &target);
-            Q.ps01[2 * (size_t)p] = make_float4(0.f, 0.f, 0.f, 1.0f);
-            reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), idx, 0u);
+            Q.ps01[kSlotF4 * (size_t)p] = make_float4(0.f, 0.f, 0.f, 1.0f);
+            reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), idx, 0u);
             ++cn.scatter;
             to_trav = true;
         }
@@ -552,10 +553,10 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
         dist = CUDART_INF_F;
         light = -1;
     }
-    Q.ray[2 * (size_t)p] = make_float4(pos.x, pos.y, pos.z, dist);
-    Q.ray[2 * (size_t)p + 1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW | ((light + 1) << 8)));
-    reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
-    Q.ps2[2 * (size_t)p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
+    Q.ray[kSlotF4 * (size_t)p] = make_float4(pos.x, pos.y, pos.z, dist);
+    Q.ray[kSlotF4 * (size_t)p + 1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(RAY_SHADOW | ((light + 1) << 8)));
+    reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w);
+    Q.ps2[kSlotF4 * (size_t)p] = make_float4(target_tau, albedo, dist, __int_as_float(light));
     // a ray to a point light that has a direction grid takes its candidates from the grid (wave_trav_kernel<RAY_LIGHT>)
     return (light >= 0 && light < 32 && ((S.lg_mask >> light) & 1u)) ? DEST_TRAV_LIGHT : DEST_TRAV;
 }
@@ -594,11 +595,11 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
         for (int c = kFirst + 1; c < kLast; ++c) if (cls == c) { j = i - base[c]; nc = nA[c]; }
         if (i < total && j < nc) {
             p = Q.listA[(size_t)cls * Q.P + j];
-            const uint4 h0 = Q.hit01[2 * (size_t)p];   // overlap count + first overlap
+            const uint4 h0 = Q.hit01[kSlotF4 * (size_t)p];   // overlap count + first overlap
             const int K = (int)h0.x;
-            const float4 s0 = Q.ps01[2 * (size_t)p];
-            const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
-            const float4 ro = Q.ray[2 * (size_t)p], rd = Q.ray[2 * (size_t)p + 1];
+            const float4 s0 = Q.ps01[kSlotF4 * (size_t)p];
+            const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1];
+            const float4 ro = Q.ray[kSlotF4 * (size_t)p], rd = Q.ray[kSlotF4 * (size_t)p + 1];
             const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
             const float target_tau = ro.w;
             Pcg rng; rng.state = (uint64_t)s1.x | ((uint64_t)s1.y << 32); rng.inc = 3;
@@ -709,12 +710,12 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
         unsigned int p = 0;
         if (i < nB) {
             p = Q.listB[i];
-            float4 s0 = Q.ps01[2 * (size_t)p];
-            uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1];
-            const float4 s2 = Q.ps2[2 * (size_t)p];
+            float4 s0 = Q.ps01[kSlotF4 * (size_t)p];
+            uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1];
+            const float4 s2 = Q.ps2[kSlotF4 * (size_t)p];
             const float albedo = s2.y, nee_dist = s2.z;
             const int light = __float_as_int(s2.w);
-            const long long tf = reinterpret_cast<const long long*>(Q.ps2 + 2 * (size_t)p + 1)[0];
+            const long long tf = reinterpret_cast<const long long*>(Q.ps2 + kSlotF4 * (size_t)p + 1)[0];
             // exp(-float(sum)), sum = double sum of the clipped depths (gmm.h:577); exactly 0 beyond the cutoff
             const float Tr = tf > tau_cutoff_fixed() ? 0.0f : expf(-(float)((double)tf / kTauFixed));
             float Li0, Li1, Li2;
@@ -754,11 +755,11 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
                     A.sampleL[s1.z] = make_float4(s0.x, s0.y, s0.z, (float)s1.w);
                 } else {
                     const f3 nd = sample_direction_ni(&stt);
-                    const float4 ro = Q.ray[2 * (size_t)p];  // the scatter position is the shadow ray's origin
+                    const float4 ro = Q.ray[kSlotF4 * (size_t)p];  // the scatter position is the shadow ray's origin
                     float target;
                     publish_scatter_ray(Q, p, mk3(ro.x, ro.y, ro.z), nd, stt, &target);
-                    Q.ps01[2 * (size_t)p] = s0;
-                    reinterpret_cast<uint4*>(Q.ps01)[2 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w + 1u);
+                    Q.ps01[kSlotF4 * (size_t)p] = s0;
+                    reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1] = make_uint4((unsigned int)stt, (unsigned int)(stt >> 32), s1.z, s1.w + 1u);
                     ++cn.scatter;
                     dest = DEST_TRAV;
                 }
