@@ -56,9 +56,7 @@ struct WavePool {
     float4* ps2;          // [8p]: target_tau, albedo, nee_dist, nee_light bits; [8p+1]: shadow ray's optical depth sum (int64, 2^-40 units)
     float4* ps01;         // [8p]: L0 L1 L2 thr; [8p+1] (as uint4): rng state lo/hi, work (pass-local sample id), bounce
     uint4* hit01;         // [8p]: overlap count, (t0, t1, index) of overlap 0; [8p+1]: (t0, t1, index) of overlap 1, pad
-    float* hit_t0;        // overlaps 2..kWaveCap-1: [k - 2][P]
-    float* hit_t1;
-    uint32_t* hit_gi;
+    uint4* hitx;          // overlaps 2..kWaveCap-1: [p][k - 2] = (t0, t1, index, pad), contiguous per slot
     unsigned int* listTs;  // slots whose free-flight ray waits for traversal
     unsigned int* listTh;  // slots whose shadow ray waits for traversal (environment rays, lights without a grid)
     unsigned int* listTl;  // slots whose shadow ray goes to a point light that has a direction grid

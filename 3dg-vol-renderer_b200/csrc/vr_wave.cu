@@ -32,7 +32,7 @@ namespace vr {
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t wave_pool_bytes(int P) {
     const size_t p = (size_t)P;
-    return align256(p * 32) * 4 + align256(p * 4 * (kWaveCap - 2)) * 3 + align256(p * 4) * 5 + align256(p * 4 * (kPostClasses + 1)) +
+    return align256(p * 32) * 4 + align256(p * 16 * (kWaveCap - 2)) + align256(p * 4) * 5 + align256(p * 4 * (kPostClasses + 1)) +
            align256(kWaveCounters * 4);
 }
 void wave_pool_carve(WavePool* q, int P, void* base) {
@@ -43,8 +43,7 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
     // one 128-byte record per slot (kSlotF4 float4s): ray | ps2 | ps01 | hit01, see vr_internal.h
     float4* slab = (float4*)take(p * 128);
     q->ray = slab; q->ps2 = slab + 2; q->ps01 = slab + 4; q->hit01 = (uint4*)(slab + 6);
-    q->hit_t0 = (float*)take(p * 4 * (kWaveCap - 2)); q->hit_t1 = (float*)take(p * 4 * (kWaveCap - 2));
-    q->hit_gi = (uint32_t*)take(p * 4 * (kWaveCap - 2));
+    q->hitx = (uint4*)take(p * 16 * (kWaveCap - 2));
     q->listTs = (unsigned int*)take(p * 4); q->listTh = (unsigned int*)take(p * 4); q->listTl = (unsigned int*)take(p * 4);
     q->listA = (unsigned int*)take(p * 4 * (kPostClasses + 1)); q->listB = (unsigned int*)take(p * 4); q->listC = (unsigned int*)take(p * 4);
     q->cnt = (unsigned int*)take(kWaveCounters * 4);
@@ -80,14 +79,13 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
 }
 enum { DEST_NONE = 0, DEST_TRAV = 1, DEST_REGEN = 2, DEST_TRAV_LIGHT = 3 };
 // overlap records of a slot: the count and the first two records share one 32-byte sector (85 % of the free-flight
-// rays of a sparse mixture gather at most two components), the rest live in [k - 2][P] arrays
+// rays of a sparse mixture gather at most two components), the rest are 16-byte records, contiguous per slot
 __device__ __forceinline__ void pool_store_hit(const WavePool& Q, unsigned int p, int k, float t0, float t1, uint32_t gi) {
     if (k < 2) {
         uint32_t* r = reinterpret_cast<uint32_t*>(Q.hit01 + kSlotF4 * (size_t)p) + 1 + 3 * k;
         r[0] = __float_as_uint(t0); r[1] = __float_as_uint(t1); r[2] = gi;
     } else {
-        const size_t at = (size_t)(k - 2) * Q.P + p;
-        Q.hit_t0[at] = t0; Q.hit_t1[at] = t1; Q.hit_gi[at] = gi;
+        Q.hitx[(size_t)p * (kWaveCap - 2) + (k - 2)] = make_uint4(__float_as_uint(t0), __float_as_uint(t1), gi, 0u);
     }
 }
 __device__ __forceinline__ void pool_load_hit(const WavePool& Q, unsigned int p, int k, const uint4& h0, float* t0, float* t1, uint32_t* gi) {
@@ -96,8 +94,8 @@ __device__ __forceinline__ void pool_load_hit(const WavePool& Q, unsigned int p,
         const uint4 h1 = Q.hit01[kSlotF4 * (size_t)p + 1];
         *t0 = __uint_as_float(h1.x); *t1 = __uint_as_float(h1.y); *gi = h1.z;
     } else {
-        const size_t at = (size_t)(k - 2) * Q.P + p;
-        *t0 = Q.hit_t0[at]; *t1 = Q.hit_t1[at]; *gi = Q.hit_gi[at];
+        const uint4 h = Q.hitx[(size_t)p * (kWaveCap - 2) + (k - 2)];
+        *t0 = __uint_as_float(h.x); *t1 = __uint_as_float(h.y); *gi = h.z;
     }
 }
 __device__ __forceinline__ int post_class(int K) { return K <= 1 ? 0 : K == 2 ? 1 : K <= 4 ? 2 : K <= 8 ? 3 : 4; }
