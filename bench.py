@@ -38,8 +38,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ENV = (0.53, 0.81, 0.92)
-# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, profiles/r01_v8_wave_all_kernels.md
-DOMINANT_KERNEL_DRAM_BYTES = None
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, wave_trav_kernel<0> (free-flight
+# traversal, 30 % of a step): 501.5 + 146.3 MB for a full wave of 3.6 M rays, profiles/r01_v9_wave_all_kernels.md
+# (ncu --set full, caches flushed between replays; only meaningful for the C2 workload it was captured on)
+DOMINANT_KERNEL_DRAM_BYTES = 647.8e6
 CONFIGS = {
     # name: (n_gaussians, seed, nonuniform, W, H, spp, integrator)
     "c1": dict(n=1000, seed=1, nonuniform=False, W=512, H=512, spp=64, integrator="ss",
@@ -422,7 +424,7 @@ def main():
                 achieved=achieved if frac_f >= frac_m else achieved_mufu, peak=peak_tflops if frac_f >= frac_m else peak_mufu,
                 unit="TFLOP/s" if frac_f >= frac_m else "Tops/s", frac=max(frac_f, frac_m),
                 # DRAM bytes of the dominant kernel (wave_trav_kernel<free-flight>) per launch, ncu --set full capture of this command
-                traffic=DOMINANT_KERNEL_DRAM_BYTES,
+                traffic=DOMINANT_KERNEL_DRAM_BYTES if a.config == "c2" else None,
                 fp32=dict(achieved=achieved, peak=peak_tflops, unit="TFLOP/s", frac=frac_f, flop_per_sample=flop_per_sample),
                 mufu=dict(achieved=achieved_mufu, peak=peak_mufu, unit="Tops/s", frac=frac_m, ops_per_sample=mufu_per_sample),
                 hbm=dict(achieved=hbm_gbs, peak=peaks.get("hbm_gbs", 6650.0), unit="GB/s", frac=hbm_gbs / peaks.get("hbm_gbs", 6650.0),
