@@ -329,6 +329,29 @@ def test_full_size_config1_properties(ctx, ob, vr, scenegen):
     assert frac_within(a[200:232, 240:272], ref[200:232, 240:272], 1e-4) >= 0.98
 
 
+def test_full_size_config2_properties(ctx, ob, vr, scenegen):
+    """BASELINE config 2, the benchmark workload (10k Gaussians, make_nonuniform_random seed 2, 1024^2, 256 spp, multiple
+    scattering) at FULL size, with everything the bench run uses switched on (light grids, two-part passes, deferred
+    solves): deterministic, finite, the right number of samples, a row-partitioned render is bit-identical to the whole,
+    and a window of it equals the oracle's (same scene, same camera, same 256-sample streams)."""
+    scene = scenegen.generate(10000, 2, nonuniform=True)
+    _, oc = setup(ctx, ob, vr, scenegen, None, "pin", scene=scene)
+    p = vr.Context.params(vr.INTEGRATOR_MS, 1024, 1024, 256)
+    a, st = ctx.render(p)
+    assert st["samples"] == 1024 * 1024 * 256
+    assert np.isfinite(a).all() and a.min() >= 0
+    halves = np.zeros_like(a)
+    for r in range(2):
+        ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 1024, 1024, 256, part=(r, 2)), out=halves)
+    assert np.array_equal(halves, a)
+    win = (500, 600, 516, 616)   # x0, y0, x1, y1: 16 x 16 pixels in the dense lower half of the mixture
+    ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 1024, 1024, 256, window=win)
+    assert frac_within(a[600:616, 500:516], ref[600:616, 500:516], 1e-4) >= 0.97
+    # the same window rendered alone (a small render: no grids, one part) is the same image
+    w, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 1024, 1024, 256, window=win))
+    assert np.array_equal(w[600:616, 500:516], a[600:616, 500:516])
+
+
 # ------------------------------------------------------------------------------------------------
 # inverse path
 # ------------------------------------------------------------------------------------------------
