@@ -68,6 +68,7 @@ int vr_create(vr_context** out, int device_id) {
     VR_CUDA(cudaMallocHost((void**)&ctx->h_stats, sizeof(unsigned long long) * kNumStats));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_counters, sizeof(unsigned int) * 32));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_wave_counters, sizeof(unsigned int) * kMaxWaveParts * kWaveCounters));
+    ctx->wave_graphs = wave_graph_cache_create();
     VR_CUDA(ctx->stats.ensure(sizeof(unsigned long long) * kNumStats));
     VR_CUDA(ctx->counters.ensure(sizeof(unsigned int) * 4));
     ctx->blocks_per_sm_main = std::max(1, path_kernel_blocks_per_sm(false));
@@ -88,6 +89,7 @@ void vr_destroy(vr_context* ctx) {
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     if (ctx->h_wave_counters) cudaFreeHost(ctx->h_wave_counters);
+    vr::wave_graph_cache_destroy(ctx->wave_graphs);
     for (cudaStream_t ws : ctx->wave_streams) if (ws) cudaStreamDestroy(ws);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -76,6 +76,7 @@ struct vr_context {
     int wave_slots = 0;                            // 0 = 24576 per SM (sweep in profiles/r01_tuning.md)
     int wave_parts = 2;                            // independent parts (own pool + stream) a big pass is cut into
     cudaStream_t wave_streams[vr::kMaxWaveParts] = {nullptr, nullptr, nullptr, nullptr};
+    vr::WaveGraphCache* wave_graphs = nullptr;     // CUDA graphs of the iteration batches, reused while the launch arguments stay the same
     unsigned int* h_wave_counters = nullptr;       // pinned, kMaxWaveParts * kWaveCounters
     // ---- inverse
     vr::SfdState* sfd = nullptr;

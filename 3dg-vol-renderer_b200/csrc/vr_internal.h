@@ -69,8 +69,12 @@ size_t wave_pool_bytes(int P);
 void wave_pool_carve(WavePool* q, int P, void* base);
 // runs the whole pass (a.work_count samples) ; returns the number of iterations enqueued, < 0 on CUDA error
 constexpr int kMaxWaveParts = 4;
+// instantiated CUDA graphs of the per-part iteration batches, kept between renders (a context owns one)
+struct WaveGraphCache;
+WaveGraphCache* wave_graph_cache_create();
+void wave_graph_cache_destroy(WaveGraphCache* c);
 int run_wavefront_pass(const RenderArgs& a, void* pool_mem, int P_total, int parts, int num_sms, unsigned int* h_cnt_pinned /* parts * kWaveCounters */,
-                       cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches);
+                       cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches, struct WaveGraphCache* graphs);
 
 constexpr int kBlockThreads = 128;
 constexpr int kLocalCap = 32;        // overlaps kept in local memory by the main kernel

@@ -109,7 +109,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
                 VR_CUDA(ctx->wavepool.ensure(wave_pool_bytes(P / parts) * parts));
                 for (int i = 0; i < parts; ++i)
                     if (!ctx->wave_streams[i]) VR_CUDA(cudaStreamCreateWithFlags(&ctx->wave_streams[i], cudaStreamNonBlocking));
-                if (run_wavefront_pass(A, ctx->wavepool.p, P, parts, ctx->num_sms, ctx->h_wave_counters, s, ctx->wave_streams, &launches) < 0) {
+                if (run_wavefront_pass(A, ctx->wavepool.p, P, parts, ctx->num_sms, ctx->h_wave_counters, s, ctx->wave_streams, &launches, ctx->wave_graphs) < 0) {
                     VR_CUDA(cudaGetLastError());
                     return fail(ctx, VR_ERR_CUDA, "wavefront pass failed");
                 }

@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 #include "vr_internal.h"
 #include "vr_pathcommon.cuh"
@@ -781,8 +782,25 @@ __global__ void wave_init_kernel(const __grid_constant__ WavePool Q, unsigned in
 // One pass = a.work_count samples.  The pass is cut into `parts` pixel ranges, each with its own pool of slots, counters
 // and stream; the kernel chains of the parts are independent, so the tail of one part's kernel (persistent warps waiting
 // for the last rays, 9-15 % of SM cycles per kernel in profiles/r01_v7) is filled by the other part's kernels.
+// A graph is reusable when every kernel argument and grid of the batch is byte-identical (repeated renders of one
+// configuration: the bench loop, the S + 1 renders per view of every inverse iteration).
+struct WaveGraphKey { RenderArgs a; WavePool q; int grid[5]; int defer; };
+struct WaveGraphCache {
+    struct Entry { bool valid; WaveGraphKey key; cudaGraphExec_t exec; } e[kMaxWaveParts][2];
+};
+WaveGraphCache* wave_graph_cache_create() {
+    WaveGraphCache* c = new WaveGraphCache;
+    memset((void*)c, 0, sizeof(*c));
+    return c;
+}
+void wave_graph_cache_destroy(WaveGraphCache* c) {
+    if (!c) return;
+    for (auto& row : c->e) for (auto& en : row) if (en.exec) cudaGraphExecDestroy(en.exec);
+    delete c;
+}
+
 int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int parts, int num_sms, unsigned int* h_cnt_all,
-                       cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches) {
+                       cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches, WaveGraphCache* graphs) {
     static int bps_s = 0, bps_h = 0, bps_l = 0;
     if (!bps_s) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
@@ -799,6 +817,8 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         RenderArgs a; WavePool q; cudaStream_t st; cudaEvent_t ev; unsigned int* h; bool done, defer;
         int grid_s, grid_h, grid_l, grid_post, grid_post256;
     } part[kMaxWaveParts];
+    static const bool graph_env = !(getenv("VR_WAVE_GRAPH") && getenv("VR_WAVE_GRAPH")[0] == '0');
+    const bool use_graph = graph_env && !prof && graphs != nullptr;   // the profile mode synchronises inside an iteration
     static const int defer_env = getenv("VR_WAVE_DEFER") ? atoi(getenv("VR_WAVE_DEFER")) : -1;   // 0 / 1 force, default adaptive
     const int P_part = P_total / parts;
     const size_t pool_stride = wave_pool_bytes(P_part);
@@ -837,49 +857,77 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     unsigned long long cls_total[kPostClasses + 1] = {0, 0, 0, 0, 0, 0};
     if (prof) for (auto& e : pe) cudaEventCreate(&e);
     bool failed = false;
+    // one iteration of a part: every kernel consumes the list the previous one filled
+    auto enqueue_iteration = [&](Part& pt) {
+        const RenderArgs& a = pt.a; const WavePool& q = pt.q; cudaStream_t st = pt.st;
+        if (prof) cudaEventRecord(pe[0], st);
+        wave_regen_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
+        if (prof) cudaEventRecord(pe[1], st);
+        wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
+        if (prof) cudaEventRecord(pe[2], st);
+        wave_post_a_kernel<1><<<pt.grid_post, 128, 0, st>>>(a, q);
+        if (pt.defer) {
+            wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
+            wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
+        } else {
+            wave_post_a_kernel<3><<<pt.grid_post, 128, 0, st>>>(a, q);
+        }
+        if (prof) {
+            cudaEventRecord(pe[3], st);
+            unsigned int hc[kWaveCounters];
+            cudaMemcpyAsync(hc, q.cnt, sizeof(hc), cudaMemcpyDeviceToHost, st);
+            cudaStreamSynchronize(st);
+            for (int c = 0; c <= kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
+        }
+        wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
+        if (prof) cudaEventRecord(pe[6], st);
+        if (a.scene.lg_mask) wave_trav_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
+        if (prof) cudaEventRecord(pe[4], st);
+        wave_post_b_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
+        if (prof) {
+            cudaEventRecord(pe[5], st);
+            cudaEventSynchronize(pe[5]);
+            for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); ptm[k] += ms; }
+            { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
+        }
+    };
+    // The batch of kBatch iterations is a fixed chain of 6-8 kernels with fixed grids and arguments: it is captured
+    // once per part (and per deferral mode) into a CUDA graph and replayed, so a batch costs one launch on the host and
+    // the kernels of short waves (small renders, the drain of a pass) follow each other without launch gaps.
     while (!failed) {
         bool any = false;
-        for (int b = 0; b < kBatch; ++b) {
-            for (int i = 0; i < parts; ++i) {
-                Part& pt = part[i];
-                if (pt.done) continue;
-                any = true;
-                const RenderArgs& a = pt.a; const WavePool& q = pt.q; cudaStream_t st = pt.st;
-                // chain: every kernel consumes the list the previous one filled
-                if (prof) cudaEventRecord(pe[0], st);
-                wave_regen_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
-                if (prof) cudaEventRecord(pe[1], st);
-                wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
-                if (prof) cudaEventRecord(pe[2], st);
-                wave_post_a_kernel<1><<<pt.grid_post, 128, 0, st>>>(a, q);
-                if (pt.defer) {
-                    wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
-                    wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
-                } else {
-                    wave_post_a_kernel<3><<<pt.grid_post, 128, 0, st>>>(a, q);
+        for (int i = 0; i < parts; ++i) {
+            Part& pt = part[i];
+            if (pt.done) continue;
+            any = true;
+            const unsigned int per_iter = 6u + (pt.defer ? 1u : 0u) + (pt.a.scene.lg_mask ? 1u : 0u);
+            if (use_graph) {
+                WaveGraphCache::Entry& en = graphs->e[i][pt.defer ? 1 : 0];
+                WaveGraphKey key;
+                memset((void*)&key, 0, sizeof(key));
+                memcpy((void*)&key.a, (const void*)&pt.a, sizeof(RenderArgs)); memcpy((void*)&key.q, (const void*)&pt.q, sizeof(WavePool));
+                key.grid[0] = pt.grid_s; key.grid[1] = pt.grid_h; key.grid[2] = pt.grid_l; key.grid[3] = pt.grid_post; key.grid[4] = pt.grid_post256;
+                key.defer = pt.defer ? 1 : 0;
+                if (!en.valid || memcmp((const void*)&en.key, (const void*)&key, sizeof(key)) != 0) {
+                    if (en.exec) { cudaGraphExecDestroy(en.exec); en.exec = nullptr; }
+                    en.valid = false;
+                    cudaGraph_t g = nullptr;
+                    if (cudaStreamBeginCapture(pt.st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { failed = true; break; }
+                    for (int b = 0; b < kBatch; ++b) enqueue_iteration(pt);
+                    if (cudaStreamEndCapture(pt.st, &g) != cudaSuccess || cudaGraphInstantiate(&en.exec, g, 0) != cudaSuccess) { failed = true; en.exec = nullptr; }
+                    if (g) cudaGraphDestroy(g);
+                    if (failed) break;
+                    memcpy((void*)&en.key, (const void*)&key, sizeof(key));
+                    en.valid = true;
                 }
-                if (prof) {
-                    cudaEventRecord(pe[3], st);
-                    unsigned int hc[kWaveCounters];
-                    cudaMemcpyAsync(hc, q.cnt, sizeof(hc), cudaMemcpyDeviceToHost, st);
-                    cudaStreamSynchronize(st);
-                    for (int c = 0; c <= kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
-                }
-                wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
-                if (prof) cudaEventRecord(pe[6], st);
-                if (a.scene.lg_mask) { wave_trav_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q); ++*launches; }
-                if (prof) cudaEventRecord(pe[4], st);
-                wave_post_b_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
-                if (prof) {
-                    cudaEventRecord(pe[5], st);
-                    cudaEventSynchronize(pe[5]);
-                    for (int k = 0; k < 5; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[k], pe[k + 1]); ptm[k] += ms; }
-                    { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
-                }
-                *launches += 7;
+                cudaGraphExec_t ge = en.exec;
+                if (cudaGraphLaunch(ge, pt.st) != cudaSuccess) { failed = true; break; }
+            } else {
+                for (int b = 0; b < kBatch; ++b) enqueue_iteration(pt);
             }
-            ++iters;
+            *launches += per_iter * kBatch;
         }
+        iters += kBatch;
         if (!any) break;
         for (int i = 0; i < parts; ++i) {
             Part& pt = part[i];
