@@ -3,7 +3,9 @@
 
 #include <algorithm>
 #include <cmath>
+#include <atomic>
 #include <limits>
+#include <thread>
 
 namespace vr {
 namespace {
@@ -106,6 +108,11 @@ struct Builder {
         return left;
     }
 
+    // a subtree left to a worker thread: nodes[ni].child[c] is patched once the subtree's place in `nodes` is known
+    struct Task { int ni, c, first, count, left, depth; };
+    std::vector<Task>* defer = nullptr;   // non-null: subtrees below kDeferDepth with enough work are listed, not built
+    static constexpr int kDeferDepth = 4, kDeferMinCount = 512;
+
     // builds the subtree over [first, first+count) (count >= 2, to be split) into nodes[ni]
     void build_node(int ni, int first, int count, int left, int depth) {
         max_depth = std::max(max_depth, depth);
@@ -118,6 +125,8 @@ struct Builder {
             if (l == 0) {
                 nodes[ni].child[c] = leaf_code(f, k);
                 max_leaf = std::max(max_leaf, k);
+            } else if (defer && depth >= kDeferDepth && k >= kDeferMinCount) {
+                defer->push_back(Task{ni, c, f, k, l, depth + 1});
             } else {
                 int ci = (int)nodes.size();
                 nodes.push_back(BvhNode{});
@@ -151,8 +160,45 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
         nd.child[0] = Builder::leaf_code(0, n);
         nd.child[1] = Builder::leaf_code(0, 0);
         b.max_leaf = n;
-    } else {
+    } else if (n < 4096) {
         b.build_node(0, 0, n, left, 1);
+    } else {
+        // The top levels are built here; every subtree below them works on its own range of `perm`, so the subtrees are
+        // built by worker threads into private node arrays and appended in task order.  The task list depends only on the
+        // input, not on the thread count or timing: the tree is the same on every run and every machine.
+        std::vector<Builder::Task> tasks;
+        b.defer = &tasks;
+        b.build_node(0, 0, n, left, 1);
+        b.defer = nullptr;
+        struct Sub { std::vector<BvhNode> nodes; int max_depth = 0, max_leaf = 0; };
+        std::vector<Sub> subs(tasks.size());
+        std::atomic<size_t> next{0};
+        auto work = [&] {
+            for (size_t t; (t = next.fetch_add(1)) < tasks.size();) {
+                const Builder::Task& tk = tasks[t];
+                Builder lb{n, lo, hi, out->perm, subs[t].nodes};
+                subs[t].nodes.reserve((size_t)tk.count);
+                subs[t].nodes.push_back(BvhNode{});
+                lb.build_node(0, tk.first, tk.count, tk.left, tk.depth);
+                subs[t].max_depth = lb.max_depth; subs[t].max_leaf = lb.max_leaf;
+            }
+        };
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const size_t nthreads = std::min<size_t>(std::min<size_t>(tasks.size(), hw), 16);
+        std::vector<std::thread> pool;
+        for (size_t t = 1; t < nthreads; ++t) pool.emplace_back(work);
+        work();
+        for (std::thread& th : pool) th.join();
+        for (size_t t = 0; t < tasks.size(); ++t) {
+            const int offset = (int)out->nodes.size();
+            out->nodes[(size_t)tasks[t].ni].child[tasks[t].c] = offset;
+            for (BvhNode nd : subs[t].nodes) {
+                for (int c = 0; c < 2; ++c) if (nd.child[c] >= 0) nd.child[c] += offset;
+                out->nodes.push_back(nd);
+            }
+            b.max_depth = std::max(b.max_depth, subs[t].max_depth);
+            b.max_leaf = std::max(b.max_leaf, subs[t].max_leaf);
+        }
     }
     out->max_depth = b.max_depth;
     out->max_leaf = b.max_leaf;
