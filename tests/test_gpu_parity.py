@@ -329,6 +329,25 @@ def test_full_size_config1_properties(ctx, ob, vr, scenegen):
     assert frac_within(a[200:232, 240:272], ref[200:232, 240:272], 1e-4) >= 0.98
 
 
+@pytest.mark.parametrize("integ", ["ms", "ss"])
+def test_single_kernel_engine_cross_check(ctx, ob, vr, scenegen, integ):
+    """vr_set_option("engine", 1): the warp-scheduled single-kernel engine kept as a cross-check of the wavefront one.
+    Same parity bar against the oracle, and the two engines agree with each other to rounding (their shadow sums are
+    accumulated differently: double in traversal order vs 2^-40 fixed point)."""
+    scene, oc = setup(ctx, ob, vr, scenegen, "rand300", "pin")
+    it_o = ob.INTEGRATOR_MS if integ == "ms" else ob.INTEGRATOR_SS
+    it_v = vr.INTEGRATOR_MS if integ == "ms" else vr.INTEGRATOR_SS
+    ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, it_o, 48, 48, 16)
+    wave, _ = ctx.render(vr.Context.params(it_v, 48, 48, 16))
+    try:
+        ctx.set_option("engine", 1)
+        single, _ = ctx.render(vr.Context.params(it_v, 48, 48, 16))
+    finally:
+        ctx.set_option("engine", 0)
+    assert frac_within(single, ref, 1e-4) >= 0.98
+    assert frac_within(single, wave, 1e-5) >= 0.99
+
+
 def test_full_size_config2_properties(ctx, ob, vr, scenegen):
     """BASELINE config 2, the benchmark workload (10k Gaussians, make_nonuniform_random seed 2, 1024^2, 256 spp, multiple
     scattering) at FULL size, with everything the bench run uses switched on (light grids, two-part passes, deferred
