@@ -201,14 +201,19 @@ __device__ int gather_overlaps(const SceneDev& S, f3 o, f3 d, float target_tau, 
     return K;
 }
 
-// GaussianMixtureModel::transmittance_up_to (gmm.h:517-578): sum of clipped optical depths in double
+// GaussianMixtureModel::transmittance_up_to (gmm.h:517-578): exp(-sum of clipped optical depths).  The reference sums
+// in double in ITS traversal order; every engine here sums the float depths in 2^-40 fixed point instead, which is
+// order-independent and within 1e-12 of the double sum, so that a sample's value does not depend on which kernel
+// (wavefront, drain, overflow re-trace) or which candidate order produced it.
+constexpr double kTauFixed = 1099511627776.0;  // 2^40
+__device__ __forceinline__ long long tau_cutoff_fixed() { return (long long)((double)kShadowTauCutoff * kTauFixed); }
 static __device__ float shadow_transmittance(const SceneDev& S, f3 o, f3 d, float tmax) {
     if (tmax <= 0.0f) return 1.0f;
     if (S.n == 0) return 1.0f;
     const RaySetup rs = ray_setup(o, d);
     int stack[kStackDepth];
     int sp = 0, cur = 0;
-    double sum = 0.0;
+    long long sum = 0;
     while (true) {
         if (cur >= 0) {
             bool h0, h1; float tn0, tn1; int c0, c1;
@@ -230,14 +235,14 @@ static __device__ float shadow_transmittance(const SceneDev& S, f3 o, f3 d, floa
                 float t0, t1;
                 if (!quad_intersect(q, &t0, &t1)) continue;
                 const float a = fmaxf(0.0f, t0), b = fminf(tmax, t1);
-                if (b > a) sum += (double)depth_between(depth_const(g, q), a, b);
+                if (b > a) sum += __double2ll_rn((double)depth_between(depth_const(g, q), a, b) * kTauFixed);
             }
-            if (sum > (double)kShadowTauCutoff) return 0.0f;  // expf(-float(sum)) is exactly 0 from here on
+            if (sum > tau_cutoff_fixed()) return 0.0f;  // expf(-x) is exactly 0 from here on
         }
         if (sp == 0) break;
         cur = stack[--sp];
     }
-    return expf(-(float)sum);
+    return sum > tau_cutoff_fixed() ? 0.0f : expf(-(float)((double)sum / kTauFixed));
 }
 
 // ------------------------------------------------------------------------------------------

@@ -69,6 +69,8 @@ size_t wave_pool_bytes(int P);
 void wave_pool_carve(WavePool* q, int P, void* base);
 // runs the whole pass (a.work_count samples) ; returns the number of iterations enqueued, < 0 on CUDA error
 constexpr int kMaxWaveParts = 4;
+// finishes the n_live paths listed in q.listTs (their free-flight rays pending) in one kernel, one thread per path (vr_kernels.cu)
+void launch_wave_drain(const RenderArgs& a, const WavePool& q, unsigned int n_live, cudaStream_t s);
 // instantiated CUDA graphs of the per-part iteration batches, kept between renders (a context owns one)
 struct WaveGraphCache;
 WaveGraphCache* wave_graph_cache_create();

@@ -221,6 +221,60 @@ __global__ void __launch_bounds__(kBlockThreads) path_kernel(const __grid_consta
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// drain of a wavefront pass.  Once every sample has been issued, the last paths need ~100 more iterations of the
+// kernel chain at a few per cent pool occupancy, each bounded by its own latency (~1.5 ms per iteration): 10 % of a
+// C2 step.  The paths still alive are finished here instead, one thread per path, bounce after bounce without a
+// kernel boundary.  What stays exposed is the latency of the longest path (~95 bounces at ~1 ms each: one path per
+// warp was measured and is no faster), so the gain is 1 % at C2 but 25-40 % for small renders (inverse mode at low spp),
+// where the drain is most of a pass.  A slot whose free-flight ray is pending holds exactly this engine's path state (origin, direction,
+// throughput, radiance, bounce count, the stream state BEFORE the target draw), and both engines run the same device
+// functions on it, so a sample's value does not depend on where its path was finished.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlockThreads) wave_drain_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q,
+                                                                   unsigned int n_live) {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int n_scatter = 0, n_shadow = 0, n_hits = 0, n_over = 0;
+    if (i < n_live) {
+        const unsigned int p = Q.listTs[i];
+        const float4 ro = Q.ray[kSlotF4 * (size_t)p], rd = Q.ray[kSlotF4 * (size_t)p + 1];
+        const float4 s0 = Q.ps01[kSlotF4 * (size_t)p];
+        const uint4 s1 = reinterpret_cast<const uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1];
+        PathState ps;
+        ps.rng_state = (uint64_t)s1.x | ((uint64_t)s1.y << 32);
+        ps.o = mk3(ro.x, ro.y, ro.z); ps.d = mk3(rd.x, rd.y, rd.z);
+        ps.L0 = s0.x; ps.L1 = s0.y; ps.L2 = s0.z; ps.thr = s0.w;
+        ps.work = s1.z; ps.bounce = (int)s1.w;
+        int si;
+        lane_xy(A, ps.work, &ps.x, &ps.y, &si);
+        LocalStore<kLocalCap> st;
+        int r;
+        do { r = path_vertex(A, ps, st, n_scatter, n_shadow, n_hits); } while (r == 0);
+        --n_scatter;   // the pending ray was counted when the wavefront published it
+        if (r == 1) {
+            A.sampleL[ps.work] = make_float4(ps.L0, ps.L1, ps.L2, (float)ps.bounce);
+        } else {       // more overlaps than the local store holds: the whole sample is re-traced by the arena kernel
+            A.overflow_list[atomicAdd(A.overflow_count, 1u)] = ps.work + A.work_base;
+            ++n_over;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_scatter += __shfl_down_sync(0xffffffffu, n_scatter, o);
+        n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+        n_hits += __shfl_down_sync(0xffffffffu, n_hits, o);
+        n_over += __shfl_down_sync(0xffffffffu, n_over, o);
+    }
+    if ((threadIdx.x & 31u) == 0) {
+        if (n_scatter) atomicAdd(A.stats + ST_SCATTER_RAYS, (unsigned long long)(long long)(int)n_scatter);
+        if (n_shadow) atomicAdd(A.stats + ST_SHADOW_RAYS, (unsigned long long)n_shadow);
+        if (n_hits) atomicAdd(A.stats + ST_HITS, (unsigned long long)n_hits);
+        if (n_over) atomicAdd(A.stats + ST_OVERFLOW, (unsigned long long)n_over);
+    }
+}
+void launch_wave_drain(const RenderArgs& a, const WavePool& q, unsigned int n_live, cudaStream_t s) {
+    if (n_live) wave_drain_kernel<<<(n_live + kBlockThreads - 1) / kBlockThreads, kBlockThreads, 0, s>>>(a, q, n_live);
+}
+
 constexpr size_t kWarpKernelSmem = sizeof(WarpShared) * (kBlockThreads / 32);
 int path_kernel_blocks_per_sm(bool arena) {
     int nb = 0;

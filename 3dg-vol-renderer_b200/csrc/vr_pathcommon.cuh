@@ -5,9 +5,7 @@
 namespace vr {
 
 constexpr int kMaxLeafDev = 1;                 // == vr::kMaxLeaf of the host builder (vr_bvh.h)
-constexpr double kTauFixed = 1099511627776.0;  // 2^40: shadow optical depth in fixed point
 enum { RAY_SCATTER = 0, RAY_SHADOW = 1, RAY_LIGHT = 2 };   // RAY_LIGHT: shadow ray to a point light with a direction grid
-__device__ __forceinline__ long long tau_cutoff_fixed() { return (long long)((double)kShadowTauCutoff * kTauFixed); }
 
 __device__ __forceinline__ void lane_xy(const RenderArgs& A, unsigned int work, int* x, int* y, int* si) {
     const unsigned int p = A.pixel_base + work / (unsigned int)A.spp;

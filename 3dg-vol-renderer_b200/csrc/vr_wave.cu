@@ -19,6 +19,7 @@
 // The per-sample arithmetic is the same device code as the other engines (vr_device.cuh).
 #include <algorithm>
 #include <cstdio>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -819,6 +820,9 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     } part[kMaxWaveParts];
     static const bool graph_env = !(getenv("VR_WAVE_GRAPH") && getenv("VR_WAVE_GRAPH")[0] == '0');
     const bool use_graph = graph_env && !prof && graphs != nullptr;   // the profile mode synchronises inside an iteration
+    static const bool timeline = getenv("VR_WAVE_TIMELINE") != nullptr;   // stderr: per batch (part, ms since pass start, live rays, samples issued)
+    const auto tl0 = std::chrono::steady_clock::now();
+    static const bool drain_on = !(getenv("VR_WAVE_DRAIN") && getenv("VR_WAVE_DRAIN")[0] == '0');
     static const int defer_env = getenv("VR_WAVE_DEFER") ? atoi(getenv("VR_WAVE_DEFER")) : -1;   // 0 / 1 force, default adaptive
     const int P_part = P_total / parts;
     const size_t pool_stride = wave_pool_bytes(P_part);
@@ -943,8 +947,18 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             // deferring the iterative solves redoes those slots' walk: it pays while they are few (sparse mixtures: 8 % of the
             // general slots at C2), not when a third of all slots need one (C3, heavy overlap)
             if (defer_env < 0 && pt.defer && pt.h[WC_SUM_GENERAL] > 4096u && 5ull * pt.h[WC_SUM_DEFERRED] > pt.h[WC_SUM_GENERAL]) pt.defer = false;
+            if (timeline)
+                fprintf(stderr, "[timeline] part %d iter %d t %.3f ms live %u issued %u of %u\n", i, iters,
+                        std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tl0).count(), pt.h[WC_NTS], std::min(pt.h[WC_NEXT_SAMPLE], pt.a.work_count), pt.a.work_count);
             const bool more_samples = pt.h[WC_NEXT_SAMPLE] < pt.a.work_count;
             if (pt.h[WC_NTS] == 0 && (pt.h[WC_NC] == 0 || !more_samples)) pt.done = true;
+            // every sample is out and few paths are left: finish them in one kernel instead of ~100 more iterations
+            // that are bounded by their own latency (see wave_drain_kernel)
+            else if (drain_on && !more_samples && pt.h[WC_NTS] <= (unsigned int)pt.q.P / 8u) {
+                launch_wave_drain(pt.a, pt.q, pt.h[WC_NTS], pt.st);
+                ++*launches;
+                pt.done = true;
+            }
         }
         if (iters > (1 << 24)) break;
     }
