@@ -18,9 +18,13 @@ struct RenderArgs {
     int solver, min_bounces;
     int x0, y0, win_w;     // owned pixel p -> x = x0 + p % win_w, y = y0 + (p / win_w) * part_count + part_rank
     int part_rank, part_count;
-    unsigned int pixel_base;      // first owned pixel of this pass (of this part of the pass, wavefront engine)
-    unsigned int work_base;       // wavefront engine: id of this part's first sample within the pass (0 otherwise)
-    unsigned int work_count;      // samples in this pass = pass pixels * spp
+    unsigned int pixel_base;      // first owned pixel of this pass
+    unsigned int work_base;       // added to a sample id when it is listed for the re-trace kernel (0: ids are pass-wide)
+    unsigned int work_count;      // samples in this pass = pass pixels * spp (wavefront engine: of this PART of the pass)
+    // wavefront engine: the parts of a pass own interleaved chunks of wave_chunk consecutive pass pixels (one window row),
+    // chunk c belongs to part c % wave_parts; a part counts its samples 0..work_count-1 and wave_global_work() maps them
+    // to pass-wide sample ids (what sampleL, the overflow list and lane_xy are indexed by)
+    unsigned int wave_part, wave_parts, wave_chunk;
     unsigned int* counter;        // work-fetch counter of this pass
     const unsigned int* worklist; // nullptr: work ids 0..work_count-1; else ids taken from this list (re-trace kernel)
     float4* sampleL;              // per-sample radiance of this pass, [pass pixel][si]

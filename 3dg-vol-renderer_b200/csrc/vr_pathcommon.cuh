@@ -14,6 +14,15 @@ __device__ __forceinline__ void lane_xy(const RenderArgs& A, unsigned int work, 
     *y = A.y0 + (int)(p / (unsigned int)A.win_w) * A.part_count + A.part_rank;
 }
 
+// part-local sample id -> pass-wide sample id (RenderArgs::wave_chunk); the samples of a pixel stay consecutive
+__device__ __forceinline__ unsigned int wave_global_work(const RenderArgs& A, unsigned int idx) {
+    if (A.wave_parts <= 1u) return idx;
+    const unsigned int spp = (unsigned int)A.spp;
+    const unsigned int lp = idx / spp, si = idx - lp * spp;
+    const unsigned int k = lp / A.wave_chunk, r = lp - k * A.wave_chunk;
+    return ((k * A.wave_parts + A.wave_part) * A.wave_chunk + r) * spp + si;
+}
+
 // heavy helpers are kept out of line ONCE so the scheduler + traversal loop stays compact
 static __device__ __noinline__ f3 sample_direction_ni(uint64_t* state) {
     Pcg rng; rng.state = *state; rng.inc = 3;

@@ -484,7 +484,8 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
         if (act && idx < A.work_count) {
             p = Q.listC[i];
             int x, y, si;
-            lane_xy(A, idx, &x, &y, &si);
+            const unsigned int work = wave_global_work(A, idx);
+            lane_xy(A, work, &x, &y, &si);
             Pcg rng; rng.seed(derive_path_seed(x, y, si), 1);
             const int n = A.nsq;
             const int sx = si % n, sy = si / n;
@@ -494,7 +495,7 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
             float target;
             publish_scatter_ray(Q, p, ray.o, ray.d, rng.state, &target);
             Q.ps01[kSlotF4 * (size_t)p] = make_float4(0.f, 0.f, 0.f, 1.0f);
-            reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), idx, 0u);
+            reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), work, 0u);
             ++cn.scatter;
             to_trav = true;
         }
@@ -780,7 +781,7 @@ __global__ void wave_init_kernel(const __grid_constant__ WavePool Q, unsigned in
 // ------------------------------------------------------------------------------------------
 // host driver of one pass
 // ------------------------------------------------------------------------------------------
-// One pass = a.work_count samples.  The pass is cut into `parts` pixel ranges, each with its own pool of slots, counters
+// One pass = a.work_count samples.  The pass is cut into `parts` interleaved sets of pixel rows, each with its own pool of slots, counters
 // and stream; the kernel chains of the parts are independent, so the tail of one part's kernel (persistent warps waiting
 // for the last rays, 9-15 % of SM cycles per kernel in profiles/r01_v7) is filled by the other part's kernels.
 // A graph is reusable when every kernel argument and grid of the batch is byte-identical (repeated renders of one
@@ -823,7 +824,13 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     static const bool timeline = getenv("VR_WAVE_TIMELINE") != nullptr;   // stderr: per batch (part, ms since pass start, live rays, samples issued)
     const auto tl0 = std::chrono::steady_clock::now();
     static const bool drain_on = !(getenv("VR_WAVE_DRAIN") && getenv("VR_WAVE_DRAIN")[0] == '0');
+    static const unsigned int drain_div = getenv("VR_WAVE_DRAIN_DIV") ? (unsigned int)std::max(1, atoi(getenv("VR_WAVE_DRAIN_DIV"))) : 8u;   // hand-over below P / drain_div live paths
     static const int defer_env = getenv("VR_WAVE_DEFER") ? atoi(getenv("VR_WAVE_DEFER")) : -1;   // 0 / 1 force, default adaptive
+    // the parts own interleaved rows of the pass (neighbouring rows cost the same, halves of an image do not: with
+    // contiguous halves one part of a C2 pass ran alone for its last 8 %)
+    unsigned int chunk = (unsigned int)std::max(1, a_all.win_w);
+    if ((pass_pixels + chunk - 1u) / chunk < 4u * (unsigned int)parts) chunk = std::max(1u, pass_pixels / (4u * (unsigned int)parts));
+    const unsigned int n_chunks = (pass_pixels + chunk - 1u) / chunk;
     const int P_part = P_total / parts;
     const size_t pool_stride = wave_pool_bytes(P_part);
     cudaEvent_t fork;
@@ -831,13 +838,15 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     if (parts > 1) cudaEventRecord(fork, s);
     for (int i = 0; i < parts; ++i) {
         Part& pt = part[i];
-        const unsigned int px0 = (unsigned int)((unsigned long long)pass_pixels * i / parts), px1 = (unsigned int)((unsigned long long)pass_pixels * (i + 1) / parts);
+        // chunks i, i + parts, ... of the pass's pixels (only the last chunk of the pass can be short)
+        const unsigned int owned = (unsigned int)i < n_chunks ? (n_chunks - (unsigned int)i + (unsigned int)parts - 1u) / (unsigned int)parts : 0u;
+        unsigned int part_pixels = owned * chunk;
+        if (owned && (n_chunks - 1u) % (unsigned int)parts == (unsigned int)i) part_pixels -= n_chunks * chunk - pass_pixels;
         pt.a = a_all;
         pt.defer = defer_env != 0;
-        pt.a.pixel_base = a_all.pixel_base + px0;
-        pt.a.work_base = px0 * (unsigned int)a_all.spp;
-        pt.a.work_count = (px1 - px0) * (unsigned int)a_all.spp;
-        pt.a.sampleL = a_all.sampleL + (size_t)px0 * a_all.spp;
+        pt.a.work_base = 0;
+        pt.a.work_count = part_pixels * (unsigned int)a_all.spp;
+        pt.a.wave_part = (unsigned int)i; pt.a.wave_parts = (unsigned int)parts; pt.a.wave_chunk = chunk;
         wave_pool_carve(&pt.q, P_part, (char*)pool_mem + pool_stride * i);
         pt.st = parts > 1 ? part_streams[i] : s;
         pt.h = h_cnt_all + kWaveCounters * i;
@@ -954,10 +963,15 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             if (pt.h[WC_NTS] == 0 && (pt.h[WC_NC] == 0 || !more_samples)) pt.done = true;
             // every sample is out and few paths are left: finish them in one kernel instead of ~100 more iterations
             // that are bounded by their own latency (see wave_drain_kernel)
-            else if (drain_on && !more_samples && pt.h[WC_NTS] <= (unsigned int)pt.q.P / 8u) {
+            else if (drain_on && !more_samples && pt.h[WC_NTS] <= (unsigned int)pt.q.P / drain_div) {
                 launch_wave_drain(pt.a, pt.q, pt.h[WC_NTS], pt.st);
                 ++*launches;
                 pt.done = true;
+                if (timeline) {
+                    cudaStreamSynchronize(pt.st);
+                    fprintf(stderr, "[timeline] part %d drained %u paths, t %.3f ms\n", i, pt.h[WC_NTS],
+                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tl0).count());
+                }
             }
         }
         if (iters > (1 << 24)) break;
