@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 #include "vr_bvh.h"
 #include "vr_lightgrid.h"
@@ -28,7 +29,25 @@ vr::SceneDev vr_context::scene_dev() const {
     return S;
 }
 
+// speculative light-grid build (vr_context.h): inputs are copies, so the job outlives any change of the context's vectors
+struct vr_context::LightGridJob {
+    std::vector<float> lo, hi, lpos;
+    int n = 0, nl = 0, res = 0;
+    vr::LightGridHost grid;
+    std::thread worker;
+};
+
 namespace vr {
+void cancel_light_grid_job(vr_context* c) {
+    if (!c || !c->lg_job) return;
+    if (c->lg_job->worker.joinable()) c->lg_job->worker.join();
+    delete c->lg_job;
+    c->lg_job = nullptr;
+}
+__global__ void remap_entries_kernel(uint32_t* __restrict__ gi, size_t count, const uint32_t* __restrict__ leaf_of_orig) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) gi[i] = __ldg(leaf_of_orig + gi[i]);
+}
 int fail(vr_context* c, int code, const std::string& msg) {
     if (c) c->err = msg;
     return code;
@@ -78,6 +97,7 @@ int vr_create(vr_context** out, int device_id) {
 
 void vr_destroy(vr_context* ctx) {
     if (!ctx) return;
+    vr::cancel_light_grid_job(ctx);
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     sfd_destroy(ctx);
@@ -105,9 +125,9 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
-    if (!strcmp(name, "light_grid")) { ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
+    if (!strcmp(name, "light_grid")) { vr::cancel_light_grid_job(ctx); ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "light_grid_min_samples")) { ctx->light_grid_min_samples = value; return VR_OK; }
-    if (!strcmp(name, "light_grid_res")) { ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
+    if (!strcmp(name, "light_grid_res")) { vr::cancel_light_grid_job(ctx); ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "wave_parts")) { ctx->wave_parts = std::max(1, std::min(kMaxWaveParts, (int)value)); ctx->wavepool.release(); return VR_OK; }
     if (!strcmp(name, "wave_slots")) { ctx->wave_slots = std::max(0, (int)value); ctx->wavepool.release(); return VR_OK; }
     return fail(ctx, VR_ERR_INVALID_ARGUMENT, std::string("unknown option ") + name);
@@ -175,6 +195,7 @@ int vr_set_lights(vr_context* ctx, int nl, const float* pos3, const float* inten
         VR_CUDA(cudaMemcpyAsync(ctx->lint.p, intensity3, (size_t)nl * 12, cudaMemcpyHostToDevice, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
     }
+    vr::cancel_light_grid_job(ctx);   // built for the previous lights
     ctx->h_lpos.assign(pos3, pos3 + (size_t)3 * std::max(nl, 0));
     ctx->lg_valid = false;
     ctx->nl = nl;
@@ -201,6 +222,7 @@ int vr_set_camera(vr_context* ctx, int kind, const float* pos3, const float* vie
 namespace vr {
 // Sigma^-1 / norm / boxes on the device, hierarchy on the host (vr_bvh.cpp), permutation on the device
 int set_gmm_from_device(vr_context* ctx, int n) {
+    cancel_light_grid_job(ctx);
     ctx->has_gmm = false;
     ctx->rec_valid = false;
     ctx->lg_valid = false;
@@ -222,6 +244,14 @@ int set_gmm_from_device(vr_context* ctx, int n) {
         VR_CUDA(cudaMemcpyAsync(lo.data(), ctx->box_lo.p, lo.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(hi.data(), ctx->box_hi.p, hi.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->lg_speculate && ctx->use_light_grid && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl) {
+            vr_context::LightGridJob* job = new vr_context::LightGridJob;
+            job->lo = lo; job->hi = hi; job->lpos = ctx->h_lpos; job->n = n; job->nl = ctx->nl; job->res = ctx->lg_res;
+            job->worker = std::thread([job] {
+                build_light_grids(job->n, job->lo.data(), job->hi.data(), nullptr, job->nl, job->lpos.data(), job->res, &job->grid);
+            });
+            ctx->lg_job = job;
+        }
         BvhBuildResult bvh;
         build_bvh(n, lo.data(), hi.data(), &bvh);
         if (bvh.max_depth > kStackDepth - 2)
@@ -257,9 +287,15 @@ int ensure_light_grids(vr_context* ctx) {
     VR_CUDA(ctx->lg_start.ensure(16)); VR_CUDA(ctx->lg_gi.ensure(16)); VR_CUDA(ctx->lg_dmin.ensure(16));
     if (ctx->use_light_grid && ctx->n > 0 && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl &&
         (int)ctx->h_leaf_of_orig.size() == ctx->n) {
-        LightGridHost g;
-        build_light_grids(ctx->n, ctx->h_box_lo.data(), ctx->h_box_hi.data(), ctx->h_leaf_of_orig.data(), ctx->nl, ctx->h_lpos.data(),
-                          ctx->lg_res, &g);
+        LightGridHost g_sync;
+        const bool speculated = ctx->lg_job != nullptr && ctx->lg_job->n == ctx->n && ctx->lg_job->nl == ctx->nl && ctx->lg_job->res == ctx->lg_res;
+        if (speculated) {
+            if (ctx->lg_job->worker.joinable()) ctx->lg_job->worker.join();
+        } else {
+            build_light_grids(ctx->n, ctx->h_box_lo.data(), ctx->h_box_hi.data(), ctx->h_leaf_of_orig.data(), ctx->nl, ctx->h_lpos.data(),
+                              ctx->lg_res, &g_sync);
+        }
+        const LightGridHost& g = speculated ? ctx->lg_job->grid : g_sync;
         if (g.mask) {
             VR_CUDA(ctx->lg_start.ensure(g.cell_start.size() * 4));
             VR_CUDA(ctx->lg_gi.ensure(std::max<size_t>(g.entry_gi.size(), 1) * 4));
@@ -268,11 +304,15 @@ int ensure_light_grids(vr_context* ctx) {
             if (!g.entry_gi.empty()) {
                 VR_CUDA(cudaMemcpyAsync(ctx->lg_gi.p, g.entry_gi.data(), g.entry_gi.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
                 VR_CUDA(cudaMemcpyAsync(ctx->lg_dmin.p, g.entry_dmin.data(), g.entry_dmin.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+                if (speculated)   // original -> leaf-order indices
+                    remap_entries_kernel<<<(unsigned int)((g.entry_gi.size() + 255) / 256), 256, 0, ctx->stream>>>(
+                        ctx->lg_gi.as<uint32_t>(), g.entry_gi.size(), ctx->leaf_of_orig.as<uint32_t>());
             }
             VR_CUDA(cudaStreamSynchronize(ctx->stream));
             ctx->lg_mask = g.mask;
         }
     }
+    cancel_light_grid_job(ctx);
     ctx->lg_valid = true;
     return VR_OK;
 }

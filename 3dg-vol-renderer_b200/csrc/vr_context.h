@@ -51,6 +51,12 @@ struct vr_context {
     uint32_t lg_mask = 0;
     int use_light_grid = 1;
     double light_grid_min_samples = 16.0e6;       // renders smaller than this skip the grids (build cost > gain)
+    // speculative build: when the last render used grids, vr_set_gmm* starts their build on worker threads NEXT TO the
+    // hierarchy build (boxes and lights are all it needs; entries carry original indices, mapped to leaf order by a
+    // device kernel after the upload), so a set_gmm + render pair no longer pays for it in sequence
+    struct LightGridJob;                          // vr_api.cu
+    LightGridJob* lg_job = nullptr;
+    bool lg_speculate = false;
     // ---- sphere mixture
     bool has_smm = false;
     int n_spheres = 0;
@@ -73,7 +79,7 @@ struct vr_context {
     double max_pass_samples = 268435456.0;         // 2^28 samples = 4 GiB of per-sample radiance
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
     int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
-    int wave_slots = 0;                            // 0 = 24576 per SM (sweep in profiles/r01_tuning.md)
+    int wave_slots = 0;                            // 0 = 32768 per SM (sweeps in profiles/r01_tuning.md, r01_v11/)
     int wave_parts = 2;                            // independent parts (own pool + stream) a big pass is cut into
     cudaStream_t wave_streams[vr::kMaxWaveParts] = {nullptr, nullptr, nullptr, nullptr};
     vr::WaveGraphCache* wave_graphs = nullptr;     // CUDA graphs of the iteration batches, reused while the launch arguments stay the same
@@ -89,6 +95,7 @@ int fail(vr_context* c, int code, const std::string& msg);
 int cuda_fail(vr_context* c, cudaError_t e, const char* what);
 int render_device_impl(vr_context* c, const vr_render_params* p, vr_render_stats* st);
 int set_gmm_from_device(vr_context* c, int n);
+void cancel_light_grid_job(vr_context* c);  // vr_api.cu: joins and drops a speculative grid build
 int ensure_light_grids(vr_context* c);  // vr_api.cu  // mean3/cov6/density/albedo device buffers already filled
 void sfd_destroy(vr_context* c);
 }  // namespace vr

@@ -102,7 +102,7 @@ static bool build_one_light(int n, const float* lo, const float* hi, const uint3
             for (int w = r.w0; w <= r.w1; ++w)
                 for (int u = r.u0; u <= r.u1; ++u) {
                     const uint32_t at = count[((size_t)r.face * res + w) * res + u]++;
-                    (*entry_gi)[at] = leaf_of_orig[g];
+                    (*entry_gi)[at] = leaf_of_orig ? leaf_of_orig[g] : g;
                     (*entry_dmin)[at] = dmin[g];
                 }
         }

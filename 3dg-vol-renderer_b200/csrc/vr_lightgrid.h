@@ -26,7 +26,8 @@ struct LightGridHost {
 };
 
 // lo/hi: 3*n floats (boxes in ORIGINAL order), leaf_of_orig: n (original index -> leaf-order index),
-// lpos: 3*nl floats.  Lights beyond 32 get no grid.  Deterministic.
+// lpos: 3*nl floats.  Lights beyond 32 get no grid.  Deterministic.  leaf_of_orig == nullptr: entries keep ORIGINAL
+// indices (the speculative build of vr_api.cu runs next to the hierarchy build and maps them on the device afterwards).
 void build_light_grids(int n, const float* lo, const float* hi, const uint32_t* leaf_of_orig, int nl, const float* lpos, int res,
                        LightGridHost* out);
 

@@ -51,6 +51,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     // the per-light grids cost ~1 ms per 1000 components to build on the host: worth it from ~16 M samples on
     const unsigned long long render_samples = (unsigned long long)(p->x1 - p->x0) * (unsigned long long)owned_rows(p) * (unsigned long long)p->spp;
     const bool use_grids = ctx->engine == 0 && ctx->use_light_grid && (double)render_samples >= ctx->light_grid_min_samples;
+    ctx->lg_speculate = use_grids;   // the next vr_set_gmm* builds the grids next to the hierarchy
     if (use_grids) { rc = ensure_light_grids(ctx); if (rc) return rc; }
     RenderArgs A{};
     A.scene = ctx->scene_dev();
@@ -102,9 +103,9 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             VR_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(unsigned int) * 4, s));
             VR_CUDA(cudaEventRecord(ctx->ev[2], s));
             if (ctx->engine == 0) {
-                const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 24576;
+                const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 32768;
                 // big passes are cut into independent parts on their own streams so that kernel tails overlap
-                int parts = (unsigned long long)A.work_count >= 4ULL * (unsigned long long)P ? ctx->wave_parts : 1;
+                int parts = (unsigned long long)A.work_count >= 4ULL * (unsigned long long)std::min(P, ctx->num_sms * 24576) ? ctx->wave_parts : 1;
                 parts = std::max(1, std::min(parts, kMaxWaveParts));
                 VR_CUDA(ctx->wavepool.ensure(wave_pool_bytes(P / parts) * parts));
                 for (int i = 0; i < parts; ++i)

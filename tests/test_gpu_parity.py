@@ -270,6 +270,39 @@ def test_light_grid_is_only_a_candidate_source(ctx, ob, vr, scenegen):
     ctx.set_option("light_grid", 1); ctx.set_option("light_grid_res", 256); ctx.set_option("light_grid_min_samples", 16e6)
 
 
+def test_speculative_light_grid_build_equals_lazy_build(ctx, ob, vr, scenegen):
+    """Once a render has used the grids, vr_set_gmm builds the next ones on worker threads next to the hierarchy build
+    (entries in original order, mapped to leaf order on the device).  The set_gmm + render pair of a user loop (bench e2e,
+    the S + 1 renders of an SFD iteration) must give the bits of the lazy build and of a render without grids, also when
+    the mixture changes between calls or the lights are replaced while a build is in flight."""
+    a = scenegen.generate(2500, 21, nonuniform=True, diameter_range=(0.02, 0.09))
+    b = scenegen.generate(1800, 22, nonuniform=False, diameter_range=(0.02, 0.09))
+    p = vr.Context.params(vr.INTEGRATOR_MS, 96, 64, 16)
+    ctx.set_option("light_grid_min_samples", 0)
+    ref = {}
+    for name, sc in (("a", a), ("b", b)):          # no grids at all
+        ctx.set_option("light_grid", 0)
+        setup(ctx, ob, vr, scenegen, None, "pin", scene=sc)
+        ref[name] = ctx.render(p)[0]
+    ctx.set_option("light_grid", 1)
+    setup(ctx, ob, vr, scenegen, None, "pin", scene=a)
+    assert np.array_equal(ctx.render(p)[0], ref["a"])          # lazy build; arms the speculation
+    for name, sc in (("a", a), ("b", b), ("b", b), ("a", a)):
+        ctx.set_gmm(sc)                                          # lights unchanged: the build runs next to the hierarchy build
+        assert np.array_equal(ctx.render(p)[0], ref[name]), name
+    ctx.set_gmm(b)                                               # build in flight ...
+    ctx.set_lights(a["lights"][:2], ENV)                         # ... for lights that are replaced: dropped, rebuilt lazily
+    img2 = ctx.render(p)[0]
+    ctx.set_option("light_grid", 0)
+    ctx.set_gmm(b)
+    assert np.array_equal(ctx.render(p)[0], img2)
+    ctx.set_gmm(a)                                               # a job nobody consumes (small render below, grids off)
+    ctx.set_option("light_grid", 1); ctx.set_option("light_grid_min_samples", 16e6)
+    ctx.set_gmm(a)
+    assert np.isfinite(ctx.render(p)[0]).all()                   # small render without grids: the pending build is simply dropped
+    ctx.set_lights(a["lights"], ENV)
+
+
 # ------------------------------------------------------------------------------------------------
 # edge cases and size-independent properties
 # ------------------------------------------------------------------------------------------------
