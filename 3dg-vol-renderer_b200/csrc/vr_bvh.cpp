@@ -4,6 +4,10 @@
 #include <algorithm>
 #include <cmath>
 #include <atomic>
+#include <cstdlib>
+#ifdef __linux__
+#include <sched.h>
+#endif
 #include <limits>
 #include <thread>
 
@@ -183,7 +187,14 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
                 subs[t].max_depth = lb.max_depth; subs[t].max_leaf = lb.max_leaf;
             }
         };
-        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        // host cores this process may use, shared with the other ranks of the node when launched by torchrun (one process
+        // per GPU: 8 ranks x 16 workers on a 16-core host only add scheduling latency to a ~1 ms build)
+        unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+#ifdef __linux__
+        cpu_set_t cpus;
+        if (sched_getaffinity(0, sizeof(cpus), &cpus) == 0) hw = std::max(1u, (unsigned)CPU_COUNT(&cpus));
+#endif
+        if (const char* lws = std::getenv("LOCAL_WORLD_SIZE")) hw = std::max(1u, hw / (unsigned)std::max(1, std::atoi(lws)));
         const size_t nthreads = std::min<size_t>(std::min<size_t>(tasks.size(), hw), 16);
         std::vector<std::thread> pool;
         for (size_t t = 1; t < nthreads; ++t) pool.emplace_back(work);
