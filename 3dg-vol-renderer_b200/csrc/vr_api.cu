@@ -195,9 +195,15 @@ int vr_set_lights(vr_context* ctx, int nl, const float* pos3, const float* inten
         VR_CUDA(cudaMemcpyAsync(ctx->lint.p, intensity3, (size_t)nl * 12, cudaMemcpyHostToDevice, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
     }
-    vr::cancel_light_grid_job(ctx);   // built for the previous lights
-    ctx->h_lpos.assign(pos3, pos3 + (size_t)3 * std::max(nl, 0));
-    ctx->lg_valid = false;
+    // the direction grids depend on the light POSITIONS only: setting the same lights again (the C++ Integrator::render does
+    // so on every call) keeps the grids and a build in flight
+    const bool same_positions = nl == ctx->nl && ctx->h_lpos.size() == (size_t)3 * std::max(nl, 0) &&
+                                (nl == 0 || memcmp(ctx->h_lpos.data(), pos3, sizeof(float) * 3 * (size_t)nl) == 0);
+    if (!same_positions) {
+        vr::cancel_light_grid_job(ctx);   // built for the previous lights
+        ctx->h_lpos.assign(pos3, pos3 + (size_t)3 * std::max(nl, 0));
+        ctx->lg_valid = false;
+    }
     ctx->nl = nl;
     if (env_rgb) { ctx->env[0] = env_rgb[0]; ctx->env[1] = env_rgb[1]; ctx->env[2] = env_rgb[2]; }
     return VR_OK;

@@ -346,6 +346,29 @@ def test_window_and_row_partition_are_exact(ctx, ob, vr, scenegen):
     assert np.array_equal(multi, full) and st["kernel_launches"] > 10
 
 
+def test_wave_parts_do_not_change_the_image(ctx, ob, vr, scenegen):
+    """A big pass is cut into parts that own interleaved chunks of the pass's pixels (rows; shorter chunks when the pass has
+    few rows, a short last chunk when the pass does not end on a row).  The sample ids the parts produce must be the
+    pass-wide ones: the image with 1, 2, 3 and 4 parts is the same, bit for bit, as is the one of many small passes."""
+    setup(ctx, ob, vr, scenegen, "rand2k", "pin")
+    ctx.set_option("wave_slots", 148 * 64)             # parts are used from 4 * slots = 37 888 samples on: small renders exercise them
+    for W, H, spp, win in ((96, 64, 16, None), (640, 3, 25, None), (97, 41, 16, (3, 2, 90, 39))):
+        imgs = []
+        for parts in (1, 2, 3, 4):
+            ctx.set_option("wave_parts", parts)
+            img = np.full((H, W, 3), -1.0, np.float32)
+            ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp, window=win), out=img)
+            imgs.append(img)
+            assert np.array_equal(img, imgs[0]), (W, H, spp, parts)
+        ctx.set_option("wave_parts", 3)
+        ctx.set_option("max_pass_samples", 2500 * spp)      # passes of 2500 pixels: they begin and end in the middle of a row
+        img = np.full((H, W, 3), -1.0, np.float32)
+        ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp, window=win), out=img)
+        ctx.set_option("max_pass_samples", 2 ** 28)
+        assert np.array_equal(img, imgs[0]), (W, H, spp, "passes")
+    ctx.set_option("wave_parts", 2); ctx.set_option("wave_slots", 0)
+
+
 def test_full_size_config1_properties(ctx, ob, vr, scenegen):
     """BASELINE config 1 (1k Gaussians, 512^2, 64 spp, single scatter) at full size: deterministic,
     radiance finite and bounded, and a window of it equals the oracle's."""
