@@ -3,6 +3,9 @@
 // VR_ERR_NO_DEVICE and nothing else can be called.
 #include <algorithm>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -228,6 +231,15 @@ int vr_set_camera(vr_context* ctx, int kind, const float* pos3, const float* vie
 namespace vr {
 // Sigma^-1 / norm / boxes on the device, hierarchy on the host (vr_bvh.cpp), permutation on the device
 int set_gmm_from_device(vr_context* ctx, int n) {
+    static const bool time_setup = getenv("VR_TIME_SETUP") != nullptr;   // stderr: host time of each phase of the scene setup
+    const auto ts0 = std::chrono::steady_clock::now();
+    double ts_prev = 0.0;
+    auto lap = [&](const char* what) {
+        if (!time_setup) return;
+        const double t = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ts0).count();
+        fprintf(stderr, "[setup] %-28s %7.3f ms\n", what, t - ts_prev);
+        ts_prev = t;
+    };
     cancel_light_grid_job(ctx);
     ctx->has_gmm = false;
     ctx->rec_valid = false;
@@ -250,6 +262,7 @@ int set_gmm_from_device(vr_context* ctx, int n) {
         VR_CUDA(cudaMemcpyAsync(lo.data(), ctx->box_lo.p, lo.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(hi.data(), ctx->box_hi.p, hi.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        lap("inverse covariances, boxes");
         if (ctx->lg_speculate && ctx->use_light_grid && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl) {
             vr_context::LightGridJob* job = new vr_context::LightGridJob;
             job->lo = lo; job->hi = hi; job->lpos = ctx->h_lpos; job->n = n; job->nl = ctx->nl; job->res = ctx->lg_res;
@@ -260,6 +273,7 @@ int set_gmm_from_device(vr_context* ctx, int n) {
         }
         BvhBuildResult bvh;
         build_bvh(n, lo.data(), hi.data(), &bvh);
+        lap("hierarchy build");
         if (bvh.max_depth > kStackDepth - 2)
             return fail(ctx, VR_ERR_UNSUPPORTED, "hierarchy deeper than the traversal stack");
         VR_CUDA(ctx->nodes.ensure(bvh.nodes.size() * sizeof(BvhNode)));
@@ -267,6 +281,7 @@ int set_gmm_from_device(vr_context* ctx, int n) {
         std::vector<BvhNodeQ> qn;
         BvhQuantGrid grid;
         quantize_bvh(bvh, &grid, &qn);
+        lap("quantisation");
         for (int k = 0; k < 3; ++k) { ctx->qorg[k] = grid.org[k]; ctx->qcell[k] = grid.cell[k]; }
         VR_CUDA(ctx->qnodes.ensure(qn.size() * sizeof(BvhNodeQ)));
         VR_CUDA(cudaMemcpyAsync(ctx->qnodes.p, qn.data(), qn.size() * sizeof(BvhNodeQ), cudaMemcpyHostToDevice, ctx->stream));
@@ -280,6 +295,7 @@ int set_gmm_from_device(vr_context* ctx, int n) {
         ctx->h_box_lo.swap(lo); ctx->h_box_hi.swap(hi);
         ctx->n_nodes = (int)bvh.nodes.size();
         ctx->bvh_depth = bvh.max_depth;
+        lap("upload, permutation");
     }
     ctx->has_gmm = true;
     return VR_OK;
