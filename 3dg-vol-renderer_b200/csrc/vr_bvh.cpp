@@ -34,6 +34,7 @@ struct Builder {
     int n;
     const float* lo;
     const float* hi;
+    const float* cen;     // 3 * n centroids, 0.5f * (lo + hi)
     std::vector<uint32_t>& perm;
     std::vector<BvhNode>& nodes;
     int max_depth = 0, max_leaf = 0;
@@ -46,7 +47,6 @@ struct Builder {
         for (int i = first; i < first + count; ++i) b.grow(lo + 3 * perm[i], hi + 3 * perm[i]);
         return b;
     }
-    float centroid(uint32_t g, int axis) const { return 0.5f * (lo[3 * g + axis] + hi[3 * g + axis]); }
 
     static int leaf_code(int first, int count) { return ~((first << 3) | count); }
 
@@ -60,32 +60,52 @@ struct Builder {
         }
     }
 
-    // chooses a split of [first, first+count); returns the size of the left part (0 = make a leaf)
+    // chooses a split of [first, first+count); returns the size of the left part (0 = make a leaf).
+    // One pass over the range fills the bins of all three axes (the boxes are read once instead of three times); the
+    // sweeps then pick the cheapest (axis, bin) in axis order with a strict comparison, so ties go to the lower axis / bin.
     int split(int first, int count, const Box& box) {
         Box cb; cb.reset();
+        for (int i = first; i < first + count; ++i) { const float* c = cen + 3 * (size_t)perm[i]; cb.grow(c, c); }
+        if (count == 2 && kMaxLeaf == 1) {
+            // two components are always separated (a leaf holds one): every axis on which the centroids differ puts them
+            // into the first and the last bin at the same cost, so the lowest such axis wins and the nearer one goes left
+            for (int axis = 0; axis < 3; ++axis) {
+                if (!(cb.hi[axis] - cb.lo[axis] > 0.f)) continue;
+                if (cen[3 * (size_t)perm[first] + axis] > cen[3 * (size_t)perm[first + 1] + axis]) std::swap(perm[first], perm[first + 1]);
+                return 1;
+            }
+            return 1;   // coinciding centroids: split by index
+        }
+        float cmin[3], scale[3];
+        bool use[3];
+        for (int axis = 0; axis < 3; ++axis) {
+            const float cext = cb.hi[axis] - cb.lo[axis];
+            use[axis] = cext > 0.f;
+            cmin[axis] = cb.lo[axis];
+            scale[axis] = use[axis] ? kBins / cext : 0.f;
+        }
+        Box bb[3][kBins]; int bc[3][kBins];
+        for (int axis = 0; axis < 3; ++axis)
+            for (int b = 0; b < kBins; ++b) { bb[axis][b].reset(); bc[axis][b] = 0; }
         for (int i = first; i < first + count; ++i) {
-            float c[3] = {centroid(perm[i], 0), centroid(perm[i], 1), centroid(perm[i], 2)};
-            cb.grow(c, c);
+            const uint32_t g = perm[i];
+            const float* c = cen + 3 * (size_t)g;
+            for (int axis = 0; axis < 3; ++axis) {
+                if (!use[axis]) continue;
+                const int b = std::min(kBins - 1, std::max(0, (int)((c[axis] - cmin[axis]) * scale[axis])));
+                bb[axis][b].grow(lo + 3 * (size_t)g, hi + 3 * (size_t)g); bc[axis][b]++;
+            }
         }
         float best_cost = std::numeric_limits<float>::infinity();
         int best_axis = -1, best_bin = -1;
         for (int axis = 0; axis < 3; ++axis) {
-            float cmin = cb.lo[axis], cext = cb.hi[axis] - cb.lo[axis];
-            if (!(cext > 0.f)) continue;
-            Box bb[kBins]; int bc[kBins];
-            for (int b = 0; b < kBins; ++b) { bb[b].reset(); bc[b] = 0; }
-            float scale = kBins / cext;
-            for (int i = first; i < first + count; ++i) {
-                uint32_t g = perm[i];
-                int b = std::min(kBins - 1, std::max(0, (int)((centroid(g, axis) - cmin) * scale)));
-                bb[b].grow(lo + 3 * g, hi + 3 * g); bc[b]++;
-            }
+            if (!use[axis]) continue;
             float right_area[kBins]; int right_cnt[kBins];
             Box acc; acc.reset(); int cnt = 0;
-            for (int b = kBins - 1; b > 0; --b) { acc.grow(bb[b]); cnt += bc[b]; right_area[b] = acc.half_area(); right_cnt[b] = cnt; }
+            for (int b = kBins - 1; b > 0; --b) { acc.grow(bb[axis][b]); cnt += bc[axis][b]; right_area[b] = acc.half_area(); right_cnt[b] = cnt; }
             acc.reset(); cnt = 0;
             for (int b = 0; b < kBins - 1; ++b) {
-                acc.grow(bb[b]); cnt += bc[b];
+                acc.grow(bb[axis][b]); cnt += bc[axis][b];
                 if (cnt == 0 || right_cnt[b + 1] == 0) continue;
                 float cost = acc.half_area() * cnt + right_area[b + 1] * right_cnt[b + 1];
                 if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = b; }
@@ -101,10 +121,10 @@ struct Builder {
             // all centroids coincide: median split by index to bound the leaf size
             return count / 2;
         }
-        float cmin = cb.lo[best_axis], scale = kBins / (cb.hi[best_axis] - cb.lo[best_axis]);
-        int axis = best_axis, bin = best_bin;
+        const float pmin = cmin[best_axis], pscale = scale[best_axis];
+        const int axis = best_axis, bin = best_bin;
         auto mid = std::stable_partition(perm.begin() + first, perm.begin() + first + count, [&](uint32_t g) {
-            int b = std::min(kBins - 1, std::max(0, (int)((centroid(g, axis) - cmin) * scale)));
+            int b = std::min(kBins - 1, std::max(0, (int)((cen[3 * (size_t)g + axis] - pmin) * pscale)));
             return b <= bin;
         });
         int left = (int)(mid - (perm.begin() + first));
@@ -149,7 +169,9 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
     out->max_depth = 0; out->max_leaf = 0;
     if (n <= 0) return;
     for (int i = 0; i < n; ++i) out->perm[i] = (uint32_t)i;
-    Builder b{n, lo, hi, out->perm, out->nodes};
+    std::vector<float> cen((size_t)3 * n);
+    for (size_t k = 0; k < cen.size(); ++k) cen[k] = 0.5f * (lo[k] + hi[k]);
+    Builder b{n, lo, hi, cen.data(), out->perm, out->nodes};
     out->nodes.reserve((size_t)n);
     out->nodes.push_back(BvhNode{});
     Box root = b.range_box(0, n);
@@ -180,7 +202,7 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
         auto work = [&] {
             for (size_t t; (t = next.fetch_add(1)) < tasks.size();) {
                 const Builder::Task& tk = tasks[t];
-                Builder lb{n, lo, hi, out->perm, subs[t].nodes};
+                Builder lb{n, lo, hi, cen.data(), out->perm, subs[t].nodes};
                 subs[t].nodes.reserve((size_t)tk.count);
                 subs[t].nodes.push_back(BvhNode{});
                 lb.build_node(0, tk.first, tk.count, tk.left, tk.depth);
