@@ -72,6 +72,7 @@ struct vr_context {
     int img_w = 0, img_h = 0;
     int rec_w = 0, rec_h = 0, rec_words = 0, rec_n = 0;
     bool rec_valid = false;
+    unsigned long long samples_valid = 0;          // samples of the last render still held in sampleL (0: none / multi-pass)
     unsigned long long* h_stats = nullptr;         // pinned
     unsigned int* h_counters = nullptr;            // pinned
     // ---- options

@@ -80,6 +80,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
         ctx->rec_w = W; ctx->rec_h = H; ctx->rec_words = words; ctx->rec_n = ctx->n;
     }
     const unsigned long long npix = (unsigned long long)A.win_w * (unsigned long long)owned_rows(p);
+    ctx->samples_valid = 0;
     VR_CUDA(cudaMemsetAsync(ctx->stats.p, 0, sizeof(unsigned long long) * kNumStats, s));
     VR_CUDA(cudaEventRecord(ctx->ev[0], s));
     double kernel_ms = 0.0;
@@ -151,6 +152,9 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     float total = 0.f;
     VR_CUDA(cudaEventElapsedTime(&total, ctx->ev[0], ctx->ev[1]));
     if (A.record_bits) ctx->rec_valid = true;
+    // per-sample radiance of a render that fitted one pass stays readable (vr_get_samples)
+    if (npix > 0 && npix * (unsigned long long)p->spp <= (unsigned long long)std::min(ctx->max_pass_samples, 4.0e9))
+        ctx->samples_valid = npix * (unsigned long long)p->spp;
     if (st) {
         st->kernel_ms = kernel_ms; st->total_ms = total;
         st->samples = npix * (unsigned long long)p->spp;
@@ -211,6 +215,18 @@ int vr_transmittance(vr_context* ctx, int nrays, const float* o3, const float* d
     VR_CUDA(cudaGetLastError());
     VR_CUDA(cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, s));
     VR_CUDA(cudaStreamSynchronize(s));
+    return VR_OK;
+}
+
+// per-sample radiance of the last free-flight render (single pass): float4 per sample = (r, g, b, bounce index at the end of
+// the path), ordered [owned pixel in row-major window order][si] -- what integrator.h:702 sums per pixel
+int vr_get_samples(vr_context* ctx, float* out4, uint64_t count) {
+    if (!ctx || !out4) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_get_samples: bad arguments");
+    if (!ctx->samples_valid || count > ctx->samples_valid)
+        return fail(ctx, VR_ERR_NO_SCENE, "vr_get_samples: the last render left no per-sample buffer of that size (multi-pass render?)");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    VR_CUDA(cudaMemcpyAsync(out4, ctx->sampleL.p, (size_t)count * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
     return VR_OK;
 }
 

@@ -28,7 +28,7 @@ STATUS = {0: "VR_OK", 1: "VR_ERR_INVALID_ARGUMENT", 2: "VR_ERR_CUDA", 3: "VR_ERR
 # every symbol include/volrender.h declares (tests/test_cabi.py checks the header against this and the .so)
 SYMBOLS = ["vr_create", "vr_destroy", "vr_last_error", "vr_version", "vr_device_count", "vr_stream", "vr_set_gmm",
            "vr_set_gmm_params", "vr_set_smm", "vr_set_lights", "vr_set_camera", "vr_render", "vr_render_device",
-           "vr_image_dev", "vr_get_recorded", "vr_transmittance", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
+           "vr_image_dev", "vr_get_recorded", "vr_get_samples", "vr_transmittance", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
            "vr_sfd_apply", "vr_sfd_reset_fdiff", "vr_sfd_accumulate", "vr_sfd_read", "vr_sfd_fdiff_dev",
            "vr_sfd_get_params", "vr_sfd_get_state", "vr_sfd_set_state", "vr_adam_step", "vr_unpack_params", "vr_set_option", "vr_kat_pcg", "vr_kat_gaussian",
            "vr_kat_camera_rays", "vr_kat_events", "vr_kat_libm", "vr_kat_erfinv"]
@@ -92,6 +92,7 @@ def lib():
     L.vr_render_device.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(RenderStats)]
     L.vr_image_dev.argtypes = [vp]; L.vr_image_dev.restype = vp
     L.vr_get_recorded.argtypes = [vp, fp, fp, ci]
+    L.vr_get_samples.argtypes = [vp, fp, C.c_uint64]
     L.vr_transmittance.argtypes = [vp, ci, fp, fp, fp, fp]
     L.vr_sfd_begin.argtypes = [vp, ci, fp, fp, C.c_float, C.c_float, C.c_float, C.c_float]
     L.vr_sfd_set_target.argtypes = [vp, ci, ci, fp]
@@ -239,6 +240,12 @@ class Context:
         cnt = np.zeros(W * H, np.int32); idx = np.zeros((W * H, cap), np.uint32)
         self._ck(self.L.vr_get_recorded(self.h, _ptr(cnt), _ptr(idx), cap))
         return cnt, idx
+
+    def samples(self, n_pixels, spp):
+        """per-sample (r, g, b, bounce) of the last single-pass free-flight render: [n_pixels, spp, 4]"""
+        out = np.empty((n_pixels, spp, 4), np.float32)
+        self._ck(self.L.vr_get_samples(self.h, _ptr(out), n_pixels * spp))
+        return out
 
     def transmittance(self, o, d, tmax):
         o, d, tmax = _f32(o), _f32(d), _f32(tmax)

@@ -121,6 +121,11 @@ const float* vr_image_dev(vr_context* ctx); /* device pointer, 3*W*H floats of t
 /* recorded per-pixel Gaussian sets of the last render with record != 0: counts[W*H] and, if
  * idx != NULL, up to cap indices per pixel (ascending original Gaussian index) */
 int vr_get_recorded(vr_context* ctx, int* counts, uint32_t* idx, int cap);
+/* per-SAMPLE radiance of the last vr_render* call of a free-flight integrator that fitted one pass
+ * (max_pass_samples): count float4 = (r, g, b, bounce index when the path ended), ordered
+ * [owned pixel, row-major in the window][si]; the si-ordered sum / spp is the pixel (integrator.h:702-706).
+ * Debug / parity aid for single-sample attribution of pixel differences. */
+int vr_get_samples(vr_context* ctx, float* out4, uint64_t count);
 
 /* ---- GaussianMixtureModel::transmittance_up_to (gmm.h:517-578) on a batch of rays ----------
  * directions must be unit length (the Ray ctor normalises, ray.h:11-12) */

@@ -79,6 +79,9 @@ def lib():
                             C.c_void_p, C.c_int]
     L.vo_pixel_samples.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(Camera), C.c_int, C.c_int,
                                    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
+    L.vo_render_samples.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_void_p]
+    L.vo_libm_batch.argtypes = [C.c_int, _f32p, _f32p, _f32p, _f32p]
     L.vo_num_threads.restype = C.c_int
     L.vo_counters_get.argtypes = [np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")]
     L.vo_pixel_losses.argtypes = [_f32p, _f32p, C.c_int, _f32p]
@@ -184,6 +187,43 @@ def pixel_samples(gmm: Gmm, lights, env, cam, integrator, W, H, spp, x, y, min_b
     lib().vo_pixel_samples(gmm.h, lights.shape[0], _c(lights[:, 0:3]), _c(lights[:, 3:6]), _c(env), C.byref(cam),
                            integrator, solver, W, H, spp, min_bounces, x, y, out.reshape(-1))
     return out
+
+
+def render_samples(gmm: Gmm, lights, env, cam: Camera, integrator: int, W: int, H: int, spp: int, min_bounces: int = 5,
+                   solver: int = SOLVER_ANALYTIC_NEWTON, window=None, perturb: int = 0, margins: bool = False):
+    """Per-sample radiance of a pixel window: array [wh, ww, spp, 4] = (r, g, b, bounce index at the end of the path)
+    and, with margins=True, [wh, ww, spp] smallest relative margin of each sample's discrete decisions.
+    perturb 1/2: free-flight distances +/- 1 ulp, 3/4: sampled optical depths * (1 +/- 2^-21)  (volpath_oracle.c)."""
+    lights = _c(lights).reshape(-1, 6)
+    lpos = _c(lights[:, 0:3]); lint = _c(lights[:, 3:6])
+    if lpos.size == 0:
+        lpos = np.zeros(3, np.float32); lint = np.zeros(3, np.float32)
+    x0, y0, x1, y1 = window if window is not None else (0, 0, W, H)
+    out = np.zeros((y1 - y0, x1 - x0, spp, 4), np.float32)
+    mg = np.zeros((y1 - y0, x1 - x0, spp), np.float32) if margins else None
+    lib().vo_render_samples(gmm.h, lights.shape[0], lpos, lint, _c(env), C.byref(cam), integrator, solver, W, H, spp,
+                            min_bounces, x0, y0, x1, y1, perturb, out.reshape(-1),
+                            mg.ctypes.data_as(C.c_void_p) if margins else None)
+    return (out, mg) if margins else out
+
+
+def sample_sensitivity(gmm: Gmm, lights, env, cam, integrator, W, H, spp, rtol=2e-5, atol=1e-7, **kw):
+    """Samples whose value moves by more than rtol under a few-ulp perturbation of a free-flight distance or a sampled
+    optical depth (perturb modes 1..4): returns (samples[..., 4], sensitive[...] bool, margin[...])."""
+    base, mg = render_samples(gmm, lights, env, cam, integrator, W, H, spp, margins=True, **kw)
+    sens = np.zeros(base.shape[:-1], bool)
+    for mode in (1, 2, 3, 4):
+        alt = render_samples(gmm, lights, env, cam, integrator, W, H, spp, perturb=mode, **kw)
+        d = np.abs(alt[..., :3] - base[..., :3]) > atol + rtol * np.abs(base[..., :3])
+        sens |= d.any(axis=-1) | (alt[..., 3] != base[..., 3])
+    return base, sens, mg
+
+
+def libm_batch(x):
+    x = _c(x)
+    s = np.empty_like(x); c = np.empty_like(x); a = np.empty_like(x)
+    lib().vo_libm_batch(x.size, x, s, c, a)
+    return s, c, a
 
 
 def render_spheres(smm: dict, env, cam, W, H, step=0.01, env_samples=5):

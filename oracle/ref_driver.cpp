@@ -17,11 +17,44 @@
 //   kat      scene=F n=N seed=S out=kat.bin       known-answer vectors
 //   sfd      scene=F target=img.f32 signs=signs.i8 S=s iters=k w= h= spp= ... out=prefix
 //   march    scene=F integrator=test|march_pure|march_gauss w= h= step= env= envcolor=r,g,b cam... out=img.f32
-//   spheres  scene=F w= h= step= env= cam... out=img.f32   (RayMarchingSpheres; env part is
-//            random_device-seeded in the reference -> statistical use only)
+//   spheres  scene=F w= h= step= env= [envcolor=r,g,b] cam... out=img.f32   (RayMarchingSpheres; the env part is
+//            random_device-seeded in the reference -> statistical use only, SURVEY.md F9 -- unless envcolor=0,0,0,
+//            which makes that term vanish: the image is then deterministic and pins the sphere path)
+//   samples  scene=F w= h= spp= [min_bounces=] [win=x0,y0,x1,y1] cam... out=samples.f32
+//            per-SAMPLE radiance of MultiScatterGaussians (float4 per (y, x, si): rgb + bounce index at the end of the
+//            path) for single-sample attribution of pixel differences, SURVEY.md 7.3
+// Every standard / Eigen header the reference pulls in is included FIRST, then `private` is made public for the
+// reference headers only: the per-sample dump (cmd_samples) has to call MultiScatterGaussians::get_free_flight_distance
+// (integrator.h:422-498), which the reference keeps private.  The headers on disk stay untouched.
+#include <omp.h>
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <filesystem>
+#include <fstream>
+#include <iostream>
+#include <limits>
+#include <memory>
+#include <new>
+#include <numbers>
+#include <optional>
+#include <random>
+#include <stdexcept>
+#include <string>
+#include <unordered_set>
+#include <vector>
+#include <Eigen/Cholesky>
+#include <Eigen/Core>
+#include <Eigen/Dense>
+#include <Eigen/Eigenvalues>
+#include <Eigen/Geometry>
+#define private public
 #include "integrator.h"
 #include "test_integrators.h"
 #include "inverse_integrator.h"
+#undef private
 
 #include <chrono>
 #include <cstdio>
@@ -383,6 +416,7 @@ static int cmd_pack(const Args& a) {
 // ---------------------------------------------------------------------------
 static int cmd_spheres(const Args& a) {
     Scene scene = Scene::load_SMM(get(a, "scene"));
+    if (!get(a, "envcolor").empty()) scene.env_color = vec3(get(a, "envcolor"));
     int W = std::stoi(get(a, "w", "64")), H = std::stoi(get(a, "h", "64"));
     auto cam = make_camera(a);
     Image image(W, H);
@@ -423,8 +457,122 @@ static int cmd_march(const Args& a) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------
+// Per-sample radiance of MultiScatterGaussians.  The reference only ever returns the pixel mean
+// (integrator.h:702-706), so the sample loop integrator.h:557-702 is walked here, statement by statement, around
+// the reference's OWN routines: derive_path_seed / PCG32 (rng.h), Camera::sample_ray, Scene::intersect_events,
+// MultiScatterGaussians::get_free_flight_distance (private in the header, see the top of this file),
+// evaluate_albedo, transmittance_up_to, sample_uniform_direction.  The walk is then CHECKED against the reference's
+// render(): the si-ordered float sum of the dumped samples / spp must reproduce every pixel of its image bit for bit
+// ("render_mismatch": 0 in the JSON line) -- so the dump is the reference's per-sample output, not a restatement's.
+static int cmd_samples(const Args& a) {
+    Scene scene = Scene::load_GMM(get(a, "scene"));
+    const int W = std::stoi(get(a, "w", "32")), H = std::stoi(get(a, "h", "32"));
+    const int spp = std::stoi(get(a, "spp", "16"));
+    const int min_scatter = std::stoi(get(a, "min_bounces", "5"));
+    int x0 = 0, y0 = 0, x1 = W, y1 = H;
+    if (!get(a, "win").empty()) {
+        std::stringstream ss(get(a, "win")); std::string tok; int v[4] = {0, 0, W, H};
+        for (int i = 0; i < 4 && std::getline(ss, tok, ','); ++i) v[i] = std::stoi(tok);
+        x0 = v[0]; y0 = v[1]; x1 = v[2]; y1 = v[3];
+    }
+    auto cam = make_camera(a);
+    MultiScatterGaussians ms(cam, spp, min_scatter);
+    const size_t Nprims = scene.get_num_primitives();
+    const int ww = x1 - x0, wh = y1 - y0;
+    std::vector<float> out(size_t(4) * ww * wh * spp, 0.f);
+    #pragma omp parallel
+    {
+        std::vector<PrimitiveHitEvent> events;
+        std::vector<size_t> active;
+        std::vector<int> idx_pos(Nprims, 0), idx_epoch(Nprims, 0);
+        int epoch_counter = 0;
+        #pragma omp for collapse(2) schedule(dynamic,1)
+        for (int y = y0; y < y1; ++y) {
+            for (int x = x0; x < x1; ++x) {
+                for (int si = 0; si < spp; ++si) {
+                    uint64_t seed = derive_path_seed(x, y, si);                       // :558
+                    PCG32 rng(seed, 1);
+                    int n = int(std::sqrt(spp));                                      // :562
+                    int sx = si % n, sy = si / n;
+                    float u = (x + (sx + rng.uniform()) / n) / W;                     // :567-568
+                    float v = (y + (sy + rng.uniform()) / n) / H;
+                    Ray ray = cam->sample_ray({u, v});                                // :570
+                    Eigen::Vector3f throughput = Eigen::Vector3f::Ones();
+                    Eigen::Vector3f L_accum = Eigen::Vector3f::Zero();
+                    int bounce = 0;
+                    for (;; ++bounce) {                                               // :590
+                        events.clear();
+                        scene.intersect_events(ray, events);                          // :593
+                        if (events.empty()) { L_accum += throughput.cwiseProduct(scene.env_color); break; }
+                        float target_tau = -std::log(1.0f - rng.uniform());           // :600
+                        active.clear();
+                        float t_scatter = ms.get_free_flight_distance(ray, events, target_tau, scene.gmm->at(0), active,
+                                                                      idx_pos, idx_epoch, epoch_counter);   // :605
+                        if (t_scatter < 0.f) { L_accum += throughput.cwiseProduct(scene.env_color); break; }  // :647
+                        Eigen::Vector3f pos = ray.origin + t_scatter * ray.direction; // :653
+                        float albedo = scene.gmm->at(0).evaluate_albedo(active, pos);
+                        bool is_env = (rng.uniform() < 1.f / (scene.lights.size() + 1));   // :657
+                        Eigen::Vector3f Li = Eigen::Vector3f::Zero();
+                        if (!is_env) {
+                            int li = int(rng.uniform() * scene.lights.size());
+                            const auto& L = scene.lights[li];
+                            Eigen::Vector3f wi = (L.position - pos).normalized();
+                            float dist = (L.position - pos).norm();
+                            Ray shadow(pos, wi);
+                            float Tr = scene.gmm->at(0).transmittance_up_to(shadow, dist);
+                            Li = Tr * L.intensity / (dist * dist);
+                        } else {
+                            Eigen::Vector3f wi = sample_uniform_direction(rng);
+                            Ray eray(pos, wi);
+                            float inf = std::numeric_limits<float>::infinity();
+                            float Tr = scene.gmm->at(0).transmittance_up_to(eray, inf);
+                            Li = Tr * scene.env_color * (4.0f * std::numbers::pi);
+                        }
+                        float phase_pdf = 1.f / (4.0f * std::numbers::pi);             // :681
+                        float w_ne = float(scene.lights.size() + 1);
+                        Eigen::Vector3f contrib = (throughput * (albedo * phase_pdf * w_ne)).cwiseProduct(Li);
+                        L_accum += contrib;
+                        throughput *= albedo;                                         // :688
+                        if (bounce >= min_scatter) {                                  // :691
+                            float rr = std::min(throughput.maxCoeff(), 0.9f);
+                            if (rng.uniform() > rr) break;
+                            throughput /= rr;
+                        }
+                        Eigen::Vector3f new_dir = sample_uniform_direction(rng);      // :698
+                        ray = Ray(pos, new_dir);
+                    }
+                    float* o = &out[(size_t(size_t(y - y0) * ww + (x - x0)) * spp + si) * 4];
+                    o[0] = L_accum[0]; o[1] = L_accum[1]; o[2] = L_accum[2]; o[3] = float(bounce);
+                }
+            }
+        }
+    }
+    // check against the reference's own render(): si-ordered sums reproduce its pixels bit for bit
+    Image image(W, H);
+    ms.render(scene, image);
+    long mismatch = 0;
+    for (int y = y0; y < y1; ++y)
+        for (int x = x0; x < x1; ++x) {
+            Eigen::Vector3f pixel_L = Eigen::Vector3f::Zero();
+            for (int si = 0; si < spp; ++si) {
+                const float* o = &out[(size_t(size_t(y - y0) * ww + (x - x0)) * spp + si) * 4];
+                pixel_L += Eigen::Vector3f(o[0], o[1], o[2]);
+            }
+            Eigen::Vector3f m = pixel_L / float(spp), r = image.get_pixel(x, y);
+            if (memcmp(m.data(), r.data(), 12) != 0) ++mismatch;
+        }
+    FILE* f = fopen(get(a, "out").c_str(), "wb");
+    if (!f) { perror("open out"); return 2; }
+    fwrite(out.data(), 4, out.size(), f);
+    fclose(f);
+    printf("{\"cmd\": \"samples\", \"w\": %d, \"h\": %d, \"spp\": %d, \"window\": [%d, %d, %d, %d], \"render_mismatch\": %ld}\n",
+           W, H, spp, x0, y0, x1, y1, mismatch);
+    return mismatch == 0 ? 0 : 4;
+}
+
 int main(int argc, char** argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|kat|sfd|pack|spheres|march key=value...\n"); return 1; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|kat|sfd|pack|spheres|march|samples key=value...\n"); return 1; }
     Args a = parse_args(argc, argv, 2);
     std::string c(argv[1]);
     // the reference prints banners on stdout; keep our JSON line last.
@@ -435,6 +583,7 @@ int main(int argc, char** argv) {
         if (c == "pack") return cmd_pack(a);
         if (c == "spheres") return cmd_spheres(a);
         if (c == "march") return cmd_march(a);
+        if (c == "samples") return cmd_samples(a);
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());
         return 2;

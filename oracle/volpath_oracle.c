@@ -53,6 +53,19 @@ static void vo_counters_fold(void) {
     memset(vo_cnt, 0, sizeof(vo_cnt));
 }
 
+/* Single-sample attribution: vo_render_samples can re-run a sample with its free-flight distance or
+ * its sampled optical depth moved by a few ulp (vo_perturb) and reports the smallest relative margin of the sample's
+ * discrete decisions (vo_min_margin): the comparison acc + seg > target (integrator.h:455), the Russian-roulette test
+ * (:693) and the tolerance tests of the iterative solvers (distance_solvers.h:39,84,112).  A sample whose value moves
+ * under such a perturbation is one an FP32 implementation with a different libm may legitimately disagree on. */
+static __thread int vo_perturb;       /* 0 none, 1/2: t_scatter +/- 1 ulp, 3/4: target_tau * (1 +/- 2^-21) */
+static __thread float vo_min_margin;  /* reset per sample */
+static inline void vo_margin(float lhs, float rhs) {
+    float den = fabsf(rhs) > 1e-30f ? fabsf(rhs) : 1e-30f;
+    float mg = fabsf(lhs - rhs) / den;
+    if (mg < vo_min_margin) vo_min_margin = mg;
+}
+
 /* ------------------------------------------------------------------------- */
 /* RNG -- include/rng.h:13-57                                                 */
 /* ------------------------------------------------------------------------- */
@@ -493,6 +506,7 @@ static float solve_bisection(const vo_gmm* m, const vo_ray* ray, float ta, float
         float tau = 0.0f;
         for (int k = 0; k < na; ++k) tau += gauss_optical_depth(&m->g[act[k]], ray, ta, mid);
         float f = tau - target;
+        vo_margin(fabsf(f), 1e-6f); vo_margin(tau, target);
         if (fabsf(f) <= 1e-6f) return mid;
         if (f < 0.0f) a = mid; else b = mid;
     }
@@ -513,6 +527,7 @@ static float solve_newton(const vo_gmm* m, const vo_ray* ray, float ta, float tb
     float t = 0.5f * (a + b);
     for (int iter = 0; iter < 8; ++iter) {
         float f = newton_f(m, ray, ta, b, act, na, t, target);
+        vo_margin(fabsf(f), tol);
         if (fabsf(f) <= tol) return clampf(t, a, b);
         float h = fmaxf(1e-5f, (b - a) * 1e-6f);
         float tp = fminf(b, t + h);
@@ -522,6 +537,7 @@ static float solve_newton(const vo_gmm* m, const vo_ray* ray, float ta, float tb
             return solve_bisection(m, ray, ta, tb, act, na, target);
         float t_next = t - f / deriv;
         if (!isfinite(t_next) || t_next < a || t_next > b) return solve_bisection(m, ray, ta, tb, act, na, target);
+        vo_margin(fabsf(t_next - t), tol * fmaxf(1.0f, fabsf(t)));
         if (fabsf(t_next - t) <= tol * fmaxf(1.0f, fabsf(t))) { t = t_next; return clampf(t, a, b); }
         t = t_next;
     }
@@ -669,6 +685,7 @@ typedef struct {
     int epoch_counter;
     unsigned char* active_mask; /* N, single-scatter path */
     uint32_t* pix_list; int n_pix, cap_pix; /* recording */
+    int last_bounce;                        /* value of `bounce` (integrator.h:590) when the last sample's path ended */
 } vo_scratch;
 
 static void active_push(vo_scratch* s, uint32_t g) {
@@ -697,6 +714,7 @@ static float ms_free_flight(const vo_gmm* m, const vo_ray* ray, vo_scratch* s, f
         float t_evt = s->ev.e[ei].t;
         double seg_tau = 0.0;
         for (int k = 0; k < s->na; ++k) seg_tau += (double)gauss_optical_depth(&m->g[s->active[k]], ray, t_prev, t_evt);
+        vo_margin((float)(acc_tau + seg_tau), target_tau);
         if (acc_tau + seg_tau > (double)target_tau) {
             float remaining = (float)((double)target_tau - acc_tau);
             return solve_distance(m, ray, t_prev, t_evt, s->active, s->na, remaining, solver, key);
@@ -771,11 +789,15 @@ static void ms_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
     const float phase_pdf = (float)(1.0f / (4.0f * VO_PI));
     const float w_ne = (float)(L->nl + 1);
     for (int bounce = 0;; ++bounce) {
+        s->last_bounce = bounce;
         gmm_intersect_events(m, &ray, &s->ev, &s->st);
         if (s->ev.n == 0) { for (int c = 0; c < 3; ++c) Lacc[c] += thr[c] * L->env[c]; break; }
         float target_tau = -logf(1.0f - pcg_uniform(&rng));
+        if (vo_perturb == 3) target_tau *= 1.0f + 0x1p-21f; else if (vo_perturb == 4) target_tau *= 1.0f - 0x1p-21f;
         s->na = 0;
         float t_scatter = ms_free_flight(m, &ray, s, target_tau, solver, rng.state);
+        if (t_scatter >= 0.0f && vo_perturb == 1) t_scatter = nextafterf(t_scatter, INFINITY);
+        else if (t_scatter > 0.0f && vo_perturb == 2) t_scatter = nextafterf(t_scatter, 0.0f);
         if (record) {
             const float tol = 1e-6f;
             if (t_scatter >= 0.0f) {
@@ -796,7 +818,9 @@ static void ms_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
         if (bounce >= min_scatter) {
             float mx = fmaxf(thr[0], fmaxf(thr[1], thr[2]));
             float rr = fminf(mx, 0.9f);
-            if (pcg_uniform(&rng) > rr) break;
+            float ur = pcg_uniform(&rng);
+            vo_margin(ur, rr);
+            if (ur > rr) { s->last_bounce = bounce; break; }
             for (int c = 0; c < 3; ++c) thr[c] /= rr;
         }
         v3 nd = sample_uniform_direction(&rng);
@@ -818,6 +842,8 @@ static void ss_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
     gmm_intersect_events(m, &ray, &s->ev, &s->st);
     if (s->ev.n == 0) { for (int c = 0; c < 3; ++c) out[c] = L->env[c]; return; }
     float target_tau = -logf(1.0f - pcg_uniform(&rng));
+    if (vo_perturb == 3) target_tau *= 1.0f + 0x1p-21f; else if (vo_perturb == 4) target_tau *= 1.0f - 0x1p-21f;
+    s->last_bounce = 0;
     /* active is a bool vector rescanned in ascending index order at every event (integrator.h:335,344-346) */
     float acc_tau = 0.0f, t_prev = 0.0f, t_scatter = -1.0f;
     int touched_n = 0;
@@ -827,8 +853,11 @@ static void ss_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
         for (int i = 0; i < m->n; ++i) if (s->active_mask[i]) active_push(s, (uint32_t)i);
         float seg_tau = 0.0f;
         for (int k = 0; k < s->na; ++k) seg_tau += gauss_optical_depth(&m->g[s->active[k]], &ray, t_prev, t_evt);
+        vo_margin(acc_tau + seg_tau, target_tau);
         if (acc_tau + seg_tau > target_tau) {
             t_scatter = solve_distance(m, &ray, t_prev, t_evt, s->active, s->na, target_tau - acc_tau, solver, rng.state);
+            if (t_scatter >= 0.0f && vo_perturb == 1) t_scatter = nextafterf(t_scatter, INFINITY);
+            else if (t_scatter > 0.0f && vo_perturb == 2) t_scatter = nextafterf(t_scatter, 0.0f);
             break;
         }
         acc_tau += seg_tau;
@@ -899,6 +928,47 @@ VO_EXPORT void vo_pixel_samples(const vo_gmm* m, int nl, const float* lpos, cons
         else ms_sample(m, &L, cam, x, y, si, spp, W, H, min_bounces, solver, 0, &s, out_rgb_per_sample + 3 * si);
     }
     scratch_free(&s);
+}
+/* per-sample output of a pixel window: out4[((y - y0) * (x1 - x0) + (x - x0)) * spp + si] = (r, g, b, bounce index at the
+ * end of the path); margin (optional, same indexing, one float per sample) = smallest relative margin of the sample's
+ * discrete decisions; perturb: see vo_perturb above.  Summed in si order and divided by spp the samples of a pixel give
+ * vo_render's pixel bit for bit. */
+VO_EXPORT void vo_render_samples(const vo_gmm* m, int nl, const float* lpos, const float* lint, const float* env,
+                                 const vo_camera* cam, int integrator, int solver, int W, int H, int spp, int min_bounces,
+                                 int x0, int y0, int x1, int y1, int perturb, float* out4, float* margin) {
+    vo_lights L; L.nl = nl; L.pos = lpos; L.intensity = lint; L.env[0] = env[0]; L.env[1] = env[1]; L.env[2] = env[2];
+#pragma omp parallel
+    {
+        vo_scratch s;
+        scratch_init(&s, m->n);
+        vo_perturb = perturb;
+#pragma omp for collapse(2) schedule(dynamic, 1)
+        for (int y = y0; y < y1; ++y) {
+            for (int x = x0; x < x1; ++x) {
+                for (int si = 0; si < spp; ++si) {
+                    const size_t k = ((size_t)(y - y0) * (size_t)(x1 - x0) + (size_t)(x - x0)) * (size_t)spp + (size_t)si;
+                    float Ls[3];
+                    vo_min_margin = INFINITY;
+                    if (integrator == VO_INTEGRATOR_SS) ss_sample(m, &L, cam, x, y, si, spp, W, H, solver, &s, Ls);
+                    else ms_sample(m, &L, cam, x, y, si, spp, W, H, min_bounces, solver, 0, &s, Ls);
+                    out4[4 * k] = Ls[0]; out4[4 * k + 1] = Ls[1]; out4[4 * k + 2] = Ls[2]; out4[4 * k + 3] = (float)s.last_bounce;
+                    if (margin) margin[k] = vo_min_margin;
+                }
+            }
+        }
+        vo_perturb = 0;
+        scratch_free(&s);
+        vo_counters_fold();
+    }
+}
+/* sinf / cosf / acosf of the host libm on a batch (the device carries ports of these, csrc/vr_math.cuh) */
+VO_EXPORT void vo_libm_batch(int n, const float* x, float* s_out, float* c_out, float* a_out) {
+#pragma omp parallel for
+    for (int i = 0; i < n; ++i) {
+        if (s_out) s_out[i] = sinf(x[i]);
+        if (c_out) c_out[i] = cosf(x[i]);
+        if (a_out) a_out[i] = acosf(x[i]);
+    }
 }
 VO_EXPORT int vo_num_threads(void) {
 #ifdef _OPENMP
