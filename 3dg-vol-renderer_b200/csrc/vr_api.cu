@@ -105,7 +105,8 @@ void vr_destroy(vr_context* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     sfd_destroy(ctx);
     for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
-                      &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->spheres, &ctx->lpos, &ctx->lint,
+                      &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->lam, &ctx->qnodes, &ctx->lg_start, &ctx->lg_gi,
+                      &ctx->lg_dmin, &ctx->spheres, &ctx->lpos, &ctx->lint,
                       &ctx->image, &ctx->sampleL, &ctx->counters, &ctx->stats, &ctx->overflow_list, &ctx->arena,
                       &ctx->record_bits, &ctx->scratch, &ctx->wavepool})
         b->release();
@@ -128,6 +129,7 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
+    if (!strcmp(name, "box_kappa")) { ctx->box_kappa = std::max(0.0, value); return VR_OK; }   // takes effect at the next vr_set_gmm*
     if (!strcmp(name, "light_grid")) { vr::cancel_light_grid_job(ctx); ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "light_grid_min_samples")) { ctx->light_grid_min_samples = value; return VR_OK; }
     if (!strcmp(name, "light_grid_res")) { vr::cancel_light_grid_job(ctx); ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
@@ -230,7 +232,7 @@ int vr_set_camera(vr_context* ctx, int kind, const float* pos3, const float* vie
 
 namespace vr {
 // Sigma^-1 / norm / boxes on the device, hierarchy on the host (vr_bvh.cpp), permutation on the device
-int set_gmm_from_device(vr_context* ctx, int n) {
+int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
     static const bool time_setup = getenv("VR_TIME_SETUP") != nullptr;   // stderr: host time of each phase of the scene setup
     const auto ts0 = std::chrono::steady_clock::now();
     double ts_prev = 0.0;
@@ -248,20 +250,27 @@ int set_gmm_from_device(vr_context* ctx, int n) {
     const size_t m = (size_t)std::max(n, 1);
     VR_CUDA(ctx->gauss_orig.ensure(m * 48)); VR_CUDA(ctx->gauss_leaf.ensure(m * 48));
     VR_CUDA(ctx->perm.ensure(m * 4)); VR_CUDA(ctx->leaf_of_orig.ensure(m * 4));
-    VR_CUDA(ctx->box_lo.ensure(m * 12)); VR_CUDA(ctx->box_hi.ensure(m * 12));
+    VR_CUDA(ctx->box_lo.ensure(m * 12)); VR_CUDA(ctx->box_hi.ensure(m * 12)); VR_CUDA(ctx->lam.ensure(m * 4));
     VR_CUDA(ctx->nodes.ensure(64)); VR_CUDA(ctx->qnodes.ensure(32));
     ctx->n = n; ctx->n_nodes = 0;
+    ctx->built_R = ctx->built_X = 0.f;
     if (n > 0) {
-        // slab tests run on (lo*idir - o*idir): position error ~ 1 ulp of the larger of |lo|, |o|.  Pad for
-        // origins within ~16 units of the coordinate origin (cameras further out are clamped by has_far_origin()).
-        const float pad_abs = 2e-6f * 32.0f;
         launch_prepare_gaussians(n, ctx->mean3.as<float>(), ctx->cov6.as<float>(), ctx->density.as<float>(),
                                  ctx->albedo.as<float>(), ctx->gauss_orig.as<float4>(), ctx->box_lo.as<float>(),
-                                 ctx->box_hi.as<float>(), pad_abs, ctx->stream);
-        std::vector<float> lo((size_t)3 * n), hi((size_t)3 * n);
+                                 ctx->box_hi.as<float>(), ctx->lam.as<float>(), ctx->stream);
+        std::vector<float> lo((size_t)3 * n), hi((size_t)3 * n), lam((size_t)n);
         VR_CUDA(cudaMemcpyAsync(lo.data(), ctx->box_lo.p, lo.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(hi.data(), ctx->box_hi.p, hi.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(lam.data(), ctx->lam.p, lam.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
+        // the boxes come back TIGHT; they are inflated for the reach of the ray origins (vr_bvh.h): the camera that is set,
+        // or origins within 8 units of the mixture when there is none yet, and never less than a caller-stated reach
+        BoxReach reach = box_reach(n, lo.data(), hi.data(), ctx->has_camera ? ctx->cam.pos : nullptr, ctx->bb_lo, ctx->bb_hi);
+        const BoxReach dflt = box_reach_of(ctx->bb_lo, ctx->bb_hi, nullptr);
+        reach.R = std::max(reach.R, dflt.R); reach.X = std::max(reach.X, dflt.X);
+        if (reach_RX) { reach.R = std::max(reach.R, reach_RX[0]); reach.X = std::max(reach.X, reach_RX[1]); }
+        inflate_boxes(n, lo.data(), hi.data(), lam.data(), reach, ctx->box_kappa);
+        ctx->built_R = reach.R; ctx->built_X = reach.X;
         lap("inverse covariances, boxes");
         if (ctx->lg_speculate && ctx->use_light_grid && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl) {
             vr_context::LightGridJob* job = new vr_context::LightGridJob;
@@ -299,6 +308,20 @@ int set_gmm_from_device(vr_context* ctx, int n) {
     }
     ctx->has_gmm = true;
     return VR_OK;
+}
+
+// A hierarchy inflated for ray origins within (R, X) must not be used by rays from farther out: the slab test could
+// reject a box whose ellipsoid the reference's FP32 quadric accepts (vr_bvh.h).  Rebuild with 25 % head room instead.
+int ensure_reach(vr_context* ctx, float R, float X) {
+    if (!ctx->has_gmm || ctx->n <= 0) return VR_OK;
+    if (R <= ctx->built_R && X <= ctx->built_X) return VR_OK;
+    const float rx[2] = {std::max(R, ctx->built_R) * 1.25f, std::max(X, ctx->built_X) * 1.25f};
+    return set_gmm_from_device(ctx, ctx->n, rx);
+}
+int ensure_camera_reach(vr_context* ctx) {
+    if (!ctx->has_gmm || ctx->n <= 0 || !ctx->has_camera) return VR_OK;
+    const BoxReach need = box_reach_of(ctx->bb_lo, ctx->bb_hi, ctx->cam.pos);
+    return ensure_reach(ctx, need.R, need.X);
 }
 
 // per-light direction grids for the wavefront engine's point-light shadow rays (vr_lightgrid.h); (re)built when the

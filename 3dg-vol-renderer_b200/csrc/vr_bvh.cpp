@@ -237,6 +237,60 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out) {
     out->max_leaf = b.max_leaf;
 }
 
+BoxReach box_reach_of(const float* bb_lo, const float* bb_hi, const float* cam_pos) {
+    double diag2 = 0.0, maxabs = 0.0, camd2 = 0.0, camabs = 0.0;
+    for (int k = 0; k < 3; ++k) {
+        const double e = (double)bb_hi[k] - (double)bb_lo[k];
+        diag2 += e * e;
+        maxabs = std::max(maxabs, std::max(std::fabs((double)bb_lo[k]), std::fabs((double)bb_hi[k])));
+        if (cam_pos) {
+            // farthest point of the box from the camera, per axis
+            const double d = std::max(std::fabs((double)cam_pos[k] - (double)bb_lo[k]), std::fabs((double)cam_pos[k] - (double)bb_hi[k]));
+            camd2 += d * d;
+            camabs = std::max(camabs, std::fabs((double)cam_pos[k]));
+        }
+    }
+    BoxReach r;
+    const double diag = std::sqrt(diag2);
+    // ray origins: scatter positions inside the mixture (bounce and shadow rays) and points of the camera's film plane,
+    // pos + u right + v up with |u|, |v| <= 1 (camera.h:45-73): sqrt(2) from pos, rounded up to 1.5
+    if (cam_pos) { r.R = (float)std::max(diag, std::sqrt(camd2) + 1.5); r.X = (float)std::max(maxabs, camabs + 1.5); }
+    else { r.R = (float)(diag + 8.0); r.X = (float)(maxabs + 8.0); }
+    if (!std::isfinite(r.R)) r.R = 3.0e38f;
+    if (!std::isfinite(r.X)) r.X = 3.0e38f;
+    return r;
+}
+
+BoxReach box_reach(int n, const float* lo, const float* hi, const float* cam_pos, float* bb_lo, float* bb_hi) {
+    for (int k = 0; k < 3; ++k) { bb_lo[k] = std::numeric_limits<float>::infinity(); bb_hi[k] = -bb_lo[k]; }
+    for (int i = 0; i < n; ++i)
+        for (int k = 0; k < 3; ++k) {
+            const float l = lo[3 * (size_t)i + k], h = hi[3 * (size_t)i + k];
+            if (std::fabs(l) < 1e30f) bb_lo[k] = std::min(bb_lo[k], l);     // a non-finite box (h = 3e38) must not set the reach
+            if (std::fabs(h) < 1e30f) bb_hi[k] = std::max(bb_hi[k], h);
+        }
+    for (int k = 0; k < 3; ++k) if (!(bb_lo[k] <= bb_hi[k])) { bb_lo[k] = 0.f; bb_hi[k] = 0.f; }
+    return box_reach_of(bb_lo, bb_hi, cam_pos);
+}
+
+void inflate_boxes(int n, float* lo, float* hi, const float* lam, BoxReach reach, double kappa) {
+    const double eps = 5.9604644775390625e-08;   // 2^-24
+    const double geom = (double)reach.R * (2.0 * (double)reach.R + (double)reach.X);
+    const float pad_abs = 4e-6f * std::max(16.0f, reach.X);
+    for (int i = 0; i < n; ++i) {
+        double rel = std::max(0.003, kappa * eps * (double)lam[i] * geom);
+        if (!(rel < 1.0)) rel = 1.0;            // beyond this the quadric test itself is noise; the box is doubled at most
+        for (int k = 0; k < 3; ++k) {
+            const float l = lo[3 * (size_t)i + k], h = hi[3 * (size_t)i + k];
+            const float c = 0.5f * (l + h), e = 0.5f * (h - l);
+            if (!(std::fabs(e) < 1e30f)) continue;                           // already "everything"
+            const float g = (float)((double)e * (1.0 + rel)) + pad_abs;
+            lo[3 * (size_t)i + k] = c - g;
+            hi[3 * (size_t)i + k] = c + g;
+        }
+    }
+}
+
 void quantize_bvh(const BvhBuildResult& tree, BvhQuantGrid* grid, std::vector<BvhNodeQ>* out) {
     out->clear();
     double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};

@@ -46,4 +46,21 @@ void quantize_bvh(const BvhBuildResult& tree, BvhQuantGrid* grid, std::vector<Bv
 // lo/hi: 3*n floats each (per-Gaussian boxes).  Deterministic.
 void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out);
 
+// Slack of the culling boxes.  The reference decides an overlap with an FP32 quadric test (gaussian.h:126-164) whose
+// discriminant B^2 - 4A(C0 - 9) cancels catastrophically: with p = o - mu, C0 = p^T M p ~ lam * R^2 (lam = largest eigenvalue
+// of Sigma^-1, R = distance from the ray origin), the accepted squared Mahalanobis radius is 9 +- O(eps * lam * R^2), and
+// p itself carries the rounding of coordinates of magnitude X: another O(eps * lam * R * X).  A box that is to contain every
+// ray the FLOAT test accepts must therefore grow with the reach of the ray origins.  BoxReach states that reach:
+//   R = the farthest a ray origin can be from a point of the mixture, X = the largest coordinate magnitude of origins and
+//   mixture.  inflate_boxes grows the tight 3-sigma half extents h to h * (1 + max(0.003, kappa * eps * lam * R * (2 R + X)))
+//   + 4e-6 * max(16, X) (the absolute term covers the slab arithmetic of the traversal, vr_device.cuh).
+struct BoxReach { float R, X; };
+// bounding box of the tight boxes -> bb_lo/bb_hi[3]; cam_pos = nullptr: no camera known yet (the reach then assumes ray
+// origins within 8 units of the mixture's bounding box)
+BoxReach box_reach(int n, const float* lo, const float* hi, const float* cam_pos, float* bb_lo, float* bb_hi);
+// the reach a camera at cam_pos needs over a mixture bounded by bb_lo/bb_hi (film-plane offsets of camera.h:45-73 included)
+BoxReach box_reach_of(const float* bb_lo, const float* bb_hi, const float* cam_pos);
+constexpr double kBoxKappa = 0.012;
+void inflate_boxes(int n, float* lo, float* hi, const float* lam, BoxReach reach, double kappa = kBoxKappa);
+
 }  // namespace vr

@@ -7,6 +7,7 @@
 
 #include "../../include/volrender.h"
 #include "vr_internal.h"
+#include "vr_bvh.h"
 
 namespace vr {
 
@@ -40,7 +41,11 @@ struct vr_context {
     bool has_gmm = false;
     int n = 0, n_nodes = 0, bvh_depth = 0;
     vr::DevBuf mean3, cov6, density, albedo;       // inputs as given (original order)
-    vr::DevBuf gauss_orig, gauss_leaf, nodes, qnodes, perm, leaf_of_orig, box_lo, box_hi;
+    vr::DevBuf gauss_orig, gauss_leaf, nodes, qnodes, perm, leaf_of_orig, box_lo, box_hi, lam;
+    // reach of the ray origins the culling boxes were inflated for (vr_bvh.h BoxReach) and the mixture's bounding box:
+    // a camera or a ray batch that reaches farther makes the next render rebuild the hierarchy (ensure_reach)
+    double box_kappa = vr::kBoxKappa;
+    float built_R = 0.f, built_X = 0.f, bb_lo[3] = {0.f, 0.f, 0.f}, bb_hi[3] = {0.f, 0.f, 0.f};
     float qorg[3] = {0.f, 0.f, 0.f}, qcell[3] = {1.f, 1.f, 1.f};   // grid of the compact tree (vr_bvh.h BvhQuantGrid)
     // host copies kept for the per-light direction grids (vr_lightgrid.h), built lazily before a render
     std::vector<float> h_box_lo, h_box_hi, h_lpos;
@@ -95,7 +100,9 @@ namespace vr {
 int fail(vr_context* c, int code, const std::string& msg);
 int cuda_fail(vr_context* c, cudaError_t e, const char* what);
 int render_device_impl(vr_context* c, const vr_render_params* p, vr_render_stats* st);
-int set_gmm_from_device(vr_context* c, int n);
+int set_gmm_from_device(vr_context* c, int n, const float* reach_RX = nullptr);   // reach_RX: minimum BoxReach {R, X} to build for
+int ensure_reach(vr_context* c, float R, float X);   // rebuilds the hierarchy when it was inflated for a smaller reach
+int ensure_camera_reach(vr_context* c);              // ... for the camera currently set
 void cancel_light_grid_job(vr_context* c);  // vr_api.cu: joins and drops a speculative grid build
 int ensure_light_grids(vr_context* c);  // vr_api.cu  // mean3/cov6/density/albedo device buffers already filled
 void sfd_destroy(vr_context* c);

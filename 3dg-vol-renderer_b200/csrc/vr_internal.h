@@ -82,6 +82,12 @@ void wave_graph_cache_destroy(WaveGraphCache* c);
 int run_wavefront_pass(const RenderArgs& a, void* pool_mem, int P_total, int parts, int num_sms, unsigned int* h_cnt_pinned /* parts * kWaveCounters */,
                        cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches, struct WaveGraphCache* graphs);
 
+// known-answer hook over the wavefront free-flight traversal (vr_wave.cu): overlap sets of n caller rays, unpruned.
+// pool_mem: wave_pool_bytes(n) bytes; sample_scratch: n float4; counts[n] = overlaps found (may exceed kWaveCap),
+// idx[n][cap] = original indices of the first min(count, kWaveCap, cap) in gather order
+int run_wave_gather_kat(const SceneDev& S, int n, const float* d_o3, const float* d_d3, void* pool_mem, float4* sample_scratch,
+                        unsigned long long* stats, int cap, int* d_counts, uint32_t* d_idx, int num_sms, cudaStream_t s);
+
 constexpr int kBlockThreads = 128;
 constexpr int kLocalCap = 32;        // overlaps kept in local memory by the main kernel
 
@@ -105,9 +111,10 @@ void launch_kat_events(const SceneDev& S, const float* o3, const float* d3, int 
 void launch_kat_libm(int n, const float* x, float* s_out, float* c_out, float* a_out, cudaStream_t s);
 void launch_kat_erfinv(int n, const double* x, double* y, cudaStream_t s);
 
-// scene preparation: cov6 -> Sigma^-1, norm, padded 3-sigma boxes (gaussian.h:52-56,304-319)
+// scene preparation: cov6 -> Sigma^-1, norm, TIGHT 3-sigma boxes (gaussian.h:52-56,304-319) and a bound of Sigma^-1's
+// largest eigenvalue per component (the boxes are inflated afterwards, vr_bvh.h inflate_boxes)
 void launch_prepare_gaussians(int n, const float* mean3, const float* cov6, const float* density, const float* albedo,
-                              float4* gauss_orig_order, float* box_lo, float* box_hi, float pad_abs, cudaStream_t s);
+                              float4* gauss_orig_order, float* box_lo, float* box_hi, float* lam, cudaStream_t s);
 void launch_permute_gaussians(int n, const float4* src, const uint32_t* perm, float4* dst, uint32_t* leaf_of_orig,
                               cudaStream_t s);
 // apply_params_to_gmm_local math (gmm.h:634-674)

@@ -81,6 +81,12 @@ __global__ void fdiff_kernel(OwnedPixels o, int words, int n, const uint32_t* __
     }
 }
 
+static void launch_fdiff(const OwnedPixels& o, int words, int n, const uint32_t* bits_base, const uint32_t* bits_plus, const float* loss_base,
+                         const float* loss_plus, long long* F, cudaStream_t st) {
+    const long long total = (long long)o.win_w * o.rows * words;
+    if (total > 0) fdiff_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(o, words, n, bits_base, bits_plus, loss_base, loss_plus, F);
+}
+
 __global__ void perturb_kernel(int D, const float* __restrict__ params, const signed char* __restrict__ s,
                                const float* __restrict__ eps, float* __restrict__ out) {  // inverse_integrator.h:146-148
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -226,10 +232,8 @@ int vr_sfd_accumulate(vr_context* ctx, const vr_render_params* rp, int S, const 
         if (npix_owned > 0) {
             pixel_loss_kernel<<<(npix_owned + 127) / 128, 128, 0, st>>>(o, ctx->image.as<float>(), s->target.as<float>(),
                                                                          s->loss_plus.as<float>(), nullptr);
-            const long long total = (long long)npix_owned * words;
-            fdiff_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(o, words, n, s->bits_base.as<uint32_t>(),
-                                                                           ctx->record_bits.as<uint32_t>(), s->loss_base.as<float>(),
-                                                                           s->loss_plus.as<float>(), s->fdiff_fixed.as<long long>() + (size_t)k * n);
+            launch_fdiff(o, words, n, s->bits_base.as<uint32_t>(), ctx->record_bits.as<uint32_t>(), s->loss_base.as<float>(),
+                         s->loss_plus.as<float>(), s->fdiff_fixed.as<long long>() + (size_t)k * n, st);
         }
     }
     VR_CUDA(cudaStreamSynchronize(st));
@@ -290,6 +294,33 @@ int vr_sfd_apply(vr_context* ctx, int S, const int8_t* signs, const double* F_di
                                                   s->beta1, s->beta2, s->adam_eps);
     VR_CUDA(cudaGetLastError());
     if (grad_out) VR_CUDA(cudaMemcpyAsync(grad_out, s->grad.p, (size_t)D * 4, cudaMemcpyDeviceToHost, st));
+    VR_CUDA(cudaStreamSynchronize(st));
+    return VR_OK;
+}
+
+// known-answer hook of the localised loss difference (inverse_integrator.h:157-179): caller-supplied recorded sets (bitmaps, one
+// row of `words` u32 per pixel, bit g = Gaussian g) and per-pixel losses -> F_diff[n] in int64 fixed point (2^-32 units)
+int vr_kat_fdiff(vr_context* ctx, int npix, int n, const uint32_t* bits_base, const uint32_t* bits_plus, const float* loss_base,
+                 const float* loss_plus, int64_t* F_fixed) {
+    if (!ctx || npix <= 0 || n <= 0 || !bits_base || !bits_plus || !loss_base || !loss_plus || !F_fixed)
+        return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_kat_fdiff: bad arguments");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    const int words = (n + 31) / 32;
+    const size_t bb = (size_t)npix * words * 4, lb = (size_t)npix * 4, fb = (size_t)n * 8;
+    VR_CUDA(ctx->scratch.ensure(2 * bb + 2 * lb + fb + 64));
+    char* b = ctx->scratch.as<char>();
+    long long* dF = (long long*)b; uint32_t* db0 = (uint32_t*)(b + ((fb + 15) & ~(size_t)15)); uint32_t* db1 = db0 + (size_t)npix * words;
+    float* dl0 = (float*)(db1 + (size_t)npix * words); float* dl1 = dl0 + npix;
+    cudaStream_t st = ctx->stream;
+    VR_CUDA(cudaMemcpyAsync(db0, bits_base, bb, cudaMemcpyHostToDevice, st));
+    VR_CUDA(cudaMemcpyAsync(db1, bits_plus, bb, cudaMemcpyHostToDevice, st));
+    VR_CUDA(cudaMemcpyAsync(dl0, loss_base, lb, cudaMemcpyHostToDevice, st));
+    VR_CUDA(cudaMemcpyAsync(dl1, loss_plus, lb, cudaMemcpyHostToDevice, st));
+    VR_CUDA(cudaMemsetAsync(dF, 0, fb, st));
+    OwnedPixels o; o.W = npix; o.x0 = 0; o.y0 = 0; o.win_w = npix; o.rows = 1; o.part_rank = 0; o.part_count = 1;
+    launch_fdiff(o, words, n, db0, db1, dl0, dl1, dF, st);
+    VR_CUDA(cudaGetLastError());
+    VR_CUDA(cudaMemcpyAsync(F_fixed, dF, fb, cudaMemcpyDeviceToHost, st));
     VR_CUDA(cudaStreamSynchronize(st));
     return VR_OK;
 }

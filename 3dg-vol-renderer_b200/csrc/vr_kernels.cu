@@ -432,7 +432,7 @@ __device__ __forceinline__ float cof3(const float* a, int i, int j) {  // Eigen 
 __global__ void prepare_gaussians_kernel(int n, const float* __restrict__ mean3, const float* __restrict__ cov6,
                                          const float* __restrict__ density, const float* __restrict__ albedo,
                                          float4* __restrict__ out, float* __restrict__ box_lo, float* __restrict__ box_hi,
-                                         float pad_abs) {
+                                         float* __restrict__ lam) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float* c = cov6 + 6 * (size_t)i;
@@ -456,18 +456,20 @@ __global__ void prepare_gaussians_kernel(int n, const float* __restrict__ mean3,
     out[3 * (size_t)i + 1] = make_float4(m01, m02, m11, m12);
     out[3 * (size_t)i + 2] = make_float4(m22, density[i], norm, albedo[i]);
     const float mean[3] = {mx, my, mz};
-    for (int k = 0; k < 3; ++k) {  // tight 3-sigma extent, padded for the FP32 slack of the quadric test
-        float h = 3.0f * sqrtf(fmaxf(a[4 * k], 0.0f)) * 1.003f + pad_abs;
+    for (int k = 0; k < 3; ++k) {  // TIGHT 3-sigma extent; inflate_boxes() (vr_bvh.cpp) adds the slack of the FP32 quadric test
+        float h = 3.0f * sqrtf(fmaxf(a[4 * k], 0.0f));
         if (!(h >= 0.0f) || !isfinite(h)) h = 3.0e38f;
         box_lo[3 * (size_t)i + k] = mean[k] - h;
         box_hi[3 * (size_t)i + k] = mean[k] + h;
     }
+    // Gershgorin bound of the largest eigenvalue of Sigma^-1: scale of the quadric's rounding error (inflate_boxes)
+    lam[i] = fmaxf(fmaxf(fabsf(m00) + fabsf(m01) + fabsf(m02), fabsf(m01) + fabsf(m11) + fabsf(m12)), fabsf(m02) + fabsf(m12) + fabsf(m22));
 }
 void launch_prepare_gaussians(int n, const float* mean3, const float* cov6, const float* density, const float* albedo,
-                              float4* gauss_orig_order, float* box_lo, float* box_hi, float pad_abs, cudaStream_t s) {
+                              float4* gauss_orig_order, float* box_lo, float* box_hi, float* lam, cudaStream_t s) {
     if (n > 0)
         prepare_gaussians_kernel<<<(n + 127) / 128, 128, 0, s>>>(n, mean3, cov6, density, albedo, gauss_orig_order, box_lo,
-                                                                   box_hi, pad_abs);
+                                                                   box_hi, lam);
 }
 __global__ void permute_gaussians_kernel(int n, const float4* __restrict__ src, const uint32_t* __restrict__ perm,
                                          float4* __restrict__ dst, uint32_t* __restrict__ leaf_of_orig) {

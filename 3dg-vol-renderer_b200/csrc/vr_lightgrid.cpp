@@ -48,7 +48,14 @@ bool face_rect(const double lo[3], const double hi[3], int m, bool negative, int
 static bool build_one_light(int n, const float* lo, const float* hi, const uint32_t* leaf_of_orig, const float* lpos3, int res,
                             std::vector<uint32_t>* start_rel, std::vector<uint32_t>* entry_gi, std::vector<float>* entry_dmin) {
     const size_t cells = (size_t)6 * res * res;
-    const double pad = 1e-4;     // absolute slack around every box (scene units): rounding of ray origins / directions
+    // absolute slack around every box (scene units): rounding of ray origins / directions / distances, which grows with the
+    // magnitude of the coordinates involved (a mixture or a light far from the coordinate origin)
+    double maxabs = std::max(std::max(std::fabs((double)lpos3[0]), std::fabs((double)lpos3[1])), std::fabs((double)lpos3[2]));
+    for (size_t k = 0; k < (size_t)3 * n; ++k) {
+        if (std::fabs(lo[k]) < 1e30f) maxabs = std::max(maxabs, std::fabs((double)lo[k]));
+        if (std::fabs(hi[k]) < 1e30f) maxabs = std::max(maxabs, std::fabs((double)hi[k]));
+    }
+    const double pad = std::max(1e-4, 64.0 * 5.9604644775390625e-08 * maxabs);
     const double near_limit = 0.05;
     std::vector<Rect> rects;     // per component, up to 6
     std::vector<uint32_t> rect_first((size_t)n + 1);

@@ -11,6 +11,24 @@ namespace vr {
 int render_spheres_impl(vr_context* ctx, const vr_render_params* p, vr_render_stats* st);  // vr_spheres.cu
 int render_march_impl(vr_context* ctx, const vr_render_params* p, vr_render_stats* st);    // vr_march.cu
 
+// reach of a batch of ray origins (vr_transmittance, vr_kat_gather): farthest origin from the mixture's box, largest coordinate
+static int ensure_origin_reach(vr_context* ctx, int nrays, const float* o3) {
+    if (!ctx->has_gmm || ctx->n <= 0) return VR_OK;
+    double R2 = 0.0, X = 0.0;
+    for (int i = 0; i < nrays; ++i) {
+        double d2 = 0.0;
+        for (int k = 0; k < 3; ++k) {
+            const double o = (double)o3[3 * (size_t)i + k];
+            const double d = std::max(std::fabs(o - (double)ctx->bb_lo[k]), std::fabs(o - (double)ctx->bb_hi[k]));
+            d2 += d * d;
+            X = std::max(X, std::fabs(o));
+        }
+        R2 = std::max(R2, d2);
+    }
+    if (!(R2 < 1e60) || !(X < 1e30)) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "ray origin is not finite");
+    return ensure_reach(ctx, (float)std::sqrt(R2), (float)X);
+}
+
 static int owned_rows(const vr_render_params* p) {
     const int rows = p->y1 - p->y0;
     if (p->part_rank >= rows) return 0;
@@ -41,6 +59,8 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     if (p->integrator != VR_INTEGRATOR_FREE_FLIGHT_SS && p->integrator != VR_INTEGRATOR_MULTI_SCATTER)
         return fail(ctx, VR_ERR_INVALID_ARGUMENT, "render: unknown integrator");
     if (!ctx->has_gmm) return fail(ctx, VR_ERR_NO_SCENE, "render: no Gaussian mixture set (vr_set_gmm)");
+    rc = ensure_camera_reach(ctx);   // a camera farther out than the culling boxes were inflated for: rebuild (vr_bvh.h BoxReach)
+    if (rc) return rc;
     const int W = p->width, H = p->height;
     cudaStream_t s = ctx->stream;
     VR_CUDA(ctx->image.ensure((size_t)3 * W * H * sizeof(float)));
@@ -204,6 +224,10 @@ int vr_transmittance(vr_context* ctx, int nrays, const float* o3, const float* d
     if (nrays == 0) return VR_OK;
     VR_CUDA(cudaSetDevice(ctx->device));
     const size_t n = (size_t)nrays;
+    {   // reach of this batch's origins over the mixture (vr_bvh.h BoxReach)
+        int rc = ensure_origin_reach(ctx, nrays, o3);
+        if (rc) return rc;
+    }
     VR_CUDA(ctx->scratch.ensure(n * 32));
     float* d = ctx->scratch.as<float>();
     float *d_o = d, *d_d = d + 3 * n, *d_t = d + 6 * n, *d_out = d + 7 * n;
@@ -329,6 +353,30 @@ int vr_kat_events(vr_context* ctx, const float* o3, const float* d3, int cap, fl
     const size_t ne = (size_t)std::min(*n_events, cap);
     if (ne) { VR_DOWN(t, d_t, ne * 4); VR_DOWN(entering, d_e, ne * 4); VR_DOWN(index, d_i, ne * 4); }
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VR_OK;
+}
+
+int vr_kat_gather(vr_context* ctx, int n, const float* o3, const float* d3, int cap, int32_t* counts, uint32_t* idx) {
+    if (!ctx || n <= 0 || !o3 || !d3 || cap <= 0 || !counts || !idx) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_kat_gather: bad arguments");
+    if (!ctx->has_gmm) return fail(ctx, VR_ERR_NO_SCENE, "vr_kat_gather: no Gaussian mixture set");
+    if (n > (1 << 22)) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_kat_gather: at most 2^22 rays per call");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    int rc = ensure_origin_reach(ctx, n, o3);
+    if (rc) return rc;
+    const size_t m = (size_t)n;
+    VR_CUDA(ctx->wavepool.ensure(wave_pool_bytes(n)));
+    VR_CUDA(ctx->scratch.ensure(m * (24 + 16 + 4 + 4 * (size_t)cap) + 256));
+    char* b = ctx->scratch.as<char>();
+    float4* d_samp = (float4*)b; float* d_o = (float*)(b + m * 16); float* d_d = d_o + 3 * m;
+    int* d_cnt = (int*)(d_d + 3 * m); uint32_t* d_idx = (uint32_t*)(d_cnt + m);
+    VR_UP(d_o, o3, m * 12); VR_UP(d_d, d3, m * 12);
+    VR_CUDA(cudaMemsetAsync(d_idx, 0xff, m * 4 * (size_t)cap, ctx->stream));
+    if (run_wave_gather_kat(ctx->scene_dev(), n, d_o, d_d, ctx->wavepool.p, d_samp, ctx->stats.as<unsigned long long>(), cap, d_cnt, d_idx,
+                            ctx->num_sms, ctx->stream) < 0)
+        return cuda_fail(ctx, cudaGetLastError(), "vr_kat_gather");
+    VR_DOWN(counts, d_cnt, m * 4); VR_DOWN(idx, d_idx, m * 4 * (size_t)cap);
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    VR_CUDA(cudaGetLastError());
     return VR_OK;
 }
 

@@ -779,6 +779,51 @@ __global__ void wave_init_kernel(const __grid_constant__ WavePool Q, unsigned in
 }
 
 // ------------------------------------------------------------------------------------------
+// known-answer hook: wave_trav_kernel<RAY_SCATTER> itself (quantised nodes, candidate queue, batched quadric tests) on a
+// batch of caller rays with an infinite sampled depth, i.e. nothing is pruned: the overlap SET of every ray
+// ------------------------------------------------------------------------------------------
+__global__ void kat_gather_init_kernel(const __grid_constant__ WavePool Q, unsigned int n, const float* __restrict__ o3, const float* __restrict__ d3) {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < kWaveCounters) Q.cnt[i] = (i == WC_NTS) ? n : 0u;
+    if (i >= n) return;
+    Q.ray[kSlotF4 * (size_t)i] = make_float4(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2], CUDART_INF_F);
+    Q.ray[kSlotF4 * (size_t)i + 1] = make_float4(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2], __int_as_float(RAY_SCATTER));
+    Q.ps01[kSlotF4 * (size_t)i] = make_float4(0.f, 0.f, 0.f, 1.0f);
+    reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)i + 1] = make_uint4(0u, 0u, i, 0u);
+    Q.hit01[kSlotF4 * (size_t)i] = make_uint4(0u, 0u, 0u, 0u);
+    Q.listTs[i] = i;
+}
+__global__ void kat_gather_extract_kernel(const __grid_constant__ WavePool Q, unsigned int n, const uint32_t* __restrict__ orig, int cap,
+                                          int* __restrict__ counts, uint32_t* __restrict__ idx) {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 h0 = Q.hit01[kSlotF4 * (size_t)i];
+    const int K = (int)h0.x;
+    counts[i] = K;
+    for (int k = 0; k < K && k < kWaveCap && k < cap; ++k) {
+        float t0, t1; uint32_t gi;
+        pool_load_hit(Q, i, k, h0, &t0, &t1, &gi);
+        idx[(size_t)i * cap + k] = __ldg(orig + gi);
+    }
+}
+int run_wave_gather_kat(const SceneDev& S, int n, const float* d_o3, const float* d_d3, void* pool_mem, float4* sample_scratch,
+                        unsigned long long* stats, int cap, int* d_counts, uint32_t* d_idx, int num_sms, cudaStream_t s) {
+    WavePool Q;
+    wave_pool_carve(&Q, n, pool_mem);
+    RenderArgs A{};
+    A.scene = S; A.scene.lg_mask = 0;
+    A.sampleL = sample_scratch; A.stats = stats;
+    A.W = A.H = A.spp = A.nsq = 1; A.win_w = 1; A.part_count = 1; A.work_count = (unsigned int)n;
+    kat_gather_init_kernel<<<(std::max(n, (int)kWaveCounters) + 255) / 256, 256, 0, s>>>(Q, (unsigned int)n, d_o3, d_d3);
+    int bps = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
+    const int grid = std::max(1, std::min(num_sms * std::max(bps, 1), (n + kBlockThreads - 1) / kBlockThreads));
+    wave_trav_kernel<RAY_SCATTER><<<grid, kBlockThreads, 0, s>>>(A, Q);
+    kat_gather_extract_kernel<<<(n + 255) / 256, 256, 0, s>>>(Q, (unsigned int)n, S.orig, cap, d_counts, d_idx);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
 // host driver of one pass
 // ------------------------------------------------------------------------------------------
 // One pass = a.work_count samples.  The pass is cut into `parts` interleaved sets of pixel rows, each with its own pool of slots, counters

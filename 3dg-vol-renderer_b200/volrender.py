@@ -31,7 +31,7 @@ SYMBOLS = ["vr_create", "vr_destroy", "vr_last_error", "vr_version", "vr_device_
            "vr_image_dev", "vr_get_recorded", "vr_get_samples", "vr_transmittance", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
            "vr_sfd_apply", "vr_sfd_reset_fdiff", "vr_sfd_accumulate", "vr_sfd_read", "vr_sfd_fdiff_dev",
            "vr_sfd_get_params", "vr_sfd_get_state", "vr_sfd_set_state", "vr_adam_step", "vr_unpack_params", "vr_set_option", "vr_kat_pcg", "vr_kat_gaussian",
-           "vr_kat_camera_rays", "vr_kat_events", "vr_kat_libm", "vr_kat_erfinv"]
+           "vr_kat_camera_rays", "vr_kat_events", "vr_kat_gather", "vr_kat_fdiff", "vr_kat_libm", "vr_kat_erfinv"]
 
 
 class RenderParams(C.Structure):
@@ -112,6 +112,8 @@ def lib():
     L.vr_kat_gaussian.argtypes = [vp, ci] + [fp] * 11
     L.vr_kat_camera_rays.argtypes = [vp, ci, fp, fp, fp]
     L.vr_kat_events.argtypes = [vp, fp, fp, ci, fp, fp, fp, C.POINTER(ci)]
+    L.vr_kat_gather.argtypes = [vp, ci, fp, fp, ci, fp, fp]
+    L.vr_kat_fdiff.argtypes = [vp, ci, ci, fp, fp, fp, fp, fp]
     L.vr_kat_libm.argtypes = [vp, ci, fp, fp, fp, fp]
     L.vr_kat_erfinv.argtypes = [vp, ci, fp, fp]
     _lib = L
@@ -344,6 +346,22 @@ class Context:
         t = np.empty(cap, np.float32); e = np.empty(cap, np.int32); idx = np.empty(cap, np.uint32); n = C.c_int(0)
         self._ck(self.L.vr_kat_events(self.h, _ptr(_f32(o)), _ptr(_f32(d)), cap, _ptr(t), _ptr(e), _ptr(idx), C.byref(n)))
         return t[:n.value], e[:n.value], idx[:n.value]
+
+    def kat_gather(self, o, d, cap=16):
+        """overlap sets of a batch of rays through the wavefront traversal kernel: counts[n], idx[n, cap] (original indices)"""
+        o, d = _f32(o), _f32(d)
+        n = o.shape[0]
+        cnt = np.empty(n, np.int32); idx = np.empty((n, cap), np.uint32)
+        self._ck(self.L.vr_kat_gather(self.h, n, _ptr(o), _ptr(d), cap, _ptr(cnt), _ptr(idx)))
+        return cnt, idx
+
+    def kat_fdiff(self, n, bits_base, bits_plus, loss_base, loss_plus):
+        """F_diff[n] in int64 fixed point (2^-32) from per-pixel recorded-set bitmaps [npix, (n+31)//32] and losses [npix]"""
+        b0 = np.ascontiguousarray(bits_base, np.uint32); b1 = np.ascontiguousarray(bits_plus, np.uint32)
+        l0, l1 = _f32(loss_base), _f32(loss_plus)
+        F = np.empty(n, np.int64)
+        self._ck(self.L.vr_kat_fdiff(self.h, l0.size, n, _ptr(b0), _ptr(b1), _ptr(l0), _ptr(l1), _ptr(F)))
+        return F
 
     def kat_libm(self, x):
         x = _f32(x); n = x.size

@@ -178,6 +178,16 @@ int vr_kat_gaussian(vr_context* ctx, int n, const float* o3, const float* d3, co
 int vr_kat_camera_rays(vr_context* ctx, int n, const float* uv2, float* o3, float* d3);
 int vr_kat_events(vr_context* ctx, const float* o3, const float* d3, int cap, float* t, int32_t* entering,
                   uint32_t* index, int* n_events);
+/* the wavefront engine's own free-flight traversal kernel (quantised hierarchy, candidate queue, batched quadric tests) on n
+ * caller rays, nothing pruned: counts[n] = components overlapped (gmm.h:457-515: the quadric test decides), idx[n*cap] = their
+ * original indices in gather order (first min(count, 16, cap); unused entries 0xffffffff).  Ray origins farther out than the
+ * hierarchy was built for trigger the same rebuild a far camera does. */
+int vr_kat_gather(vr_context* ctx, int n, const float* o3, const float* d3, int cap, int32_t* counts, uint32_t* idx);
+/* the localised loss difference of the SFD estimator (inverse_integrator.h:157-179) on caller-supplied recorded sets
+ * (bitmaps: (n+31)/32 words per pixel, bit g = Gaussian g) and per-pixel losses: F_fixed[n] = sum over the pixels in
+ * base[g] | plus[g] of round(loss_plus * 2^32) - round(loss_base * 2^32), exact integers */
+int vr_kat_fdiff(vr_context* ctx, int npix, int n, const uint32_t* bits_base, const uint32_t* bits_plus, const float* loss_base,
+                 const float* loss_plus, int64_t* F_fixed);
 int vr_kat_libm(vr_context* ctx, int n, const float* x, float* sin_out, float* cos_out, float* acos_out);
 int vr_kat_erfinv(vr_context* ctx, int n, const double* x, double* y);
 

@@ -207,16 +207,20 @@ def render_samples(gmm: Gmm, lights, env, cam: Camera, integrator: int, W: int, 
     return (out, mg) if margins else out
 
 
-def sample_sensitivity(gmm: Gmm, lights, env, cam, integrator, W, H, spp, rtol=2e-5, atol=1e-7, **kw):
+def sample_sensitivity(gmm: Gmm, lights, env, cam, integrator, W, H, spp, rtol=2e-5, atol=1e-7, response=False, **kw):
     """Samples whose value moves by more than rtol under a few-ulp perturbation of a free-flight distance or a sampled
-    optical depth (perturb modes 1..4): returns (samples[..., 4], sensitive[...] bool, margin[...])."""
+    optical depth (perturb modes 1..4): returns (samples[..., 4], sensitive[...] bool, margin[...]) and, with
+    response=True, also the largest absolute move of any channel under the four perturbations."""
     base, mg = render_samples(gmm, lights, env, cam, integrator, W, H, spp, margins=True, **kw)
     sens = np.zeros(base.shape[:-1], bool)
+    resp = np.zeros(base.shape[:-1], np.float32)
     for mode in (1, 2, 3, 4):
         alt = render_samples(gmm, lights, env, cam, integrator, W, H, spp, perturb=mode, **kw)
-        d = np.abs(alt[..., :3] - base[..., :3]) > atol + rtol * np.abs(base[..., :3])
+        dev = np.abs(alt[..., :3] - base[..., :3])
+        d = dev > atol + rtol * np.abs(base[..., :3])
         sens |= d.any(axis=-1) | (alt[..., 3] != base[..., 3])
-    return base, sens, mg
+        resp = np.maximum(resp, dev.max(axis=-1))
+    return (base, sens, mg, resp) if response else (base, sens, mg)
 
 
 def libm_batch(x):

@@ -45,6 +45,12 @@ def golden_march():
 
 
 @pytest.fixture(scope="session")
+def golden_r2():
+    """per-sample radiance, black-environment sphere images, far / scaled scenes from the reference (oracle/make_golden_r2.py)"""
+    return np.load(os.path.join(GOLD, "golden_r2.npz"))
+
+
+@pytest.fixture(scope="session")
 def scenegen():
     return load_pkg_module("scenegen")
 
@@ -60,6 +66,9 @@ CAMS = {
     "pin": dict(kind="pinhole", pos=(0, 1, 6), look=(0, 1, 0), fov=0.78539816339),
     "pin2": dict(kind="pinhole", pos=(2.5, 1.8, 3.5), look=(0, 0.9, 0), fov=0.6),
     "ortho": dict(kind="ortho", pos=(0, 1, 6), look=(0, 1, 0), fov=0.78539816339),
+    # the "pin" camera moved / scaled with the far and x50 variants of rand300 (oracle/make_golden_r2.py)
+    "pin_far": dict(kind="pinhole", pos=(100, -49, 206), look=(100, -49, 200), fov=0.78539816339),
+    "pin_x50": dict(kind="pinhole", pos=(0, 50, 300), look=(0, 50, 0), fov=0.78539816339),
 }
 ENV = (0.53, 0.81, 0.92)
 
@@ -72,3 +81,15 @@ def decode_record(raw: np.ndarray):
         c = int(raw[off]); off += 1
         out.append(raw[off:off + c].astype(np.uint32)); off += c
     return out
+
+
+_BIG_SCENES = {}
+
+
+def big_scene(scenegen, name):
+    """the seeded benchmark mixtures of SURVEY.md 8(d) (generation is a Python loop: 200k components take ~20 s, once per session)"""
+    if name not in _BIG_SCENES:
+        _BIG_SCENES[name] = {"c1": lambda: scenegen.generate(1000, 1),
+                             "c2": lambda: scenegen.generate(10000, 2, nonuniform=True),
+                             "c3": lambda: scenegen.generate(200000, 3, albedo_range=(0.9, 0.999))}[name]()
+    return _BIG_SCENES[name]

@@ -53,7 +53,7 @@ def compare(vr, ctx, scene, cam_name, integ, W, H, spp, window=None, label=""):
     g = ctx.samples(ww * wh, spp).reshape(wh, ww, spp, 4)
     t0 = time.time()
     gm = ob.Gmm(scene)
-    o, sens, mg = ob.sample_sensitivity(gm, scene["lights"], ENV, oc, it_o, W, H, spp, window=window)
+    o, sens, mg, resp = ob.sample_sensitivity(gm, scene["lights"], ENV, oc, it_o, W, H, spp, window=window, response=True)
     t_or = time.time() - t0
     ref_img = ob.render(gm, scene["lights"], ENV, oc, it_o, W, H, spp, window=window)[y0:y1, x0:x1]
     img = img[y0:y1, x0:x1]
@@ -66,6 +66,8 @@ def compare(vr, ctx, scene, cam_name, integ, W, H, spp, window=None, label=""):
     w4 = within(1e-4)
     bad = ~w4
     unexplained = bad & ~sens
+    # how far the outside samples are, in units of the oracle's own move under a 1-ulp perturbation
+    ratio = (d.max(-1) / np.maximum(resp, 1e-12))[bad]
     pix_ok = (np.abs(img - ref_img) <= 1e-6 + 1e-4 * np.abs(ref_img)).all(-1)
     pix_clean = ~sens.any(-1)                      # pixels none of whose samples is sensitive
     rel = np.abs(img - ref_img) / np.maximum(np.abs(ref_img), 1e-3)
@@ -76,7 +78,8 @@ def compare(vr, ctx, scene, cam_name, integ, W, H, spp, window=None, label=""):
              pixels=int(pix_ok.size), pixels_within_1e4=float(pix_ok.mean()), pixels_clean=float(pix_clean.mean()),
              clean_pixels_outside=int((~pix_ok & pix_clean).sum()), pixel_max_rel=float(rel.max()),
              image_mean_rel=float(abs(img.mean() - ref_img.mean()) / max(ref_img.mean(), 1e-9)), oracle_s=round(t_or, 2),
-             overflow_samples=int(st["overflow_samples"]))
+             overflow_samples=int(st["overflow_samples"]), outside_max_ratio_to_response=float(ratio.max()) if ratio.size else 0.0,
+             outside_median_ratio_to_response=float(np.median(ratio)) if ratio.size else 0.0)
     if unexplained.any():
         idx = np.argwhere(unexplained)[:6]
         r["unexplained_examples"] = [dict(at=[int(v) for v in i], gpu=[float(v) for v in g[tuple(i)]], oracle=[float(v) for v in o[tuple(i)]],
@@ -96,6 +99,11 @@ def main():
     for sc, cam, spp in (("two_gauss", "pin", 16), ("rand50", "pin", 16), ("rand50", "pin2", 9), ("rand300", "pin", 16), ("rand2k", "pin", 16), ("rand2k", "pin2", 4)):
         for integ in ("ms", "ss"):
             cases.append((f"{sc}/{cam}/{integ}/{spp} 32x32", sg.load_gmm(os.path.join(scenes, sc + ".txt")), cam, integ, 32, 32, spp, None))
+    CAMS["pin_far"] = dict(kind="pinhole", pos=(100, -49, 206), look=(100, -49, 200), fov=0.78539816339)
+    CAMS["pin_x50"] = dict(kind="pinhole", pos=(0, 50, 300), look=(0, 50, 0), fov=0.78539816339)
+    for sc, cam in (("rand300_far", "pin_far"), ("rand300_x50", "pin_x50")):
+        for integ in ("ms", "ss"):
+            cases.append((f"{sc}/{cam}/{integ}/16 32x32", sg.load_gmm(os.path.join(scenes, sc + ".txt")), cam, integ, 32, 32, 16, None))
     if not a.quick:
         c1 = sg.generate(1000, 1)
         cases.append(("C1 1k ss 512^2x64 window 32x32", c1, "pin", "ss", 512, 512, 64, (240, 200, 272, 232)))
@@ -106,7 +114,7 @@ def main():
         cases.append(("C3 200k ms 2048^2x64 window 16x16", c3, "pin", "ms", 2048, 2048, 64, (1000, 1100, 1016, 1116)))
     res = []
     cols = ("samples", "identical", "within_1e5", "within_1e4", "within_1e3", "bounce_equal", "sensitive", "outside", "outside_sensitive",
-            "outside_unexplained", "pixels_within_1e4", "pixels_clean", "clean_pixels_outside", "pixel_max_rel", "image_mean_rel")
+            "outside_unexplained", "pixels_within_1e4", "pixels_clean", "clean_pixels_outside", "pixel_max_rel", "image_mean_rel", "outside_max_ratio_to_response", "outside_median_ratio_to_response")
     print("case | " + " | ".join(cols))
     for label, scene, cam, integ, W, H, spp, win in cases:
         r = compare(vr, ctx, scene, cam, integ, W, H, spp, window=win, label=label)
