@@ -104,6 +104,8 @@ void vr_destroy(vr_context* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     sfd_destroy(ctx);
+    comm_destroy(ctx);
+    ctx->comm_scratch.release();
     for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
                       &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->lam, &ctx->qnodes, &ctx->lg_start, &ctx->lg_gi,
                       &ctx->lg_dmin, &ctx->spheres, &ctx->lpos, &ctx->lint,

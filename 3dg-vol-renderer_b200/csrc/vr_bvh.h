@@ -60,7 +60,9 @@ struct BoxReach { float R, X; };
 BoxReach box_reach(int n, const float* lo, const float* hi, const float* cam_pos, float* bb_lo, float* bb_hi);
 // the reach a camera at cam_pos needs over a mixture bounded by bb_lo/bb_hi (film-plane offsets of camera.h:45-73 included)
 BoxReach box_reach_of(const float* bb_lo, const float* bb_hi, const float* cam_pos);
-constexpr double kBoxKappa = 0.012;
+// kappa: tools/gather_sweep.py finds no missed component on 60 000 camera and interior rays of the C2 mixture even at 0, and no
+// measurable cost up to 0.06 (gpurun_out r2c2) -- 0.03 covers ~2.5 ulp of the discriminant
+constexpr double kBoxKappa = 0.03;
 void inflate_boxes(int n, float* lo, float* hi, const float* lam, BoxReach reach, double kappa = kBoxKappa);
 
 }  // namespace vr

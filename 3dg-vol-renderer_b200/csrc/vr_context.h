@@ -92,6 +92,10 @@ struct vr_context {
     unsigned int* h_wave_counters = nullptr;       // pinned, kMaxWaveParts * kWaveCounters
     // ---- inverse
     vr::SfdState* sfd = nullptr;
+    // ---- communicator of the inverse path's one collective (vr_comm.cu); comm is an ncclComm_t
+    void* comm = nullptr;
+    int comm_rank = 0, comm_size = 1;
+    vr::DevBuf comm_scratch;
 
     vr::SceneDev scene_dev() const;
 };
@@ -106,6 +110,8 @@ int ensure_camera_reach(vr_context* c);              // ... for the camera curre
 void cancel_light_grid_job(vr_context* c);  // vr_api.cu: joins and drops a speculative grid build
 int ensure_light_grids(vr_context* c);  // vr_api.cu  // mean3/cov6/density/albedo device buffers already filled
 void sfd_destroy(vr_context* c);
+int sfd_reduce_buffer(vr_context* c, long long** buf, size_t* count);   // vr_inverse.cu
+void comm_destroy(vr_context* c);                                        // vr_comm.cu
 }  // namespace vr
 
 #define VR_CUDA(call)                                                        \

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 #include "vr_context.h"
 
@@ -20,17 +21,30 @@ struct SfdState {
     int n = 0, t = 0;
     float lr = 1e-2f, beta1 = 0.9f, beta2 = 0.999f, adam_eps = 1e-8f;
     int tw = 0, th = 0;
-    DevBuf params, params_plus, eps, m, v, grad, target, loss_base, loss_plus, bits_base, fdiff_fixed, signs, fdiff_d,
-        loss_acc;
+    // fdiff_fixed: S * n fixed-point partial sums FOLLOWED by two int64 of loss accumulators, so that one all-reduce covers both
+    DevBuf params, params_plus, eps, m, v, grad, target, loss_base, loss_plus, bits_base, fdiff_fixed, signs, fdiff_d;
+    std::vector<DevBuf> view_targets;   // targets of a multi-view fit kept resident (vr_sfd_set_target_view / vr_sfd_select_view)
+    int view = -1;                      // -1: `target` (vr_sfd_set_target)
+    const float* target_ptr() const { return view >= 0 ? view_targets[(size_t)view].as<float>() : target.as<float>(); }
     int fdiff_S = 0;
+    long long* loss_acc() const { return fdiff_fixed.as<long long>() + (size_t)fdiff_S * n; }
 };
+
+// the buffer one all-reduce per iteration sums over devices (vr_comm.cu): S * n partial sums + the two loss accumulators
+int sfd_reduce_buffer(vr_context* c, long long** buf, size_t* count) {
+    if (!c || !c->sfd || c->sfd->fdiff_S <= 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_sfd_allreduce: nothing accumulated (vr_sfd_reset_fdiff / vr_sfd_accumulate first)");
+    *buf = c->sfd->fdiff_fixed.as<long long>();
+    *count = (size_t)c->sfd->fdiff_S * c->sfd->n + 2;
+    return VR_OK;
+}
 
 void sfd_destroy(vr_context* c) {
     if (!c->sfd) return;
     SfdState* s = c->sfd;
     for (DevBuf* b : {&s->params, &s->params_plus, &s->eps, &s->m, &s->v, &s->grad, &s->target, &s->loss_base, &s->loss_plus,
-                      &s->bits_base, &s->fdiff_fixed, &s->signs, &s->fdiff_d, &s->loss_acc})
+                      &s->bits_base, &s->fdiff_fixed, &s->signs, &s->fdiff_d})
         b->release();
+    for (DevBuf& b : s->view_targets) b.release();
     delete s;
     c->sfd = nullptr;
 }
@@ -174,7 +188,31 @@ int vr_sfd_set_target(vr_context* ctx, int width, int height, const float* targe
     VR_CUDA(s->target.ensure(bytes));
     VR_CUDA(cudaMemcpyAsync(s->target.p, target_rgb, bytes, cudaMemcpyHostToDevice, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
-    s->tw = width; s->th = height;
+    s->tw = width; s->th = height; s->view = -1;
+    return VR_OK;
+}
+
+// multi-view fits: every view's target is uploaded ONCE and stays on the device; vr_sfd_select_view picks the one the next
+// vr_sfd_accumulate compares against (all views share one image size)
+int vr_sfd_set_target_view(vr_context* ctx, int view, int width, int height, const float* target_rgb) {
+    if (!ctx || !ctx->sfd || view < 0 || view >= 4096 || width <= 0 || height <= 0 || !target_rgb)
+        return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_set_target_view: bad arguments (vr_sfd_begin first)");
+    VR_CUDA(cudaSetDevice(ctx->device));
+    SfdState* s = ctx->sfd;
+    if (!s->view_targets.empty() && (s->tw != width || s->th != height) && s->view >= 0)
+        return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_set_target_view: all views must share one image size");
+    if ((size_t)view >= s->view_targets.size()) s->view_targets.resize((size_t)view + 1);
+    const size_t bytes = (size_t)3 * width * height * 4;
+    VR_CUDA(s->view_targets[(size_t)view].ensure(bytes));
+    VR_CUDA(cudaMemcpyAsync(s->view_targets[(size_t)view].p, target_rgb, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    s->tw = width; s->th = height; s->view = view;
+    return VR_OK;
+}
+int vr_sfd_select_view(vr_context* ctx, int view) {
+    if (!ctx || !ctx->sfd || view < 0 || (size_t)view >= ctx->sfd->view_targets.size() || !ctx->sfd->view_targets[(size_t)view].p)
+        return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_select_view: no target was set for this view");
+    ctx->sfd->view = view;
     return VR_OK;
 }
 
@@ -182,10 +220,8 @@ int vr_sfd_reset_fdiff(vr_context* ctx, int S) {
     if (!ctx || !ctx->sfd || S <= 0) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_reset_fdiff: bad arguments");
     VR_CUDA(cudaSetDevice(ctx->device));
     SfdState* s = ctx->sfd;
-    VR_CUDA(s->fdiff_fixed.ensure((size_t)S * s->n * 8));
-    VR_CUDA(s->loss_acc.ensure(16));
-    VR_CUDA(cudaMemsetAsync(s->fdiff_fixed.p, 0, (size_t)S * s->n * 8, ctx->stream));
-    VR_CUDA(cudaMemsetAsync(s->loss_acc.p, 0, 16, ctx->stream));
+    VR_CUDA(s->fdiff_fixed.ensure(((size_t)S * s->n + 2) * 8));
+    VR_CUDA(cudaMemsetAsync(s->fdiff_fixed.p, 0, ((size_t)S * s->n + 2) * 8, ctx->stream));
     s->fdiff_S = S;
     return VR_OK;
 }
@@ -219,8 +255,8 @@ int vr_sfd_accumulate(vr_context* ctx, const vr_render_params* rp, int S, const 
     VR_CUDA(s->bits_base.ensure(bits_bytes));
     VR_CUDA(cudaMemcpyAsync(s->bits_base.p, ctx->record_bits.p, bits_bytes, cudaMemcpyDeviceToDevice, st));
     if (npix_owned > 0)
-        pixel_loss_kernel<<<(npix_owned + 127) / 128, 128, 0, st>>>(o, ctx->image.as<float>(), s->target.as<float>(),
-                                                                     s->loss_base.as<float>(), s->loss_acc.as<long long>());
+        pixel_loss_kernel<<<(npix_owned + 127) / 128, 128, 0, st>>>(o, ctx->image.as<float>(), s->target_ptr(),
+                                                                     s->loss_base.as<float>(), s->loss_acc());
     // ---- S perturbed renders (inverse_integrator.h:140-188)
     for (int k = 0; k < S; ++k) {
         perturb_kernel<<<(D + 255) / 256, 256, 0, st>>>(D, s->params.as<float>(), s->signs.as<signed char>() + (size_t)k * D,
@@ -230,14 +266,13 @@ int vr_sfd_accumulate(vr_context* ctx, const vr_render_params* rp, int S, const 
         rc = render_device_impl(ctx, &p, nullptr);
         if (rc) return rc;
         if (npix_owned > 0) {
-            pixel_loss_kernel<<<(npix_owned + 127) / 128, 128, 0, st>>>(o, ctx->image.as<float>(), s->target.as<float>(),
+            pixel_loss_kernel<<<(npix_owned + 127) / 128, 128, 0, st>>>(o, ctx->image.as<float>(), s->target_ptr(),
                                                                          s->loss_plus.as<float>(), nullptr);
             launch_fdiff(o, words, n, s->bits_base.as<uint32_t>(), ctx->record_bits.as<uint32_t>(), s->loss_base.as<float>(),
                          s->loss_plus.as<float>(), s->fdiff_fixed.as<long long>() + (size_t)k * n, st);
         }
     }
-    VR_CUDA(cudaStreamSynchronize(st));
-    VR_CUDA(cudaGetLastError());
+    VR_CUDA(cudaGetLastError());   // no synchronisation: vr_sfd_allreduce* / vr_sfd_apply / vr_sfd_read follow on the same stream
     return VR_OK;
 }
 
@@ -254,7 +289,7 @@ int vr_sfd_read(vr_context* ctx, double* F_diff, double* loss_sum) {
     }
     if (loss_sum) {
         long long l = 0;
-        VR_CUDA(cudaMemcpyAsync(&l, s->loss_acc.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        VR_CUDA(cudaMemcpyAsync(&l, s->loss_acc(), 8, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaStreamSynchronize(ctx->stream));
         *loss_sum = (double)l / kFixedScale;
     }

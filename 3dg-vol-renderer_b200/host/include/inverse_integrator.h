@@ -7,8 +7,12 @@
 // render, S sign vectors s in {-1,+1}^D, S recorded renders of params + s*eps, per-Gaussian loss
 // differences over the union of the pixels either render touched, grad = mean_s F_diff*s/eps, Adam.
 // All of it runs on the device behind vr_sfd_begin / vr_sfd_accumulate / vr_sfd_apply; with several
-// devices (VR_DEVICES) the image rows are split, the per-Gaussian partial sums (exact fixed point)
-// are added on the host in device order, and every device applies the same Adam step.
+// devices (VR_DEVICES) the image rows are split, the per-Gaussian partial sums (exact int64 fixed point)
+// are summed by ONE ncclAllReduce per iteration on the devices' streams (Session::allreduce_sfd,
+// csrc/vr_comm.cu; the reduction inverse_integrator.h:157-198 sums over pixels, hence over devices),
+// and every device applies the same Adam step.  The SFD renders use the FORWARD integrator's camera,
+// as the reference does (:119,153 go through forward_integrator->render); lights and camera are
+// uploaded again at the top of every iteration, so nothing depends on what a save render left behind.
 //
 // Differences, all additive: the sign vectors come from a SEEDED mt19937 (SFDDConfig::seed; the
 // reference seeds from std::random_device) so runs are reproducible; the optimised
@@ -146,8 +150,9 @@ public:
 
         vrhost::Session& dev = vrhost::Session::get();
         const int nd = dev.num_devices();
+        const Camera& sfd_camera = *forward_integrator->get_camera();
         for (int i = 0; i < nd; ++i) {
-            vrhost::upload_lights_and_camera(dev, i, result, *camera);
+            vrhost::upload_lights_and_camera(dev, i, result, sfd_camera);
             dev.check(i, vr_sfd_begin(dev.ctx(i), n, params.data(), eps.data(), cfg.lr, 0.9f, 0.999f, 1e-8f));
             dev.check(i, vr_sfd_set_target(dev.ctx(i), W, H, I_ref.data()));
         }
@@ -164,13 +169,13 @@ public:
             first_iter = ck.iteration;
         }
         std::vector<int8_t> signs(size_t(S) * D);
-        std::vector<double> F(size_t(S) * n), Fpart(size_t(S) * n);
         Image I_base(W, H);
         const auto t0 = clock::now();
 
         for (int iter = first_iter; iter < cfg.max_iters; ++iter) {
             for (int8_t& s : signs) s = (rng() & 1u) ? 1 : -1;
             vrhost::for_each_device(dev, [&](int i) {
+                vrhost::upload_lights_and_camera(dev, i, result, sfd_camera);
                 vr_render_params rp{};
                 rp.integrator = VR_INTEGRATOR_MULTI_SCATTER; rp.solver = forward_integrator->get_solver();
                 rp.width = W; rp.height = H; rp.spp = forward_integrator->get_num_samples(); rp.min_bounces = forward_integrator->get_min_bounces();
@@ -178,16 +183,8 @@ public:
                 dev.check(i, vr_sfd_reset_fdiff(dev.ctx(i), S));
                 dev.check(i, vr_sfd_accumulate(dev.ctx(i), &rp, S, signs.data()));
             });
-            if (nd == 1) {
-                dev.check(0, vr_sfd_apply(dev.ctx(0), S, signs.data(), nullptr, nullptr));
-            } else {
-                std::fill(F.begin(), F.end(), 0.0);
-                for (int i = 0; i < nd; ++i) {
-                    dev.check(i, vr_sfd_read(dev.ctx(i), Fpart.data(), nullptr));
-                    for (size_t k = 0; k < F.size(); ++k) F[k] += Fpart[k];
-                }
-                for (int i = 0; i < nd; ++i) dev.check(i, vr_sfd_apply(dev.ctx(i), S, signs.data(), F.data(), nullptr));
-            }
+            dev.allreduce_sfd();   // nd > 1: one all-reduce of the S * n int64 partial sums, in place on the devices
+            for (int i = 0; i < nd; ++i) dev.check(i, vr_sfd_apply(dev.ctx(i), S, signs.data(), nullptr, nullptr));
             if (cfg.checkpoint_every > 0 && !cfg.checkpoint_path.empty() && (iter + 1) % cfg.checkpoint_every == 0) {
                 vrhost::SfdCheckpoint ck;
                 ck.iteration = iter + 1;

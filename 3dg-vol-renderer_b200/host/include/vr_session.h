@@ -21,6 +21,7 @@ namespace vrhost {
 class Session {
     std::vector<vr_context*> ctxs_;
     std::vector<int> devices_;
+    bool comm_ready_ = false;
 
     Session() {
         const char* env = std::getenv("VR_DEVICES");
@@ -56,6 +57,18 @@ public:
     int num_devices() const { return int(ctxs_.size()); }
     int device_id(int i) const { return devices_[size_t(i)]; }
     vr_context* ctx(int i) const { return ctxs_[size_t(i)]; }
+
+    // The inverse path's one collective (reference reduction inverse_integrator.h:157-198): the contexts of
+    // this process form one NCCL communicator (ncclCommInitAll, made on first use) and every iteration sums the int64
+    // partial F_diff of all devices in place, on the devices' own streams -- no copy to the host.
+    void allreduce_sfd() {
+        if (num_devices() < 2) return;
+        if (!comm_ready_) {
+            if (vr_comm_init_all(ctxs_.data(), num_devices()) != VR_OK) throw std::runtime_error(std::string("volrender_b200: ") + vr_last_error(ctxs_[0]));
+            comm_ready_ = true;
+        }
+        if (vr_sfd_allreduce_all(ctxs_.data(), num_devices()) != VR_OK) throw std::runtime_error(std::string("volrender_b200: ") + vr_last_error(ctxs_[0]));
+    }
 
     // status -> exception
     void check(int i, int rc) const {

@@ -11,7 +11,8 @@
 //              [--repeat 1]
 //   vol_render --scene S.txt --inverse target.ppm [--iters 1000 --save-every 25 --sfd-samples 4 --lr 0.01
 //              --seed N --final-spp 16384 --out-dir ./sfd_output --save-scene fitted.txt
-//              --checkpoint state.bin --checkpoint-every 50 --resume state.bin --save-params params.f32]
+//              --checkpoint state.bin --checkpoint-every 50 --resume state.bin --save-params params.f32
+//              --inverse-camera-pos x,y,z]
 // Devices: VR_DEVICES="0,1,..." (default "0").
 #include <chrono>
 #include <cstdio>
@@ -114,7 +115,14 @@ int main(int argc, char** argv) {
             cfg.output_dir = a.str("out-dir", cfg.output_dir);
             cfg.checkpoint_path = a.str("checkpoint", ""); cfg.checkpoint_every = a.i("checkpoint-every", 0);
             cfg.resume_from = a.str("resume", ""); cfg.verbose = !a.has("quiet");
-            StochasticFiniteDiffInverseIntegrator inv(camera, fwd, cfg);
+            // the reference's InverseIntegrator never uses its own camera member: every SFD render goes through the forward
+            // integrator's (inverse_integrator.h:119,153).  --inverse-camera-pos builds it from another camera to show that.
+            std::shared_ptr<Camera> inv_camera = camera;
+            if (a.has("inverse-camera-pos")) {
+                const Eigen::Vector3f ip = a.v3("inverse-camera-pos", pos);
+                inv_camera = std::make_shared<Pinhole_Camera>(ip, (look - ip).normalized(), fov);
+            }
+            StochasticFiniteDiffInverseIntegrator inv(inv_camera, fwd, cfg);
             const auto t0 = std::chrono::high_resolution_clock::now();
             const bool ok = inv.optimize(scene, target);
             const std::chrono::duration<double> el = std::chrono::high_resolution_clock::now() - t0;

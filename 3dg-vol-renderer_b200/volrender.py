@@ -29,7 +29,8 @@ STATUS = {0: "VR_OK", 1: "VR_ERR_INVALID_ARGUMENT", 2: "VR_ERR_CUDA", 3: "VR_ERR
 SYMBOLS = ["vr_create", "vr_destroy", "vr_last_error", "vr_version", "vr_device_count", "vr_stream", "vr_set_gmm",
            "vr_set_gmm_params", "vr_set_smm", "vr_set_lights", "vr_set_camera", "vr_render", "vr_render_device",
            "vr_image_dev", "vr_get_recorded", "vr_get_samples", "vr_transmittance", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
-           "vr_sfd_apply", "vr_sfd_reset_fdiff", "vr_sfd_accumulate", "vr_sfd_read", "vr_sfd_fdiff_dev",
+           "vr_sfd_set_target_view", "vr_sfd_select_view", "vr_sfd_apply", "vr_sfd_reset_fdiff", "vr_sfd_accumulate", "vr_sfd_read", "vr_sfd_fdiff_dev", "vr_comm_available", "vr_comm_version",
+           "vr_comm_unique_id", "vr_comm_init_rank", "vr_comm_init_all", "vr_comm_destroy", "vr_comm_size", "vr_sfd_allreduce", "vr_sfd_allreduce_all",
            "vr_sfd_get_params", "vr_sfd_get_state", "vr_sfd_set_state", "vr_adam_step", "vr_unpack_params", "vr_set_option", "vr_kat_pcg", "vr_kat_gaussian",
            "vr_kat_camera_rays", "vr_kat_events", "vr_kat_gather", "vr_kat_fdiff", "vr_kat_libm", "vr_kat_erfinv"]
 
@@ -96,12 +97,21 @@ def lib():
     L.vr_transmittance.argtypes = [vp, ci, fp, fp, fp, fp]
     L.vr_sfd_begin.argtypes = [vp, ci, fp, fp, C.c_float, C.c_float, C.c_float, C.c_float]
     L.vr_sfd_set_target.argtypes = [vp, ci, ci, fp]
+    L.vr_sfd_set_target_view.argtypes = [vp, ci, ci, ci, fp]
+    L.vr_sfd_select_view.argtypes = [vp, ci]
     L.vr_sfd_fdiff.argtypes = [vp, C.POINTER(RenderParams), ci, fp, fp, fp, fp]
     L.vr_sfd_apply.argtypes = [vp, ci, fp, fp, fp]
     L.vr_sfd_reset_fdiff.argtypes = [vp, ci]
     L.vr_sfd_accumulate.argtypes = [vp, C.POINTER(RenderParams), ci, fp]
     L.vr_sfd_read.argtypes = [vp, fp, fp]
     L.vr_sfd_fdiff_dev.argtypes = [vp]; L.vr_sfd_fdiff_dev.restype = vp
+    L.vr_comm_unique_id.argtypes = [fp]
+    L.vr_comm_init_rank.argtypes = [vp, fp, ci, ci]
+    L.vr_comm_init_all.argtypes = [C.POINTER(vp), ci]
+    L.vr_comm_destroy.argtypes = [vp]
+    L.vr_comm_size.argtypes = [vp]
+    L.vr_sfd_allreduce.argtypes = [vp]
+    L.vr_sfd_allreduce_all.argtypes = [C.POINTER(vp), ci]
     L.vr_sfd_get_params.argtypes = [vp, fp]
     L.vr_sfd_get_state.argtypes = [vp, fp, fp, fp, C.POINTER(ci)]
     L.vr_sfd_set_state.argtypes = [vp, fp, fp, fp, ci]
@@ -265,6 +275,13 @@ class Context:
         t = _f32(target)
         self._ck(self.L.vr_sfd_set_target(self.h, t.shape[1], t.shape[0], _ptr(t)))
 
+    def sfd_set_target_view(self, view, target):
+        t = _f32(target)
+        self._ck(self.L.vr_sfd_set_target_view(self.h, view, t.shape[1], t.shape[0], _ptr(t)))
+
+    def sfd_select_view(self, view):
+        self._ck(self.L.vr_sfd_select_view(self.h, view))
+
     def sfd_fdiff(self, rp: RenderParams, signs):
         s = np.ascontiguousarray(signs, np.int8)
         S = s.shape[0]
@@ -283,6 +300,17 @@ class Context:
         F = np.zeros((S, self._sfd_n), np.float64); ls = np.zeros(1, np.float64)
         self._ck(self.L.vr_sfd_read(self.h, _ptr(F), _ptr(ls)))
         return F, float(ls[0])
+
+    # ---- the inverse path's collective (csrc/vr_comm.cu): NCCL all-reduce of the fixed-point partial sums on the context's stream
+    def comm_init_rank(self, unique_id: bytes, nranks: int, rank: int):
+        buf = (C.c_char * 128).from_buffer_copy(unique_id)
+        self._ck(self.L.vr_comm_init_rank(self.h, C.cast(buf, C.c_void_p), nranks, rank))
+
+    def comm_size(self) -> int:
+        return int(self.L.vr_comm_size(self.h))
+
+    def sfd_allreduce(self):
+        self._ck(self.L.vr_sfd_allreduce(self.h))
 
     def sfd_fdiff_dev(self) -> int:
         return int(self.L.vr_sfd_fdiff_dev(self.h) or 0)
@@ -373,3 +401,34 @@ class Context:
         x = np.ascontiguousarray(x, np.float64); y = np.empty_like(x)
         self._ck(self.L.vr_kat_erfinv(self.h, x.size, _ptr(x), _ptr(y)))
         return y
+
+
+def comm_available() -> bool:
+    return bool(lib().vr_comm_available())
+
+
+def comm_unique_id() -> bytes:
+    """ncclGetUniqueId through the library (rank 0 calls it, the 128 bytes go to every rank by the launcher's means)"""
+    buf = (C.c_char * 128)()
+    rc = lib().vr_comm_unique_id(C.cast(buf, C.c_void_p))
+    if rc:
+        raise VolRenderError(rc, "vr_comm_unique_id failed (NCCL unavailable?)")
+    return bytes(buf)
+
+
+def _handles(ctxs):
+    arr = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    return arr
+
+
+def comm_init_all(ctxs):
+    """one process driving several devices: ncclCommInitAll over the contexts (contexts on one device: peer-copy sums)"""
+    rc = lib().vr_comm_init_all(_handles(ctxs), len(ctxs))
+    if rc:
+        raise VolRenderError(rc, ctxs[0].L.vr_last_error(ctxs[0].h).decode())
+
+
+def sfd_allreduce_all(ctxs):
+    rc = lib().vr_sfd_allreduce_all(_handles(ctxs), len(ctxs))
+    if rc:
+        raise VolRenderError(rc, ctxs[0].L.vr_last_error(ctxs[0].h).decode())

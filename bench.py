@@ -165,20 +165,34 @@ class ClockSampler:
                     samples=len(sm))
 
 
-def run_inverse(a, cfg, scene, workload, rank, world, local_rank):
+def run_inverse(a, cfg, scene, workload, rank, world, local_rank, steps=None, warmup=None, cpu_baseline=True):
     """Config C4: inverse rendering.  One step = one StochasticFiniteDiffInverseIntegrator iteration
     (inverse_integrator.h:114-207) over ALL target views: per view a recorded base render and S recorded
     perturbed renders, per-Gaussian loss differences, then -- the one real exchange -- a SUM all-reduce of
-    the S*N int64 fixed-point partial sums over NCCL, and the same Adam step on every rank.
-    Views are dealt round-robin to the ranks (rows are split instead when views < ranks)."""
+    the S*N int64 fixed-point partial sums, enqueued by the library itself (vr_sfd_allreduce: ncclAllReduce on the
+    context's stream, csrc/vr_comm.cu), and the same Adam step on every rank.  torch.distributed only carries the
+    128-byte NCCL id to the ranks and times the run.  Views are dealt round-robin to the ranks (rows are split instead
+    when views < ranks); every view's target image is uploaded once and stays on its rank's device.
+    Returns the result dict on rank 0 (None elsewhere)."""
     import torch
     import torch.distributed as dist
     vr = _pkg("volrender"); sg = _pkg("scenegen"); mr = _pkg("multirank")
+    steps = steps or a.steps; warmup = a.warmup if warmup is None else warmup
     W, H, spp, S = cfg["W"], cfg["H"], cfg["spp"], cfg["S"]   # (main() has set the device and the process group)
     n_views = a.views or cfg["views"]
     N = cfg["n"]; D = 11 * N
     ctx = vr.Context(local_rank)
     ctx.set_lights(scene["lights"], ENV)
+    nccl_in_library = False
+    if world > 1:
+        if not vr.comm_available():
+            raise SystemExit("bench.py: NCCL not found by libvolrender_b200.so (libnccl.so.2)")
+        ident = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            ident = torch.frombuffer(bytearray(vr.comm_unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(ident, 0)
+        ctx.comm_init_rank(bytes(ident.cpu().numpy().tobytes()), world, rank)
+        nccl_in_library = ctx.comm_size() == world
     cams = [vr.camera_basis("pinhole", pos, look=(0, 1, 0), fov=0.78539816339) for pos in sg.orbit_cameras(n_views)]
     my_views, part_rank, part_count = mr.split_for_views(rank, world, n_views)
     # ---- setup (untimed): targets = renders of the target parameters; start = target + N(0, eps^2)
@@ -192,27 +206,24 @@ def run_inverse(a, cfg, scene, workload, rank, world, local_rank):
     targets = {}
     for v in my_views:
         ctx.set_camera(cams[v])
-        img, _ = ctx.render(rp_full)
-        targets[v] = torch.from_numpy(img).pin_memory()
+        targets[v], _ = ctx.render(rp_full)
     ctx.sfd_begin(p_start, eps, lr=1e-2)
-    fview = None
+    for v in my_views:
+        ctx.sfd_set_target_view(v, targets[v])               # resident: one H2D per view for the whole fit
     sign_rs = np.random.RandomState(4321)      # same stream on every rank: the sign vectors are shared
+    pinned_signs = torch.empty((S, D), dtype=torch.int8).pin_memory()
 
     def iteration():
-        nonlocal fview
-        signs = np.where(sign_rs.randint(0, 2, size=(S, D)) > 0, 1, -1).astype(np.int8)
+        pinned_signs.numpy()[:] = np.where(sign_rs.randint(0, 2, size=(S, D)) > 0, 1, -1)
+        signs = pinned_signs.numpy()
         ctx.sfd_reset(S)
         for v in my_views:
             ctx.set_camera(cams[v])
-            ctx.sfd_set_target(targets[v].numpy())           # H2D of the view's target, every iteration
-            ctx.sfd_accumulate(rp, signs)
-        if world > 1:
-            if fview is None:
-                fview = mr.device_int64_view(ctx.sfd_fdiff_dev(), S * N, local_rank)
-            mr.allreduce_fdiff_(fview)
-            torch.cuda.synchronize()
+            ctx.sfd_select_view(v)
+            ctx.sfd_accumulate(rp, signs)                    # H2D of the sign vectors, (1 + S) recorded renders, reductions
+        ctx.sfd_allreduce()                                   # NCCL on the context's stream (no-op on one rank)
         ctx.sfd_apply(signs, None)
-        return ctx.sfd_read(S)[1]                             # base L1 loss sum of this rank (D2H)
+        return ctx.sfd_read(S)[1]                             # total base L1 loss over all ranks and views (D2H)
 
     def barrier():
         torch.cuda.synchronize()
@@ -221,18 +232,15 @@ def run_inverse(a, cfg, scene, workload, rank, world, local_rank):
         torch.cuda.synchronize()
 
     losses = []
-    for _ in range(a.warmup):
+    for _ in range(warmup):
         losses.append(iteration())
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     barrier()
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
-    e0.record()
-    for _ in range(a.steps):
+    for _ in range(steps):
         losses.append(iteration())
-    e1.record()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
@@ -240,41 +248,37 @@ def run_inverse(a, cfg, scene, workload, rank, world, local_rank):
         t = torch.tensor([wall_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         wall_ms = float(t.item())
-        lt = torch.tensor(losses, dtype=torch.float64, device="cuda")
-        dist.all_reduce(lt)
-        losses = lt.tolist()
     params_end = ctx.sfd_params()
     ctx.close()
-    if world > 1:
-        dist.barrier(); dist.destroy_process_group()
     if rank != 0:
-        return
-    ms_per_step = wall_ms / a.steps
+        return None
+    ms_per_step = wall_ms / steps
     samples_per_iter = n_views * (1 + S) * W * H * spp
     mean_loss = [l / (n_views * W * H) for l in losses]
     cpu = None
-    if not a.no_cpu_baseline:
+    if cpu_baseline and not a.no_cpu_baseline:
         c2 = dict(cfg); c2["integrator"] = "ms"
         cpu = cpu_render_sample(c2, scene)
         cpu = dict(cpu, value=cpu["value"] * 1e6 / samples_per_iter, unit="iterations/s",
                    sample=cpu["sample"] + f"; iterations/s derived as render throughput / {samples_per_iter} samples per iteration "
                                           "(the (1+S)*views renders are >99% of a reference iteration)")
-    print(json.dumps({
-        "metric": "inverse-render iters/sec", "value": 1e3 / ms_per_step, "unit": "iterations/s", "n_gpus": world, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+    return {
+        "metric": "inverse-render iters/sec", "value": 1e3 / ms_per_step, "unit": "iterations/s", "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload, "views": n_views, "image": [W, H], "spp": spp, "S": S, "parameters": D,
                    "partition": f"views round-robin over {world} rank(s)" if n_views >= world else f"rows interleaved over {world} rank(s)",
-                   "collective": "all_reduce(SUM, int64, S*N) of the fixed-point F_diff sums per iteration" if world > 1 else "none (1 rank)",
+                   "collective": ("ncclAllReduce(SUM, int64, S*N+2) of the fixed-point F_diff sums per iteration, enqueued by "
+                                  "libvolrender_b200.so on the context's stream (vr_sfd_allreduce)") if nccl_in_library else "none (1 rank)",
                    "timing": "host wall clock around K iterations between device synchronisations (each iteration ends in a D2H read), max over ranks",
                    "l2": "each render streams a pass buffer larger than L2"},
         "e2e": {"value": 1e3 / ms_per_step, "unit": "iterations/s", "ms_per_step": ms_per_step,
-                "h2d_bytes_per_step": len(my_views) * (3 * W * H * 4 + S * D) + S * D, "d2h_bytes_per_step": 8},
+                "h2d_bytes_per_step": len(my_views) * S * D, "d2h_bytes_per_step": 8 + S * N * 8},
         "throughput_msamples_per_s": samples_per_iter / (ms_per_step * 1e-3) * 1e-6,
         "mean_l1_loss_per_iteration": mean_loss, "param_rms_distance_to_target": float(np.sqrt(np.mean((params_end - p_target) ** 2))),
         "param_rms_distance_at_start": float(np.sqrt(np.mean((p_start - p_target) ** 2))),
         "clocks": clocks, "cpu_baseline": cpu, "gpu_launches": None, "roofline": None,
-    }))
+    }
 
 
 def main():
@@ -287,6 +291,8 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override spp (perfect square) for quick runs")
     ap.add_argument("--views", type=int, default=0, help="c4: override the number of target views")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-inverse", action="store_true", help="c2: skip the short C4 (inverse rendering) run reported under 'inverse'")
+    ap.add_argument("--inverse-steps", type=int, default=2, help="timed SFD + Adam iterations of that run (after 1 warm-up iteration)")
     ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
     ap.add_argument("--wave-slots", type=int, default=0)
     ap.add_argument("--wave-parts", type=int, default=0)
@@ -329,7 +335,12 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     if a.config == "c4":
-        return run_inverse(a, cfg, scene, workload, rank, world, local_rank)
+        res = run_inverse(a, cfg, scene, workload, rank, world, local_rank)
+        if world > 1:
+            dist.barrier(); dist.destroy_process_group()
+        if rank == 0:
+            print(json.dumps(res))
+        return
     ctx = vr.Context(local_rank)
     ctx.set_option("engine", a.engine)
     if a.wave_slots:
@@ -399,6 +410,16 @@ def main():
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / a.steps
     e2e_value = total_samples / (e2e_ms * 1e-3) * 1e-6
     ctx.close()
+    # ---- the metric's second half, "inverse-render iters/sec": a short run of config C4 (16 views, 512^2, 256 spp, S = 4) on
+    #      the same N ranks, reported under "inverse" in the same JSON line (python bench.py --config c4 gives the full line)
+    inverse = None
+    if a.config == "c2" and not a.no_inverse:
+        c4 = dict(CONFIGS["c4"])
+        try:
+            inverse = run_inverse(a, c4, scene, f"{c4['label']}; seed {c4['seed']}; orbit cameras radius 6", rank, world, local_rank,
+                                  steps=a.inverse_steps, warmup=1, cpu_baseline=False)
+        except Exception as e:   # the forward line must survive a failure here
+            inverse = {"error": f"{type(e).__name__}: {e}"}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -451,6 +472,7 @@ def main():
         "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
         "rays": {k: stats[k] for k in ("samples", "scatter_rays", "shadow_rays", "hits", "overflow_samples")},
         "engine": "wavefront" if a.engine == 0 else "warp-scheduled single kernel",
+        "inverse": inverse,
     }))
 
 

@@ -142,6 +142,9 @@ int vr_transmittance(vr_context* ctx, int nrays, const float* o3, const float* d
 int vr_sfd_begin(vr_context* ctx, int n, const float* params11, const float* eps11, float lr, float beta1,
                  float beta2, float adam_eps);
 int vr_sfd_set_target(vr_context* ctx, int width, int height, const float* target_rgb);
+/* multi-view fits: upload each view's target once, select the one the next vr_sfd_accumulate compares against */
+int vr_sfd_set_target_view(vr_context* ctx, int view, int width, int height, const float* target_rgb);
+int vr_sfd_select_view(vr_context* ctx, int view);
 int vr_sfd_fdiff(vr_context* ctx, const vr_render_params* rp, int S, const int8_t* signs /* S*11n */,
                  double* F_diff /* S*n */, double* loss_sum, int64_t* loss_pixels);
 int vr_sfd_apply(vr_context* ctx, int S, const int8_t* signs, const double* F_diff /* NULL: device buffer */,
@@ -154,6 +157,22 @@ int vr_sfd_reset_fdiff(vr_context* ctx, int S);
 int vr_sfd_accumulate(vr_context* ctx, const vr_render_params* rp, int S, const int8_t* signs);
 int vr_sfd_read(vr_context* ctx, double* F_diff /* S*n or NULL */, double* loss_sum /* or NULL */);
 int64_t* vr_sfd_fdiff_dev(vr_context* ctx);
+/* ---- the one collective of the path: SUM all-reduce of the S*n int64 partial sums (+ the loss accumulators)
+ * over NCCL, enqueued on the context's stream behind the last reduction kernel; exact and order independent (integers).
+ * One process per device: rank 0 calls vr_comm_unique_id, the 128 bytes travel to every rank by the launcher's means, every
+ * rank calls vr_comm_init_rank; then per iteration vr_sfd_reset_fdiff, vr_sfd_accumulate (per view), vr_sfd_allreduce,
+ * vr_sfd_apply(F_diff = NULL).  One process driving several devices: vr_comm_init_all over its contexts, then
+ * vr_sfd_allreduce_all (one NCCL group).  Contexts that share a device, or a machine without NCCL, get the same exact sum
+ * through peer copies.  NCCL is bound at run time (libnccl.so.2); vr_comm_available() tells whether it was found. */
+int vr_comm_available(void);
+int vr_comm_version(void);                       /* ncclGetVersion, 0 when unavailable */
+int vr_comm_unique_id(void* id128);              /* 128 bytes out */
+int vr_comm_init_rank(vr_context* ctx, const void* id128, int nranks, int rank);
+int vr_comm_init_all(vr_context** ctxs, int n);
+int vr_comm_destroy(vr_context* ctx);
+int vr_comm_size(const vr_context* ctx);         /* ranks of the context's communicator (1: none) */
+int vr_sfd_allreduce(vr_context* ctx);
+int vr_sfd_allreduce_all(vr_context** ctxs, int n);
 int vr_sfd_get_params(vr_context* ctx, float* params11);
 /* optimiser state for checkpoint / resume: current parameters, Adam moments m and v (11n floats each), step count t */
 int vr_sfd_get_state(vr_context* ctx, float* params11, float* m, float* v, int* t);

@@ -193,7 +193,7 @@ def render_samples(gmm: Gmm, lights, env, cam: Camera, integrator: int, W: int, 
                    solver: int = SOLVER_ANALYTIC_NEWTON, window=None, perturb: int = 0, margins: bool = False):
     """Per-sample radiance of a pixel window: array [wh, ww, spp, 4] = (r, g, b, bounce index at the end of the path)
     and, with margins=True, [wh, ww, spp] smallest relative margin of each sample's discrete decisions.
-    perturb 1/2: free-flight distances +/- 1 ulp, 3/4: sampled optical depths * (1 +/- 2^-21)  (volpath_oracle.c)."""
+    perturb 1/2: free-flight distances +/- 1 ulp, 3/4: sampled optical depths * (1 +/- 2^-21), 5/6: distances * (1 +/- 2^-20)."""
     lights = _c(lights).reshape(-1, 6)
     lpos = _c(lights[:, 0:3]); lint = _c(lights[:, 3:6])
     if lpos.size == 0:
@@ -208,13 +208,14 @@ def render_samples(gmm: Gmm, lights, env, cam: Camera, integrator: int, W: int, 
 
 
 def sample_sensitivity(gmm: Gmm, lights, env, cam, integrator, W, H, spp, rtol=2e-5, atol=1e-7, response=False, **kw):
-    """Samples whose value moves by more than rtol under a few-ulp perturbation of a free-flight distance or a sampled
-    optical depth (perturb modes 1..4): returns (samples[..., 4], sensitive[...] bool, margin[...]) and, with
+    """Samples whose value moves by more than rtol under a few-ulp perturbation of a free-flight distance (+/- 1 ulp and
+    +/- 8 ulp: where coordinates are large the scatter POSITION is quantised much coarser than the distance, so a single ulp
+    may not cross a rounding boundary that a few do) or of a sampled optical depth (perturb modes 1..6): returns (samples[..., 4], sensitive[...] bool, margin[...]) and, with
     response=True, also the largest absolute move of any channel under the four perturbations."""
     base, mg = render_samples(gmm, lights, env, cam, integrator, W, H, spp, margins=True, **kw)
     sens = np.zeros(base.shape[:-1], bool)
     resp = np.zeros(base.shape[:-1], np.float32)
-    for mode in (1, 2, 3, 4):
+    for mode in (1, 2, 3, 4, 5, 6):
         alt = render_samples(gmm, lights, env, cam, integrator, W, H, spp, perturb=mode, **kw)
         dev = np.abs(alt[..., :3] - base[..., :3])
         d = dev > atol + rtol * np.abs(base[..., :3])

@@ -58,7 +58,7 @@ static void vo_counters_fold(void) {
  * discrete decisions (vo_min_margin): the comparison acc + seg > target (integrator.h:455), the Russian-roulette test
  * (:693) and the tolerance tests of the iterative solvers (distance_solvers.h:39,84,112).  A sample whose value moves
  * under such a perturbation is one an FP32 implementation with a different libm may legitimately disagree on. */
-static __thread int vo_perturb;       /* 0 none, 1/2: t_scatter +/- 1 ulp, 3/4: target_tau * (1 +/- 2^-21) */
+static __thread int vo_perturb;       /* 0 none, 1/2: t_scatter +/- 1 ulp, 3/4: target_tau * (1 +/- 2^-21), 5/6: t_scatter * (1 +/- 2^-20) */
 static __thread float vo_min_margin;  /* reset per sample */
 static inline void vo_margin(float lhs, float rhs) {
     float den = fabsf(rhs) > 1e-30f ? fabsf(rhs) : 1e-30f;
@@ -798,6 +798,8 @@ static void ms_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
         float t_scatter = ms_free_flight(m, &ray, s, target_tau, solver, rng.state);
         if (t_scatter >= 0.0f && vo_perturb == 1) t_scatter = nextafterf(t_scatter, INFINITY);
         else if (t_scatter > 0.0f && vo_perturb == 2) t_scatter = nextafterf(t_scatter, 0.0f);
+        else if (t_scatter > 0.0f && vo_perturb == 5) t_scatter *= 1.0f + 0x1p-20f;
+        else if (t_scatter > 0.0f && vo_perturb == 6) t_scatter *= 1.0f - 0x1p-20f;
         if (record) {
             const float tol = 1e-6f;
             if (t_scatter >= 0.0f) {
@@ -858,6 +860,8 @@ static void ss_sample(const vo_gmm* m, const vo_lights* L, const vo_camera* cam,
             t_scatter = solve_distance(m, &ray, t_prev, t_evt, s->active, s->na, target_tau - acc_tau, solver, rng.state);
             if (t_scatter >= 0.0f && vo_perturb == 1) t_scatter = nextafterf(t_scatter, INFINITY);
             else if (t_scatter > 0.0f && vo_perturb == 2) t_scatter = nextafterf(t_scatter, 0.0f);
+            else if (t_scatter > 0.0f && vo_perturb == 5) t_scatter *= 1.0f + 0x1p-20f;
+            else if (t_scatter > 0.0f && vo_perturb == 6) t_scatter *= 1.0f - 0x1p-20f;
             break;
         }
         acc_tau += seg_tau;

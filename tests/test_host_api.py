@@ -158,6 +158,48 @@ def test_vol_render_inverse_reduces_loss(host_bins, tmp_path):
     assert sum(1 for l in open(tmp_path / "fit.txt") if l.startswith("g ")) == 50
 
 
+def _inverse_params(exe, tmp_path, tag, extra=(), env=None, iters=5):
+    cam = _cam_args("pin")
+    tgt = tmp_path / "target_common.ppm"
+    scene = os.path.join(SCENES, "rand50.txt")
+    if not tgt.exists():
+        assert run([exe, "--scene", scene, "--spp", "16", "--width", "24", "--height", "24", "--out", str(tgt)] + cam).returncode == 0
+    out = tmp_path / f"{tag}.f32"
+    r = run([exe, "--scene", scene, "--inverse", str(tgt), "--spp", "16", "--save-every", "2", "--final-spp", "16", "--quiet", "--iters", str(iters),
+             "--out-dir", str(tmp_path / tag), "--save-params", str(out)] + cam + list(extra), env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    return np.fromfile(out, np.float32)
+
+
+@pytest.mark.gpu
+def test_inverse_uses_the_forward_integrators_camera(host_bins, tmp_path):
+    """The reference's StochasticFiniteDiffInverseIntegrator renders through forward_integrator->render, i.e. with the FORWARD
+    integrator's camera (inverse_integrator.h:119,153); its own camera member is never read.  An inverse integrator built
+    from a different camera object must give the same parameters, also with save renders (every 2nd iteration here)
+    interleaved with the SFD renders."""
+    exe = os.path.join(host_bins, "vol_render")
+    a = _inverse_params(exe, tmp_path, "same")
+    b = _inverse_params(exe, tmp_path, "other", extra=["--inverse-camera-pos", "3,2,-4"])
+    assert a.size == 550 and np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+def test_inverse_multi_device_allreduce_is_exact(host_bins, tmp_path):
+    """VR_DEVICES with several contexts: rows are split, the int64 partial F_diff sums of all contexts are all-reduced on the
+    devices (Session::allreduce_sfd -> vr_sfd_allreduce_all: one ncclAllReduce on distinct GPUs, peer copies + an integer add
+    when contexts share a GPU) and every context applies the same Adam step: parameters bit-identical to one context."""
+    exe = os.path.join(host_bins, "vol_render")
+    one = _inverse_params(exe, tmp_path, "dev1", env=dict(os.environ, VR_DEVICES="0"))
+    two = _inverse_params(exe, tmp_path, "dev00", env=dict(os.environ, VR_DEVICES="0,0"))
+    assert np.array_equal(one, two)
+    import subprocess
+    ngpu = len(subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True).stdout.strip().splitlines())
+    if ngpu >= 2:   # distinct GPUs: the NCCL path
+        devs = ",".join(str(i) for i in range(min(ngpu, 4)))
+        many = _inverse_params(exe, tmp_path, "devN", env=dict(os.environ, VR_DEVICES=devs))
+        assert np.array_equal(one, many)
+
+
 @pytest.mark.gpu
 def test_inverse_checkpoint_resume_is_bit_exact(host_bins, tmp_path):
     """12 iterations in one go == 6 iterations, checkpoint, resume for 6 more: identical final parameters
