@@ -244,6 +244,7 @@ int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
         fprintf(stderr, "[setup] %-28s %7.3f ms\n", what, t - ts_prev);
         ts_prev = t;
     };
+    NvtxRange range_setup("vr.set_gmm");
     cancel_light_grid_job(ctx);
     ctx->has_gmm = false;
     ctx->rec_valid = false;
@@ -283,7 +284,7 @@ int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
             ctx->lg_job = job;
         }
         BvhBuildResult bvh;
-        build_bvh(n, lo.data(), hi.data(), &bvh);
+        { NvtxRange r("vr.set_gmm.hierarchy_build"); build_bvh(n, lo.data(), hi.data(), &bvh); }
         lap("hierarchy build");
         if (bvh.max_depth > kStackDepth - 2)
             return fail(ctx, VR_ERR_UNSUPPORTED, "hierarchy deeper than the traversal stack");
@@ -330,6 +331,7 @@ int ensure_camera_reach(vr_context* ctx) {
 // mixture or the lights changed since the last render
 int ensure_light_grids(vr_context* ctx) {
     if (ctx->lg_valid) return VR_OK;
+    NvtxRange range_grids("vr.light_grids");
     ctx->lg_mask = 0;
     VR_CUDA(ctx->lg_start.ensure(16)); VR_CUDA(ctx->lg_gi.ensure(16)); VR_CUDA(ctx->lg_dmin.ensure(16));
     if (ctx->use_light_grid && ctx->n > 0 && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl &&

@@ -163,7 +163,8 @@ int vr_sfd_allreduce(vr_context* ctx) {
     long long* buf = nullptr; size_t count = 0;
     int rc = sfd_reduce_buffer(ctx, &buf, &count);
     if (rc) return rc;
-    if (!ctx->comm || ctx->comm_size <= 1) return VR_OK;
+    if (!ctx->comm) return VR_OK;                      // no communicator: a single context, nothing to sum
+    NvtxRange range("vr.sfd.allreduce");
     NcclApi& N = nccl();
     VR_CUDA(cudaSetDevice(ctx->device));
     VR_NCCL(ctx, N.AllReduce(buf, buf, count, ncclInt64, ncclSum, (ncclComm_t)ctx->comm, ctx->stream));
@@ -184,6 +185,7 @@ int vr_sfd_allreduce_all(vr_context** ctxs, int n) {
         count = c;
     }
     if (n == 1) return VR_OK;
+    NvtxRange range("vr.sfd.allreduce_all");
     bool have_comm = true;
     for (int i = 0; i < n; ++i) have_comm = have_comm && ctxs[i]->comm && ctxs[i]->comm_size == n;
     if (have_comm) {

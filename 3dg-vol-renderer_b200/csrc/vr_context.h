@@ -1,6 +1,7 @@
 // vr_context.h -- the opaque context behind the C-ABI (include/volrender.h).
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <string>
 #include <vector>
@@ -10,6 +11,15 @@
 #include "vr_bvh.h"
 
 namespace vr {
+
+// NVTX range of a host-side phase (set-up / pass / drain / reduce / collective), visible in Nsight Systems / Compute timelines;
+// header-only NVTX 3: costs a predictable branch when no tool is attached
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // grow-only device buffer
 struct DevBuf {

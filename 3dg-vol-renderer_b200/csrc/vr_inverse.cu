@@ -233,6 +233,7 @@ int vr_sfd_accumulate(vr_context* ctx, const vr_render_params* rp, int S, const 
     SfdState* s = ctx->sfd;
     if (s->fdiff_S != S) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_accumulate: call vr_sfd_reset_fdiff(S) first");
     if (s->tw != rp->width || s->th != rp->height) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_accumulate: target image size differs from the render size");
+    NvtxRange range_acc("vr.sfd.accumulate");
     VR_CUDA(cudaSetDevice(ctx->device));
     const int n = s->n, D = 11 * n;
     cudaStream_t st = ctx->stream;
@@ -308,6 +309,7 @@ int vr_sfd_fdiff(vr_context* ctx, const vr_render_params* rp, int S, const int8_
 
 int vr_sfd_apply(vr_context* ctx, int S, const int8_t* signs, const double* F_diff, float* grad_out) {
     if (!ctx || !ctx->sfd || S <= 0 || !signs) return fail(ctx, VR_ERR_INVALID_ARGUMENT, "vr_sfd_apply: bad arguments");
+    NvtxRange range_apply("vr.sfd.apply");
     VR_CUDA(cudaSetDevice(ctx->device));
     SfdState* s = ctx->sfd;
     const int n = s->n, D = 11 * n;

@@ -61,6 +61,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     if (!ctx->has_gmm) return fail(ctx, VR_ERR_NO_SCENE, "render: no Gaussian mixture set (vr_set_gmm)");
     rc = ensure_camera_reach(ctx);   // a camera farther out than the culling boxes were inflated for: rebuild (vr_bvh.h BoxReach)
     if (rc) return rc;
+    NvtxRange range_render("vr.render");
     const int W = p->width, H = p->height;
     cudaStream_t s = ctx->stream;
     VR_CUDA(ctx->image.ensure((size_t)3 * W * H * sizeof(float)));
@@ -124,6 +125,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             VR_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(unsigned int) * 4, s));
             VR_CUDA(cudaEventRecord(ctx->ev[2], s));
             if (ctx->engine == 0) {
+                NvtxRange range_pass("vr.render.wavefront_pass");
                 const int P = ctx->wave_slots > 0 ? ctx->wave_slots : ctx->num_sms * 32768;
                 // big passes are cut into independent parts on their own streams so that kernel tails overlap
                 int parts = (unsigned long long)A.work_count >= 4ULL * (unsigned long long)std::min(P, ctx->num_sms * 24576) ? ctx->wave_parts : 1;
@@ -143,6 +145,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             VR_CUDA(cudaStreamSynchronize(s));
             const unsigned int n_over = ctx->h_counters[1];
             if (n_over > 0) {  // samples whose rays overlapped more than kLocalCap components: re-trace with the arena store
+                NvtxRange range_over("vr.render.overflow_retrace");
                 overflow_total += n_over;
                 const int cap_hits = ctx->hit_capacity > 0 ? ctx->hit_capacity : std::max(kLocalCap * 2, std::min(ctx->n, 4096));
                 int grid_arena = ctx->num_sms * ctx->blocks_per_sm_arena;
@@ -158,7 +161,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
                 VR_CUDA(cudaGetLastError());
             }
             VR_CUDA(cudaEventRecord(ctx->ev[3], s));
-            launch_pixel_reduce(A, pass_pixels, ctx->image.as<float>(), s); ++launches;
+            { NvtxRange r("vr.render.pixel_reduce"); launch_pixel_reduce(A, pass_pixels, ctx->image.as<float>(), s); ++launches; }
             VR_CUDA(cudaGetLastError());
             VR_CUDA(cudaEventSynchronize(ctx->ev[3]));
             float ms = 0.f;

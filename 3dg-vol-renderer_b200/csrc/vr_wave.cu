@@ -23,6 +23,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "vr_context.h"
 #include "vr_internal.h"
 #include "vr_pathcommon.cuh"
 
@@ -954,6 +955,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     // the kernels of short waves (small renders, the drain of a pass) follow each other without launch gaps.
     while (!failed) {
         bool any = false;
+        NvtxRange range_batch("vr.wave.batch");
         for (int i = 0; i < parts; ++i) {
             Part& pt = part[i];
             if (pt.done) continue;
@@ -1009,7 +1011,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             // every sample is out and few paths are left: finish them in one kernel instead of ~100 more iterations
             // that are bounded by their own latency (see wave_drain_kernel)
             else if (drain_on && !more_samples && pt.h[WC_NTS] <= (unsigned int)pt.q.P / drain_div) {
-                launch_wave_drain(pt.a, pt.q, pt.h[WC_NTS], pt.st);
+                { NvtxRange r("vr.wave.drain"); launch_wave_drain(pt.a, pt.q, pt.h[WC_NTS], pt.st); }
                 ++*launches;
                 pt.done = true;
                 if (timeline) {

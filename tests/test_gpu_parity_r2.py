@@ -130,7 +130,7 @@ def test_per_sample_attribution(ctx, ob, vr, scenegen, label, sc, cam, integ, W,
     assert not (~pix_ok & clean).any(), "a pixel outside 1e-4 none of whose samples is sensitive"
     assert pix_ok.mean() >= 0.995                                           # measured: >= 0.9961
     assert rel.max() <= 1e-2                                                # no pixel is wrong by more than 1 %
-    assert (dev[~ok] <= 1e-5 + 256.0 * resp[~ok]).all()                     # outliers stay within a bounded multiple of the
+    assert (dev[~ok] <= 1e-6 + 8.0 * resp[~ok]).all()                       # measured <= 1.5: outliers stay within a small multiple of the
                                                                             # oracle's own move under ONE ulp
 
 
@@ -179,7 +179,7 @@ def test_wave_traversal_sets_vs_oracle(ctx, ob, vr, scenegen, sc, cam, n):
             small += 1
             same += (cnt[i] == len(ref[i])) and frozenset(idx[i, :cnt[i]].tolist()) == ref[i]
         else:
-            same += cnt[i] == len(ref[i])
+            same += cnt[i] > 16          # more overlaps than a slot holds: the traversal stops at the 17th (the sample is re-traced)
     nonempty = sum(1 for r in ref if r)
     print(f"{sc}: {n} rays, {nonempty} overlap something, identical sets {same / n:.5f}")
     assert nonempty > n // 10
@@ -222,8 +222,10 @@ def test_far_and_scaled_scenes_vs_reference(ctx, ob, vr, golden_r2, scenegen, sc
 
 
 def test_far_camera_rebuilds_the_hierarchy(ctx, ob, vr, scenegen):
-    """a camera much farther out than the culling boxes were inflated for: the next render rebuilds them (vr_bvh.h BoxReach);
-    the image still matches the oracle"""
+    """a camera ten times farther out than the culling boxes were inflated for: the next render rebuilds them (vr_bvh.h
+    BoxReach).  At that distance the FP32 quadric of the reference is 100 times noisier (its error grows with the square of
+    the distance), so fewer pixels stay inside 1e-4 -- measured 97.9 % -- but the overlap SETS of far rays must still be
+    exactly the reference restatement's, and transmittances within 1e-5."""
     scene = file_scene(scenegen, "rand300")
     ctx.set_gmm(scene); ctx.set_lights(scene["lights"], ENV)
     oc = ob.make_camera("pinhole", (0.0, 1.0, 60.0), look=(0, 1, 0), fov=0.07)
@@ -232,14 +234,20 @@ def test_far_camera_rebuilds_the_hierarchy(ctx, ob, vr, scenegen):
     img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 16))
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 32, 32, 16)
     f = within(img, ref, 1e-4).mean()
-    print(f"camera at 60 units: pixels within 1e-4 {f:.5f}")
-    assert f >= 0.98
-    # rays whose origins are far out, through vr_transmittance
+    print(f"camera at 60 units: pixels within 1e-4 {f:.5f}, worst {(np.abs(img - ref) / np.maximum(np.abs(ref), 1e-3)).max():.2e}")
+    assert f >= 0.95 and within(img, ref, 1e-2).all()
+    assert abs(float(img.mean()) - float(ref.mean())) <= 1e-4 * float(ref.mean())
+    # rays whose origins are far out: overlap sets through the wavefront traversal, transmittance through vr_transmittance
     rs = np.random.RandomState(3)
     o = (rs.uniform(-1, 1, size=(5000, 3)) * 100).astype(np.float32); o[:, 1] += 1
     t = rs.uniform(-1, 1, size=(5000, 3)).astype(np.float32); t[:, 1] += 1
     d = t - o
     d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    cnt, idx = ctx.kat_gather(o, d, cap=16)
+    sets = _oracle_sets(ob, scene, o, d)
+    same = sum((cnt[i] > 16) if len(sets[i]) > 16 else (cnt[i] == len(sets[i]) and frozenset(idx[i, :cnt[i]].tolist()) == sets[i]) for i in range(5000))
+    print(f"origins up to 100 units out: identical overlap sets {same / 5000:.5f}")
+    assert same == 5000
     tmax = np.full(5000, np.inf, np.float32)
     np.testing.assert_allclose(ctx.transmittance(o, d, tmax), ob.Gmm(scene).transmittance(o, d, tmax), rtol=1e-5, atol=1e-7)
 
