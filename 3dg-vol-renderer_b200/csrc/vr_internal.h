@@ -8,7 +8,10 @@
 namespace vr {
 
 // statistics counters accumulated by the path kernels (device array of kNumStats u64)
-enum { ST_SCATTER_RAYS = 0, ST_SHADOW_RAYS, ST_HITS, ST_OVERFLOW, ST_ERRORS, kNumStats };
+// ST_NODES .. ST_ITER: EXECUTED work of the wavefront engine (the overflow re-trace and drain kernels, < 2 % of the samples, are
+// not counted): hierarchy slab steps + light-grid entries examined, quadric tests, erf evaluations, mu_t evaluations,
+// analytic solves attempted, iterative (Newton / bisection) solves
+enum { ST_SCATTER_RAYS = 0, ST_SHADOW_RAYS, ST_HITS, ST_OVERFLOW, ST_ERRORS, ST_NODES, ST_QUADRICS, ST_ERF, ST_MU, ST_SA, ST_ITER, kNumStats };
 
 struct RenderArgs {
     SceneDev scene;

@@ -184,6 +184,8 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
         st->scatter_rays = ctx->h_stats[ST_SCATTER_RAYS]; st->shadow_rays = ctx->h_stats[ST_SHADOW_RAYS];
         st->hits = ctx->h_stats[ST_HITS]; st->overflow_samples = overflow_total;
         st->kernel_launches = launches;
+        st->node_visits = ctx->h_stats[ST_NODES]; st->quadric_tests = ctx->h_stats[ST_QUADRICS]; st->erf_evals = ctx->h_stats[ST_ERF];
+        st->mu_evals = ctx->h_stats[ST_MU]; st->analytic_solves = ctx->h_stats[ST_SA]; st->iterative_solves = ctx->h_stats[ST_ITER];
     }
     if (ctx->h_stats[ST_ERRORS])
         return fail(ctx, VR_ERR_HIT_OVERFLOW, "a ray overlapped more components than hit_capacity; raise it with vr_set_option(\"hit_capacity\")");

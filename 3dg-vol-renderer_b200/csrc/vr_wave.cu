@@ -55,7 +55,7 @@ void wave_pool_carve(WavePool* q, int P, void* base) {
 // ------------------------------------------------------------------------------------------
 // list / counter helpers
 // ------------------------------------------------------------------------------------------
-struct WaveCounters { unsigned int scatter, shadow, hits, over; };
+struct WaveCounters { unsigned int scatter, shadow, hits, over, nodes, quads, erf, mu, sa, it; };
 
 __device__ __forceinline__ void wave_append(unsigned int* list, unsigned int* counter, bool pred, unsigned int value) {
     const unsigned m = __ballot_sync(0xffffffffu, pred);
@@ -72,8 +72,20 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
         cn.shadow += __shfl_down_sync(0xffffffffu, cn.shadow, o);
         cn.hits += __shfl_down_sync(0xffffffffu, cn.hits, o);
         cn.over += __shfl_down_sync(0xffffffffu, cn.over, o);
+        cn.nodes += __shfl_down_sync(0xffffffffu, cn.nodes, o);
+        cn.quads += __shfl_down_sync(0xffffffffu, cn.quads, o);
+        cn.erf += __shfl_down_sync(0xffffffffu, cn.erf, o);
+        cn.mu += __shfl_down_sync(0xffffffffu, cn.mu, o);
+        cn.sa += __shfl_down_sync(0xffffffffu, cn.sa, o);
+        cn.it += __shfl_down_sync(0xffffffffu, cn.it, o);
     }
     if ((threadIdx.x & 31) == 0) {
+        if (cn.nodes) atomicAdd(A.stats + ST_NODES, (unsigned long long)cn.nodes);
+        if (cn.quads) atomicAdd(A.stats + ST_QUADRICS, (unsigned long long)cn.quads);
+        if (cn.erf) atomicAdd(A.stats + ST_ERF, (unsigned long long)cn.erf);
+        if (cn.mu) atomicAdd(A.stats + ST_MU, (unsigned long long)cn.mu);
+        if (cn.sa) atomicAdd(A.stats + ST_SA, (unsigned long long)cn.sa);
+        if (cn.it) atomicAdd(A.stats + ST_ITER, (unsigned long long)cn.it);
         if (cn.scatter) atomicAdd(A.stats + ST_SCATTER_RAYS, (unsigned long long)cn.scatter);
         if (cn.shadow) atomicAdd(A.stats + ST_SHADOW_RAYS, (unsigned long long)cn.shadow);
         if (cn.hits) atomicAdd(A.stats + ST_HITS, (unsigned long long)cn.hits);
@@ -170,6 +182,7 @@ template <> struct TravShared<RAY_LIGHT> : TravShared<RAY_SHADOW> {};   // same 
 enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
 
 struct TravLane {
+    unsigned int n_nodes, n_quads, n_erf;   // executed work of this lane
     int mode, cur, sp;
     int pushed;   // candidates this lane queued for its current ray; w.pending[lane] counts the ones already tested
     bool has_result;
@@ -179,8 +192,9 @@ struct TravLane {
 
 // free-flight rays: quadric test of up to 32 candidates; overlaps go to the owner's slot as (t0, t1, index)
 __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const WavePool& Q, TravShared<RAY_SCATTER>& w, int lane,
-                                                      int q_begin, int nb) {
+                                                      int q_begin, int nb, TravLane& tl) {
     if (lane < nb) {
+        ++tl.n_quads;
         const uint32_t e = w.queue[q_begin + lane];
         const int owner = (int)(e >> 27);
         const uint32_t gi = e & 0x07ffffffu;
@@ -196,6 +210,7 @@ __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const W
                 if (slot < kWaveCap) {
                     pool_store_hit(Q, w.pid[owner], slot, t0, t1, gi);
                     if (t1 < tb) {
+                        tl.n_erf += 2u;
                         // pruning only: CONSERVATIVE estimate of this component's full optical depth
                         // (fast intrinsics; 1.5x margin covers the FP32 slack of the exact expression)
                         const float dn = g.density * g.norm;
@@ -214,10 +229,11 @@ __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const W
 
 // shadow rays: quadric test; overlaps with a non-empty clipped interval go to the depth queue
 __device__ __forceinline__ void shadow_quadric_batch(const SceneDev& S, TravShared<RAY_SHADOW>& w, int lane, int q_begin, int nb,
-                                                     int& nH) {
+                                                     int& nH, TravLane& tl) {
     bool to_hq = false;
     uint32_t e = 0; float ha = 0.f, hb = 0.f;
     if (lane < nb) {
+        ++tl.n_quads;
         e = w.queue[q_begin + lane];
         const int owner = (int)(e >> 27);
         const uint32_t gi = e & 0x07ffffffu;
@@ -241,8 +257,9 @@ __device__ __forceinline__ void shadow_quadric_batch(const SceneDev& S, TravShar
 }
 
 // exact clipped optical depth of up to 32 shadow overlaps (gmm.h:563-571, gaussian.h:208-231)
-__device__ __forceinline__ void shadow_depth_batch(const SceneDev& S, TravShared<RAY_SHADOW>& w, int lane, int h_begin, int nb) {
+__device__ __forceinline__ void shadow_depth_batch(const SceneDev& S, TravShared<RAY_SHADOW>& w, int lane, int h_begin, int nb, TravLane& tl) {
     if (lane < nb) {
+        tl.n_erf += 2u;
         const uint32_t e = w.hq_id[h_begin + lane];
         const int owner = (int)(e >> 27);
         const uint32_t gi = e & 0x07ffffffu;
@@ -268,6 +285,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
         bool l0 = false, l1 = false, fin = false;
         uint32_t g0 = 0, g1 = 0;   // leaf-order indices of the candidates this lane queues in this round
         if (tl.mode == T_TRAV) {
+            ++tl.n_nodes;
             if constexpr (KIND == RAY_LIGHT) {
                 // candidates come from the cell list of the light's direction grid, nearest to the light first; the
                 // list ends for this ray at the first component that lies beyond the ray's origin (vr_lightgrid.h)
@@ -343,6 +361,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
     int stack[kStackDepth];
     TravLane tl;
     tl.mode = T_FETCH; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f; tl.pushed = 0;
+    tl.n_nodes = tl.n_quads = tl.n_erf = 0u;
     int nQ = 0, nH = 0;
     unsigned int n_escaped = 0;
     bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
@@ -354,7 +373,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
                 TravShared<RAY_SHADOW>& wh = reinterpret_cast<TravShared<RAY_SHADOW>&>(w);
                 const int nb = min(nH, 32);
                 nH -= nb;
-                shadow_depth_batch(S, wh, lane, nH, nb);
+                shadow_depth_batch(S, wh, lane, nH, nb, tl);
                 __syncwarp();
                 if (tl.mode == T_WAIT && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
                 continue;
@@ -363,8 +382,8 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
         if (nQ >= 32 || (nQ > 0 && drain)) {
             const int nb = min(nQ, 32);
             nQ -= nb;
-            if (KIND == RAY_SCATTER) scatter_quadric_batch(S, Q, reinterpret_cast<TravShared<RAY_SCATTER>&>(w), lane, nQ, nb);
-            else shadow_quadric_batch(S, reinterpret_cast<TravShared<RAY_SHADOW>&>(w), lane, nQ, nb, nH);
+            if (KIND == RAY_SCATTER) scatter_quadric_batch(S, Q, reinterpret_cast<TravShared<RAY_SCATTER>&>(w), lane, nQ, nb, tl);
+            else shadow_quadric_batch(S, reinterpret_cast<TravShared<RAY_SHADOW>&>(w), lane, nQ, nb, nH, tl);
             __syncwarp();
             if (tl.mode == T_WAIT && w.pending[lane] == tl.pushed) { tl.mode = T_FETCH; tl.has_result = true; }
             continue;
@@ -447,6 +466,8 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
         trav_rounds<KIND>(S, w, lane, tl, stack, nQ, !exhausted);
     }
     (void)n_escaped;
+    WaveCounters cn = {0u, 0u, 0u, 0u, tl.n_nodes, tl.n_quads, tl.n_erf, 0u, 0u, 0u};
+    wave_flush_counters(A, cn);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -467,7 +488,7 @@ __device__ __forceinline__ void publish_scatter_ray(const WavePool& Q, unsigned 
 __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const unsigned int nC = Q.cnt[WC_NC];
     if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NB] = 0;  // consumed by wave_post_b, the previous kernel of the chain
-    WaveCounters cn = {0u, 0u, 0u, 0u};
+    WaveCounters cn = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (nC + stride - 1) / stride;
     for (unsigned int r = 0; r < rounds; ++r) {
@@ -581,7 +602,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
         for (int c = kFirst; c < kLast; ++c) sum += nA[c];
         Q.cnt[MODE == 2 ? WC_SUM_DEFERRED : WC_SUM_GENERAL] += sum;
     }  // consumed by wave_trav<scatter>
-    WaveCounters cn = {0u, 0u, 0u, 0u};
+    WaveCounters cn = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (total + stride - 1) / stride;
     for (unsigned int r = 0; r < rounds; ++r) {
@@ -620,8 +641,10 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     const float F0 = erff_ni(erf_arg(c, t0));
                     const float F1 = erff_ni(erf_arg(c, t1));
                     const float seg = __fmul_rn(c.K, __fsub_rn(F1, F0));
+                    cn.erf += 2u;
                     if (seg > target_tau) {   // float and double comparisons agree: the conversion is exact
                         float t_an;
+                        ++cn.sa;
                         if (solve_t_given_tau(g, q, t0, t1, target_tau, &t_an)) { t = clampf(t_an, t0, t1); solved = true; }
                     } else {
                         solved = true;        // the ray leaves the component: t stays -1
@@ -629,6 +652,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     if (solved) {
                         if (t >= 0.0f) {       // evaluate_albedo over the one active component (gmm.h:128-143)
                             const float mu = gauss_mu_t(g, add3(o, scale3(t, d)));
+                            ++cn.mu;
                             const float a = __fdiv_rn(__fadd_rn(0.0f, __fmul_rn(mu, g.albedo)), __fadd_rn(0.0f, mu));
                             albedo = a < 0.0f ? 0.0f : (1.0f < a ? 1.0f : a);
                         }
@@ -685,6 +709,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 const float albedo = t >= 0.0f ? evaluate_albedo(S, st, na, add3(o, scale3(t, d))) : 0.0f;
                 dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
                 }
+                cn.erf += st.n_erf; cn.mu += st.n_mu; cn.sa += st.n_sa; cn.it += st.n_it;
             }
         }
         if (FAST) wave_append(Q.listA + (size_t)1 * Q.P, &Q.cnt[WC_NA + 1], hand_over, p);
@@ -703,7 +728,7 @@ __global__ void __launch_bounds__(256) wave_post_b_kernel(const __grid_constant_
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // both traversal kernels of this iteration are over
         Q.cnt[WC_NTH] = 0; Q.cnt[WC_NTL] = 0; Q.cnt[WC_CURSOR_S] = 0; Q.cnt[WC_CURSOR_H] = 0; Q.cnt[WC_CURSOR_L] = 0;
     }
-    WaveCounters cn = {0u, 0u, 0u, 0u};
+    WaveCounters cn = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int rounds = (nB + stride - 1) / stride;
     for (unsigned int r = 0; r < rounds; ++r) {

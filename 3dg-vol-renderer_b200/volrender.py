@@ -46,7 +46,9 @@ class RenderParams(C.Structure):
 class RenderStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("total_ms", C.c_double), ("samples", C.c_uint64),
                 ("scatter_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("hits", C.c_uint64),
-                ("overflow_samples", C.c_uint64), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("overflow_samples", C.c_uint64), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32),
+                ("node_visits", C.c_uint64), ("quadric_tests", C.c_uint64), ("erf_evals", C.c_uint64), ("mu_evals", C.c_uint64),
+                ("analytic_solves", C.c_uint64), ("iterative_solves", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

@@ -462,6 +462,22 @@ def main():
                      f"; FP32 peak = {n_sms} SMs x 128 x 2 x {sm_clock:.0f} MHz, MUFU peak = {n_sms} x 16 x clock (clock sampled under load); "
                      "time = device time of the step's wave kernels (CUDA events on the context's stream); hierarchy / grid "
                      "traversal is implementation overhead and is NOT counted as achieved work (see profiles/ for raw pipe utilisation)")
+    # EXECUTED work from the device's own counters (vr_render_stats): what the culling, the walk and the solvers really ran,
+    # in the same cost model (quadric 62 + constants 12 FLOP, erf 22, mu_t 28, analytic solve 40, vertex 40)
+    # plus 44 FLOP per hierarchy step (two child boxes: 12 FMA + 8 three-input min/max)
+    ns = float(stats["samples"]) if stats["samples"] else 1.0
+    ex = {k: stats[k] / ns for k in ("node_visits", "quadric_tests", "hits", "erf_evals", "mu_evals", "analytic_solves", "iterative_solves", "scatter_rays", "shadow_rays")}
+    ex_flop = (44 * ex["node_visits"] + 62 * ex["quadric_tests"] + 12 * ex["hits"] + 22 * ex["erf_evals"] + 28 * ex["mu_evals"] +
+               40 * ex["analytic_solves"] + 40 * ex["scatter_rays"])
+    ex_mufu = 3 * ex["quadric_tests"] + 2 * ex["hits"] + ex["erf_evals"] + ex["mu_evals"] + 4 * ex["analytic_solves"] + 5 * ex["scatter_rays"]
+    ex_f = ex_flop * samples_per_launch / (launch_ms * 1e-3) * 1e-12
+    ex_m = ex_mufu * samples_per_launch / (launch_ms * 1e-3) * 1e-12
+    roof["executed"] = dict(per_sample=ex, flop_per_sample=ex_flop, mufu_per_sample=ex_mufu,
+                            fp32=dict(achieved=ex_f, peak=peak_tflops, unit="TFLOP/s", frac=ex_f / peak_tflops),
+                            mufu=dict(achieved=ex_m, peak=peak_mufu, unit="Tops/s", frac=ex_m / peak_mufu),
+                            note="device counters of the wavefront kernels of the last timed step (overflow re-trace and drain, < 2 % of the samples, "
+                                 "not counted); the gap to the algorithmic figure above is culling (hierarchy steps, rejected quadric tests), "
+                                 "the gap to the raw pipe utilisation in profiles/ is control flow and divergence")
     cpu = None
     if not a.no_cpu_baseline:
         cpu = cpu_render_sample(cfg, scene)

@@ -85,6 +85,14 @@ typedef struct vr_render_stats {
     uint64_t overflow_samples; /* samples re-traced by the large-capacity kernel */
     uint32_t kernel_launches;  /* kernels launched by this call */
     uint32_t reserved;
+    /* EXECUTED work of the wavefront engine (what the device really did, next to the algorithmic counts of SURVEY.md 8d;
+     * the overflow re-trace and the drain of a pass, < 2 % of the samples, are not counted) */
+    uint64_t node_visits;      /* hierarchy slab steps (two child boxes each) + light-grid entries examined */
+    uint64_t quadric_tests;    /* gaussian.h:126-164 evaluations (hits + rejected candidates) */
+    uint64_t erf_evals;        /* erff evaluations (an optical_depth call of the reference = 2) */
+    uint64_t mu_evals;         /* Gaussian::mu_t evaluations */
+    uint64_t analytic_solves;  /* solve_for_t_given_tau calls */
+    uint64_t iterative_solves; /* Newton / bisection solves */
 } vr_render_stats;
 
 /* ---- lifetime ------------------------------------------------------------------------- */

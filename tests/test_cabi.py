@@ -36,9 +36,17 @@ def test_header_symbols_are_exported(vr):
 
 
 def test_struct_layouts_match_header(vr):
-    # vr_render_params: 15 int32/float fields + 4 reserved; vr_render_stats: 2 doubles + 5 u64 + 2 u32
+    # vr_render_params: 15 int32/float fields + 4 reserved; vr_render_stats: 2 doubles + 5 u64 + 2 u32 + 6 u64 (executed work)
     assert C.sizeof(vr.RenderParams) == 19 * 4
-    assert C.sizeof(vr.RenderStats) == 2 * 8 + 5 * 8 + 2 * 4
+    assert C.sizeof(vr.RenderStats) == 2 * 8 + 5 * 8 + 2 * 4 + 6 * 8
+    # the C compiler's view of the same structs
+    import subprocess, tempfile
+    src = '#include "volrender.h"\n#include <stdio.h>\nint main(void){printf("%zu %zu\\n", sizeof(vr_render_params), sizeof(vr_render_stats));return 0;}\n'
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "s.c"), "w").write(src)
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), os.path.join(d, "s.c"), "-o", os.path.join(d, "s")])
+        a, b = subprocess.check_output([os.path.join(d, "s")], text=True).split()
+    assert int(a) == C.sizeof(vr.RenderParams) and int(b) == C.sizeof(vr.RenderStats)
 
 
 def test_no_cpu_fallback(vr):
