@@ -90,6 +90,7 @@ int vr_create(vr_context** out, int device_id) {
     VR_CUDA(cudaMallocHost((void**)&ctx->h_stats, sizeof(unsigned long long) * kNumStats));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_counters, sizeof(unsigned int) * 32));
     VR_CUDA(cudaMallocHost((void**)&ctx->h_wave_counters, sizeof(unsigned int) * kMaxWaveParts * kWaveCounters));
+    VR_CUDA(cudaMallocHost((void**)&ctx->h_build_meta, sizeof(unsigned int) * 32));
     ctx->wave_graphs = wave_graph_cache_create();
     VR_CUDA(ctx->stats.ensure(sizeof(unsigned long long) * kNumStats));
     VR_CUDA(ctx->counters.ensure(sizeof(unsigned int) * 4));
@@ -108,13 +109,15 @@ void vr_destroy(vr_context* ctx) {
     ctx->comm_scratch.release();
     for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
                       &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->lam, &ctx->qnodes, &ctx->lg_start, &ctx->lg_gi,
-                      &ctx->lg_dmin, &ctx->spheres, &ctx->lpos, &ctx->lint,
+                      &ctx->lg_dmin, &ctx->lg_scratch, &ctx->spheres, &ctx->lpos, &ctx->lint,
                       &ctx->image, &ctx->sampleL, &ctx->counters, &ctx->stats, &ctx->overflow_list, &ctx->arena,
                       &ctx->record_bits, &ctx->scratch, &ctx->wavepool})
         b->release();
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     if (ctx->h_wave_counters) cudaFreeHost(ctx->h_wave_counters);
+    if (ctx->h_build_meta) cudaFreeHost(ctx->h_build_meta);
+    for (DevBuf* b : {&ctx->lbvh_keys, &ctx->lbvh_tree, &ctx->lbvh_tmp}) b->release();
     vr::wave_graph_cache_destroy(ctx->wave_graphs);
     for (cudaStream_t ws : ctx->wave_streams) if (ws) cudaStreamDestroy(ws);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
@@ -131,6 +134,8 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
+    if (!strcmp(name, "trav")) { ctx->trav_version = (int)value == 1 ? 1 : 2; return VR_OK; }
+    if (!strcmp(name, "hierarchy")) { ctx->hierarchy_builder = (int)value != 0; return VR_OK; }   // 0 device LBVH, 1 host binned SAH; next vr_set_gmm*
     if (!strcmp(name, "box_kappa")) { ctx->box_kappa = std::max(0.0, value); return VR_OK; }   // takes effect at the next vr_set_gmm*
     if (!strcmp(name, "light_grid")) { vr::cancel_light_grid_job(ctx); ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "light_grid_min_samples")) { ctx->light_grid_min_samples = value; return VR_OK; }
@@ -261,6 +266,18 @@ int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
         launch_prepare_gaussians(n, ctx->mean3.as<float>(), ctx->cov6.as<float>(), ctx->density.as<float>(),
                                  ctx->albedo.as<float>(), ctx->gauss_orig.as<float4>(), ctx->box_lo.as<float>(),
                                  ctx->box_hi.as<float>(), ctx->lam.as<float>(), ctx->stream);
+        if (ctx->hierarchy_builder == 0) {
+            // everything on the device (vr_lbvh.cu): reach + slack of the boxes, Morton order, radix tree, both node formats
+            int rc = build_hierarchy_device(ctx, n, reach_RX);
+            if (rc) return rc;
+            lap("device hierarchy build");
+            launch_permute_gaussians(n, ctx->gauss_orig.as<float4>(), ctx->perm.as<uint32_t>(), ctx->gauss_leaf.as<float4>(),
+                                     ctx->leaf_of_orig.as<uint32_t>(), ctx->stream);
+            VR_CUDA(cudaGetLastError());
+            ctx->h_box_lo.clear(); ctx->h_box_hi.clear(); ctx->h_leaf_of_orig.clear();   // (host copies, if ever needed, are fetched lazily)
+            ctx->has_gmm = true;
+            return VR_OK;
+        }
         std::vector<float> lo((size_t)3 * n), hi((size_t)3 * n), lam((size_t)n);
         VR_CUDA(cudaMemcpyAsync(lo.data(), ctx->box_lo.p, lo.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         VR_CUDA(cudaMemcpyAsync(hi.data(), ctx->box_hi.p, hi.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -313,6 +330,19 @@ int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
     return VR_OK;
 }
 
+// inflated boxes (original order) and the leaf order on the host, for the light-grid builder; the device build leaves them on
+// the device until a render large enough for grids asks for them
+int fetch_host_boxes(vr_context* ctx) {
+    const int n = ctx->n;
+    if (n <= 0 || ((int)ctx->h_box_lo.size() == 3 * n && (int)ctx->h_leaf_of_orig.size() == n)) return VR_OK;
+    ctx->h_box_lo.resize((size_t)3 * n); ctx->h_box_hi.resize((size_t)3 * n); ctx->h_leaf_of_orig.resize((size_t)n);
+    VR_CUDA(cudaMemcpyAsync(ctx->h_box_lo.data(), ctx->box_lo.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(ctx->h_box_hi.data(), ctx->box_hi.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaMemcpyAsync(ctx->h_leaf_of_orig.data(), ctx->leaf_of_orig.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VR_OK;
+}
+
 // A hierarchy inflated for ray origins within (R, X) must not be used by rays from farther out: the slab test could
 // reject a box whose ellipsoid the reference's FP32 quadric accepts (vr_bvh.h).  Rebuild with 25 % head room instead.
 int ensure_reach(vr_context* ctx, float R, float X) {
@@ -334,8 +364,16 @@ int ensure_light_grids(vr_context* ctx) {
     NvtxRange range_grids("vr.light_grids");
     ctx->lg_mask = 0;
     VR_CUDA(ctx->lg_start.ensure(16)); VR_CUDA(ctx->lg_gi.ensure(16)); VR_CUDA(ctx->lg_dmin.ensure(16));
-    if (ctx->use_light_grid && ctx->n > 0 && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl &&
-        (int)ctx->h_leaf_of_orig.size() == ctx->n) {
+    if (ctx->hierarchy_builder == 0 && ctx->use_light_grid && ctx->n > 0 && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl) {
+        int rcd = build_light_grids_device(ctx);   // count / scan / fill / sort on the device (vr_lightgrid_dev.cu)
+        if (rcd) return rcd;
+        cancel_light_grid_job(ctx);
+        ctx->lg_valid = true;
+        return VR_OK;
+    }
+    if (ctx->use_light_grid && ctx->n > 0 && ctx->nl > 0 && (int)ctx->h_lpos.size() == 3 * ctx->nl) {
+        int rcb = fetch_host_boxes(ctx);
+        if (rcb) return rcb;
         LightGridHost g_sync;
         const bool speculated = ctx->lg_job != nullptr && ctx->lg_job->n == ctx->n && ctx->lg_job->nl == ctx->nl && ctx->lg_job->res == ctx->lg_res;
         if (speculated) {

@@ -55,12 +55,15 @@ struct vr_context {
     // reach of the ray origins the culling boxes were inflated for (vr_bvh.h BoxReach) and the mixture's bounding box:
     // a camera or a ray batch that reaches farther makes the next render rebuild the hierarchy (ensure_reach)
     double box_kappa = vr::kBoxKappa;
+    int hierarchy_builder = 0;                     // 0: LBVH on the device (vr_lbvh.cu), 1: binned SAH on the host (vr_bvh.cpp)
+    vr::DevBuf lbvh_keys, lbvh_tree, lbvh_tmp;     // scratch of the device build
+    unsigned int* h_build_meta = nullptr;          // pinned, 32 words: what the device build reports back
     float built_R = 0.f, built_X = 0.f, bb_lo[3] = {0.f, 0.f, 0.f}, bb_hi[3] = {0.f, 0.f, 0.f};
     float qorg[3] = {0.f, 0.f, 0.f}, qcell[3] = {1.f, 1.f, 1.f};   // grid of the compact tree (vr_bvh.h BvhQuantGrid)
     // host copies kept for the per-light direction grids (vr_lightgrid.h), built lazily before a render
     std::vector<float> h_box_lo, h_box_hi, h_lpos;
     std::vector<uint32_t> h_leaf_of_orig;
-    vr::DevBuf lg_start, lg_gi, lg_dmin;
+    vr::DevBuf lg_start, lg_gi, lg_dmin, lg_scratch;
     bool lg_valid = false;
     int lg_res = 256;
     uint32_t lg_mask = 0;
@@ -96,6 +99,7 @@ struct vr_context {
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
     int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
     int wave_slots = 0;                            // 0 = 32768 per SM (sweeps in profiles/r01_tuning.md, r01_v11/)
+    int trav_version = 2;                          // traversal kernels of the wavefront engine (vr_wave.cu): 2 wave_trav2_kernel, 1 wave_trav_kernel
     int wave_parts = 2;                            // independent parts (own pool + stream) a big pass is cut into
     cudaStream_t wave_streams[vr::kMaxWaveParts] = {nullptr, nullptr, nullptr, nullptr};
     vr::WaveGraphCache* wave_graphs = nullptr;     // CUDA graphs of the iteration batches, reused while the launch arguments stay the same
@@ -115,6 +119,9 @@ int fail(vr_context* c, int code, const std::string& msg);
 int cuda_fail(vr_context* c, cudaError_t e, const char* what);
 int render_device_impl(vr_context* c, const vr_render_params* p, vr_render_stats* st);
 int set_gmm_from_device(vr_context* c, int n, const float* reach_RX = nullptr);   // reach_RX: minimum BoxReach {R, X} to build for
+int build_hierarchy_device(vr_context* c, int n, const float* reach_RX);          // vr_lbvh.cu
+int build_light_grids_device(vr_context* c);      // vr_lightgrid_dev.cu
+int fetch_host_boxes(vr_context* c);               // vr_api.cu: inflated boxes + leaf order on the host (light-grid builder)
 int ensure_reach(vr_context* c, float R, float X);   // rebuilds the hierarchy when it was inflated for a smaller reach
 int ensure_camera_reach(vr_context* c);              // ... for the camera currently set
 void cancel_light_grid_job(vr_context* c);  // vr_api.cu: joins and drops a speculative grid build

@@ -17,6 +17,7 @@ struct RenderArgs {
     SceneDev scene;
     CameraPod cam;
     int W, H, spp, nsq;
+    int trav_version;      // wavefront traversal kernels: 2 = wave_trav2_kernel (private candidate slots), 1 = wave_trav_kernel
     int integrator;        // 0 single scatter, 1 multi scatter
     int solver, min_bounces;
     int x0, y0, win_w;     // owned pixel p -> x = x0 + p % win_w, y = y0 + (p / win_w) * part_count + part_rank

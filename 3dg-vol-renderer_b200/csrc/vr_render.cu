@@ -82,6 +82,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     A.nsq = (int)std::sqrt((double)p->spp);  // integrator.h:562
     if (A.nsq < 1) A.nsq = 1;
     A.integrator = p->integrator;
+    A.trav_version = ctx->trav_version;
     A.solver = p->solver;
     A.min_bounces = p->min_bounces;
     A.x0 = p->x0; A.y0 = p->y0; A.win_w = p->x1 - p->x0;

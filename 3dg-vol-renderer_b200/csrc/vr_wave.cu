@@ -22,6 +22,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "vr_context.h"
 #include "vr_internal.h"
@@ -471,6 +472,287 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
 }
 
 // ------------------------------------------------------------------------------------------
+// wave_trav2<KIND>: the same traversal with the per-round bookkeeping taken out of the node loop.
+//
+// SASS of wave_trav_kernel (r01): one round = one slab step per lane costs ~168 warp instructions, of which the two slab
+// tests are 39; ~45 go into queueing the hit leaf children through two ballots, ~27 into the exit conditions, the rest into
+// child classification and the stack.  Here a lane keeps its candidates in FOUR PRIVATE shared-memory slots (a predicated
+// store each, no ballot) and the node loop is left on ONE ballot: enough lanes have stopped traversing -- finished, or their
+// slots are full.  Everything warp-cooperative happens between node loops: the slots of all lanes are compacted into one
+// list (one ballot per slot level per phase, not per round), the quadric tests run 32 at a time as before, every passing
+// shadow overlap gets its depth in the same phase, and since a phase tests EVERYTHING that is queued, a lane that finished
+// traversing is complete after it: the pending / pushed counters and their shared atomics are gone.  The pruning bound and
+// the overlap count change only inside a phase, so the node loop keeps them in registers.
+// Candidates, tests and sums are the same as wave_trav_kernel's (test_trav2_equals_trav: bit-identical images).
+// ------------------------------------------------------------------------------------------
+#ifndef VR_T2_IDLE_S
+#define VR_T2_IDLE_S 8     // leave the node loop when this many lanes do not traverse (free-flight rays)
+#endif
+#ifndef VR_T2_IDLE_H
+#define VR_T2_IDLE_H 6
+#endif
+#ifndef VR_T2_IDLE_L
+#define VR_T2_IDLE_L 8
+#endif
+constexpr int kT2Slots = 4;
+template <int KIND> struct Trav2Shared {
+    float ray[7][32];
+    unsigned int pid[32];
+    int count[32];                   // free-flight: overlaps found
+    unsigned int t_bound[32];        // free-flight: pruning bound (float bits)
+    long long tau[32];               // shadow: fixed-point optical depth
+    uint32_t slot[kT2Slots][32];     // private candidate slots of the lanes
+    uint32_t queue[kT2Slots * 32];   // compacted (owner << 27) | index
+    uint32_t hq_id[kT2Slots * 32];   // shadow: overlaps waiting for their depth
+    float hq_a[kT2Slots * 32], hq_b[kT2Slots * 32];
+};
+enum { T2_FETCH = 0, T2_TRAV, T2_FULL, T2_WAIT, T2_DONE };
+struct Trav2Lane {
+    unsigned int n_nodes, n_quads, n_erf;
+    int mode, cur, sp, nq;
+    bool has_result;
+    RaySetupQ rq;
+    float tmax, tlimit;
+};
+
+// all queued candidates of all lanes: compact, test 32 at a time; returns with every slot empty
+template <int KIND>
+__device__ __forceinline__ void trav2_phase(const SceneDev& S, const WavePool& Q, Trav2Shared<KIND>& w, int lane, Trav2Lane& tl) {
+    int total = 0;
+#pragma unroll
+    for (int k = 0; k < kT2Slots; ++k) {
+        const bool has = tl.nq > k;
+        const unsigned m = __ballot_sync(0xffffffffu, has);
+        if (has) w.queue[total + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)lane << 27) | w.slot[k][lane];
+        total += __popc(m);
+    }
+    tl.nq = 0;
+    __syncwarp();
+    int nH = 0;
+    for (int base = 0; base < total; base += 32) {
+        const int it = base + lane;
+        bool to_hq = false;
+        uint32_t e = 0; float ha = 0.f, hb = 0.f;
+        if (it < total) {
+            ++tl.n_quads;
+            e = w.queue[it];
+            const int owner = (int)(e >> 27);
+            const uint32_t gi = e & 0x07ffffffu;
+            const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
+            const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
+            const GaussRec g = load_gauss(S.gauss, gi);
+            const RayQuad q = ray_quad(g, o, d);
+            float t0, t1;
+            if (quad_intersect(q, &t0, &t1)) {
+                if constexpr (KIND == RAY_SCATTER) {
+                    const float tb = __uint_as_float(w.t_bound[owner]);
+                    if (!(t0 > tb)) {
+                        const int slot = atomicAdd(&w.count[owner], 1);
+                        if (slot < kWaveCap) {
+                            pool_store_hit(Q, w.pid[owner], slot, t0, t1, gi);
+                            if (t1 < tb) {
+                                tl.n_erf += 2u;
+                                // pruning only: CONSERVATIVE estimate of this component's full optical depth (see wave_trav_kernel)
+                                const float dn = g.density * g.norm;
+                                const float inv4A = __fdividef(1.0f, 4.0f * q.A);
+                                const float K = dn * sqrtf(6.2831853f * inv4A) * __expf(-0.5f * (q.C0 - q.B * q.B * inv4A));
+                                const float iden = rsqrtf(8.0f * q.A);
+                                const float full = K * (erff_ni((q.B + 2.0f * q.A * t1) * iden) - erff_ni((q.B + 2.0f * q.A * t0) * iden));
+                                if (full > 1.5f * w.ray[6][owner]) atomicMin(&w.t_bound[owner], __float_as_uint(t1));
+                            }
+                        }
+                    }
+                } else {
+                    if (w.tau[owner] <= tau_cutoff_fixed()) {
+                        ha = fmaxf(0.0f, t0); hb = fminf(w.ray[6][owner], t1);
+                        to_hq = hb > ha;
+                    }
+                }
+            }
+        }
+        if constexpr (KIND != RAY_SCATTER) {
+            const unsigned m = __ballot_sync(0xffffffffu, to_hq);
+            if (to_hq) {
+                const int pos = nH + __popc(m & ((1u << lane) - 1u));
+                w.hq_id[pos] = e; w.hq_a[pos] = ha; w.hq_b[pos] = hb;
+            }
+            nH += __popc(m);
+        }
+    }
+    if constexpr (KIND != RAY_SCATTER) {
+        __syncwarp();
+        // exact clipped optical depth of the overlaps (gmm.h:563-571, gaussian.h:208-231), 32 at a time
+        for (int base = 0; base < nH; base += 32) {
+            const int it = base + lane;
+            if (it < nH) {
+                tl.n_erf += 2u;
+                const uint32_t e = w.hq_id[it];
+                const int owner = (int)(e >> 27);
+                const uint32_t gi = e & 0x07ffffffu;
+                const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
+                const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
+                const GaussRec g = load_gauss(S.gauss, gi);
+                const RayQuad q = ray_quad(g, o, d);
+                const DepthConst c = depth_const(g, q);
+                const float F1 = erff_ni(erf_arg(c, w.hq_b[it]));
+                const float F0 = erff_ni(erf_arg(c, w.hq_a[it]));
+                const float tau = __fmul_rn(c.K, __fsub_rn(F1, F0));
+                atomicAdd((unsigned long long*)&w.tau[owner], (unsigned long long)__double2ll_rn((double)tau * kTauFixed));
+            }
+        }
+    }
+    __syncwarp();
+}
+
+template <int KIND>
+__global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
+    __shared__ Trav2Shared<KIND> wsh[kBlockThreads / 32];
+    Trav2Shared<KIND>& w = wsh[threadIdx.x >> 5];
+    const SceneDev& S = A.scene;
+    const int lane = threadIdx.x & 31;
+    const unsigned int nT = Q.cnt[KIND == RAY_SCATTER ? WC_NTS : (KIND == RAY_SHADOW ? WC_NTH : WC_NTL)];
+    const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : (KIND == RAY_SHADOW ? Q.listTh : Q.listTl);
+    unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : (KIND == RAY_SHADOW ? WC_CURSOR_H : WC_CURSOR_L)];
+    constexpr unsigned kIdle = KIND == RAY_SCATTER ? VR_T2_IDLE_S : (KIND == RAY_SHADOW ? VR_T2_IDLE_H : VR_T2_IDLE_L);
+    if (blockIdx.x == 0 && threadIdx.x < kPostClasses + 1) {   // lists consumed by the previous kernel of the chain are free again
+        if (KIND == RAY_SCATTER) { if (threadIdx.x == 0) Q.cnt[WC_NC] = 0; }
+        else if (KIND == RAY_SHADOW) Q.cnt[WC_NA + threadIdx.x] = 0;
+    }
+    int stack[kStackDepth];
+    Trav2Lane tl;
+    tl.mode = T2_FETCH; tl.cur = 0; tl.sp = 0; tl.nq = 0; tl.has_result = false; tl.tmax = 0.f; tl.tlimit = 0.f;
+    tl.n_nodes = tl.n_quads = tl.n_erf = 0u;
+    bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
+    while (true) {
+        // ---- node loop: one slab step (or two grid entries) per traversing lane and round, until kIdle of the lanes that still
+        //      have a ray do not traverse (finished or slots full) -- or, near the end of the wave, none does
+        if (__ballot_sync(0xffffffffu, tl.mode == T2_TRAV)) {
+            const int alive = 32 - __popc(__ballot_sync(0xffffffffu, tl.mode == T2_DONE));
+            const int keep_going = max(alive - (int)kIdle, 0);   // leave once at most this many lanes traverse
+            while (true) {
+                if (tl.mode == T2_TRAV) {
+                    ++tl.n_nodes;
+                    bool more;
+                    if constexpr (KIND == RAY_LIGHT) {
+                        int pos = tl.cur;
+                        const int end = tl.sp;
+                        more = false;
+                        if (pos < end && __ldg(S.lg_dmin + pos) <= tl.tmax) {
+                            w.slot[tl.nq++][lane] = __ldg(S.lg_gi + pos); ++pos;
+                            if (pos < end && __ldg(S.lg_dmin + pos) <= tl.tmax) { w.slot[tl.nq++][lane] = __ldg(S.lg_gi + pos); ++pos; more = true; }
+                        }
+                        tl.cur = pos;
+                    } else {
+                        bool h0, h1; float tn0, tn1;
+                        int c0, c1;
+                        node_slabs_q(S.qnodes, tl.cur, tl.rq, tl.tlimit, &h0, &h1, &tn0, &tn1, &c0, &c1);
+                        if (h0 && c0 < 0) w.slot[tl.nq++][lane] = (uint32_t)(~c0) >> 3;   // a leaf child: ONE component (an empty
+                        if (h1 && c1 < 0) w.slot[tl.nq++][lane] = (uint32_t)(~c1) >> 3;   // leaf's quantised box is unhittable)
+                        const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
+                        more = true;
+                        if (i0 && i1) {
+                            const bool swap = tn1 < tn0;
+                            stack[tl.sp++] = swap ? c0 : c1;
+                            tl.cur = swap ? c1 : c0;
+                        } else if (i0) tl.cur = c0;
+                        else if (i1) tl.cur = c1;
+                        else if (tl.sp > 0) tl.cur = stack[--tl.sp];
+                        else more = false;
+                    }
+                    if (!more) tl.mode = T2_WAIT;
+                    else if (tl.nq > kT2Slots - 2) tl.mode = T2_FULL;   // another round could bring two more
+                }
+                if (__popc(__ballot_sync(0xffffffffu, tl.mode == T2_TRAV)) <= keep_going) break;
+            }
+        }
+        // ---- phase: every queued candidate is tested; afterwards a lane that finished traversing is complete
+        if (__ballot_sync(0xffffffffu, tl.nq > 0)) trav2_phase<KIND>(S, Q, w, lane, tl);
+        if (tl.mode == T2_WAIT) { tl.mode = T2_FETCH; tl.has_result = true; }
+        else if (tl.mode == T2_FULL || tl.mode == T2_TRAV) {   // the phase may have moved this lane's bound / count / depth sum
+            tl.mode = T2_TRAV;
+            if constexpr (KIND == RAY_SCATTER) {
+                tl.tlimit = __uint_as_float(w.t_bound[lane]);
+                if (w.count[lane] > kWaveCap) { tl.mode = T2_FETCH; tl.has_result = true; }     // overflow: the sample is re-traced
+            } else {
+                if (w.tau[lane] > tau_cutoff_fixed()) { tl.mode = T2_FETCH; tl.has_result = true; }   // transmittance is exactly 0
+            }
+        }
+        const unsigned mT = __ballot_sync(0xffffffffu, tl.mode == T2_TRAV);
+        const unsigned mF = __ballot_sync(0xffffffffu, tl.mode == T2_FETCH);
+        if (mF) {
+            // ---- flush finished rays: result to the slot, slot to the list of its post kernel
+            const bool flush = tl.has_result;
+            const unsigned int p = w.pid[lane];
+            if constexpr (KIND == RAY_SCATTER) {
+                const int K = flush ? w.count[lane] : 0;
+                // a ray that overlapped nothing ends the path here (integrator.h:594-597; the target draw is not committed)
+                const bool esc = flush && K == 0;
+                if (esc) {
+                    const float4 s0 = Q.ps01[kSlotF4 * (size_t)p];
+                    const uint4 s1 = reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1];
+                    A.sampleL[s1.z] = make_float4(__fadd_rn(s0.x, __fmul_rn(s0.w, S.env[0])), __fadd_rn(s0.y, __fmul_rn(s0.w, S.env[1])),
+                                                  __fadd_rn(s0.z, __fmul_rn(s0.w, S.env[2])), (float)s1.w);
+                }
+                if (flush && K > 0) reinterpret_cast<int*>(Q.hit01 + kSlotF4 * (size_t)p)[0] = K;
+                wave_append(Q.listC, &Q.cnt[WC_NC], esc, p);
+                const int cls = post_class(K);
+#pragma unroll
+                for (int c = 0; c < kPostClasses; ++c)
+                    wave_append(Q.listA + (size_t)c * Q.P, &Q.cnt[WC_NA + c], flush && K > 0 && cls == c, p);
+            } else {
+                if (flush) reinterpret_cast<long long*>(Q.ps2 + kSlotF4 * (size_t)p + 1)[0] = w.tau[lane];
+                wave_append(Q.listB, &Q.cnt[WC_NB], flush, p);
+            }
+            tl.has_result = false;
+            // ---- fetch the next rays of the wave
+            if (!exhausted) {
+                unsigned int base = 0;
+                if (lane == __ffs(mF) - 1) base = atomicAdd(cursor, (unsigned int)__popc(mF));
+                base = __shfl_sync(0xffffffffu, base, __ffs(mF) - 1);
+                if (tl.mode == T2_FETCH) {
+                    const unsigned int idx = base + (unsigned int)__popc(mF & ((1u << lane) - 1u));
+                    if (idx < nT) {
+                        const unsigned int np = __ldg(list + idx);
+                        const float4 ro = Q.ray[kSlotF4 * (size_t)np], rd = Q.ray[kSlotF4 * (size_t)np + 1];
+                        w.ray[0][lane] = ro.x; w.ray[1][lane] = ro.y; w.ray[2][lane] = ro.z;
+                        w.ray[3][lane] = rd.x; w.ray[4][lane] = rd.y; w.ray[5][lane] = rd.z;
+                        w.ray[6][lane] = ro.w;
+                        w.pid[lane] = np;
+                        if constexpr (KIND == RAY_SCATTER) { w.count[lane] = 0; w.t_bound[lane] = 0x7f800000u; tl.tlimit = CUDART_INF_F; }
+                        else w.tau[lane] = 0LL;
+                        if constexpr (KIND == RAY_LIGHT) {
+                            const int light = (__float_as_int(rd.w) >> 8) - 1;
+                            const f3 v = mk3(ro.x - __ldg(S.lpos + 3 * light), ro.y - __ldg(S.lpos + 3 * light + 1), ro.z - __ldg(S.lpos + 3 * light + 2));
+                            const size_t cells = (size_t)6 * S.lg_res * S.lg_res;
+                            const uint32_t* cs = S.lg_start + (size_t)light * (cells + 1) + light_grid_cell_dev(v, S.lg_res);
+                            tl.cur = (int)__ldg(cs); tl.sp = (int)__ldg(cs + 1);
+                            tl.tmax = __fmaf_rn(ro.w, 1.000001f, 1e-6f);   // entries farther from the light than the ray's origin cannot overlap it
+                        } else {
+                            tl.rq = ray_setup_q(S, mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z));
+                            tl.tmax = ro.w; tl.sp = 0; tl.cur = 0;
+                            if constexpr (KIND == RAY_SHADOW) tl.tlimit = ro.w;
+                        }
+                        const bool nothing = S.n == 0 || (KIND != RAY_SCATTER && !(ro.w > 0.0f));
+                        if (nothing) tl.has_result = true;   // stays in T2_FETCH: flushed at the next flush step
+                        else tl.mode = T2_TRAV;
+                    } else {
+                        tl.mode = T2_DONE;
+                    }
+                }
+                if (base + (unsigned int)__popc(mF) >= nT) exhausted = true;
+            } else if (tl.mode == T2_FETCH) {
+                tl.mode = T2_DONE;
+            }
+            __syncwarp();
+            continue;
+        }
+        if (mT == 0) break;  // nothing traverses, nothing to flush or fetch: every lane is done
+    }
+    WaveCounters cn = {0u, 0u, 0u, 0u, tl.n_nodes, tl.n_quads, tl.n_erf, 0u, 0u, 0u};
+    wave_flush_counters(A, cn);
+}
+
+// ------------------------------------------------------------------------------------------
 // post kernels: one thread per listed slot, grid-stride in whole warps so that the aggregated
 // list appends at the end of each round are executed by converged warps
 // ------------------------------------------------------------------------------------------
@@ -874,13 +1156,20 @@ void wave_graph_cache_destroy(WaveGraphCache* c) {
 
 int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int parts, int num_sms, unsigned int* h_cnt_all,
                        cudaStream_t s, cudaStream_t* part_streams, unsigned int* launches, WaveGraphCache* graphs) {
-    static int bps_s = 0, bps_h = 0, bps_l = 0;
-    if (!bps_s) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_h, wave_trav_kernel<RAY_SHADOW>, kBlockThreads, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_l, wave_trav_kernel<RAY_LIGHT>, kBlockThreads, 0);
-        bps_s = std::max(bps_s, 1); bps_h = std::max(bps_h, 1); bps_l = std::max(bps_l, 1);
-    }
+    // resident blocks per SM of the persistent traversal kernels, per kernel version (computed once, identical on every device)
+    static std::once_flag occ_once;
+    static int occ[2][3];
+    std::call_once(occ_once, [] {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0][0], wave_trav_kernel<RAY_SCATTER>, kBlockThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0][1], wave_trav_kernel<RAY_SHADOW>, kBlockThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0][2], wave_trav_kernel<RAY_LIGHT>, kBlockThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1][0], wave_trav2_kernel<RAY_SCATTER>, kBlockThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1][1], wave_trav2_kernel<RAY_SHADOW>, kBlockThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1][2], wave_trav2_kernel<RAY_LIGHT>, kBlockThreads, 0);
+        for (auto& row : occ) for (int& v : row) v = std::max(v, 1);
+    });
+    const bool t2 = a_all.trav_version != 1;
+    const int bps_s = occ[t2 ? 1 : 0][0], bps_h = occ[t2 ? 1 : 0][1], bps_l = occ[t2 ? 1 : 0][2];
     const char* prof_env = getenv("VR_WAVE_PROFILE");
     const bool prof = prof_env && prof_env[0] == '1';
     const unsigned int pass_pixels = a_all.work_count / (unsigned int)a_all.spp;
@@ -947,7 +1236,8 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         if (prof) cudaEventRecord(pe[0], st);
         wave_regen_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
         if (prof) cudaEventRecord(pe[1], st);
-        wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
+        if (t2) wave_trav2_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
+        else wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
         if (prof) cudaEventRecord(pe[2], st);
         wave_post_a_kernel<1><<<pt.grid_post, 128, 0, st>>>(a, q);
         if (pt.defer) {
@@ -963,9 +1253,13 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             cudaStreamSynchronize(st);
             for (int c = 0; c <= kPostClasses; ++c) cls_total[c] += hc[WC_NA + c];
         }
-        wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
+        if (t2) wave_trav2_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
+        else wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
         if (prof) cudaEventRecord(pe[6], st);
-        if (a.scene.lg_mask) wave_trav_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
+        if (a.scene.lg_mask) {
+            if (t2) wave_trav2_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
+            else wave_trav_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
+        }
         if (prof) cudaEventRecord(pe[4], st);
         wave_post_b_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
         if (prof) {

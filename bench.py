@@ -296,6 +296,7 @@ def main():
     ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
     ap.add_argument("--wave-slots", type=int, default=0)
     ap.add_argument("--wave-parts", type=int, default=0)
+    ap.add_argument("--hierarchy", type=int, default=-1, help="0: hierarchy and light grids built on the device (default), 1: host binned-SAH builder")
     ap.add_argument("--box-kappa", type=float, default=-1.0, help="slack of the culling boxes (vr_bvh.h inflate_boxes), default = the library's")
     ap.add_argument("--light-grid-res", type=int, default=0, help="cells per cube-map face side of the per-light grids (default 256)")
     a = ap.parse_args()
@@ -352,6 +353,8 @@ def main():
         ctx.set_option("light_grid_res", a.light_grid_res)
     if a.box_kappa >= 0:
         ctx.set_option("box_kappa", a.box_kappa)
+    if a.hierarchy >= 0:
+        ctx.set_option("hierarchy", a.hierarchy)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
     ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cam); ctx.set_gmm(scene)
     integ = vr.INTEGRATOR_SS if cfg["integrator"] == "ss" else vr.INTEGRATOR_MS

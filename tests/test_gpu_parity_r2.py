@@ -452,3 +452,28 @@ def test_comm_allreduce_is_exact_on_every_path(ctx, vr, ob, golden, scenegen):
         finally:
             for c in cs:
                 c.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# traversal kernel versions, hierarchy builders: none of them may change a bit
+# ------------------------------------------------------------------------------------------------
+def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scenegen):
+    """wave_trav2_kernel (private candidate slots, phases) against wave_trav_kernel (shared queue), the device-built LBVH and
+    light grids against the host binned-SAH tree and host grids: candidates come in another order and from another tree,
+    the quadric test decides and the sums are order independent -> images identical bit for bit, with and without grids,
+    both integrators, also on the heavy-overlap scene whose rays overflow the per-slot overlap records."""
+    cases = [(file_scene(scenegen, "rand2k"), "pin", 96, 64, 16), (file_scene(scenegen, "rand300"), "pin2", 64, 64, 9),
+             (scenegen.generate(3000, 11, nonuniform=True, diameter_range=(0.02, 0.09)), "pin", 128, 96, 16)]
+    ctx.set_option("light_grid_min_samples", 0)
+    try:
+        for scene, cam, W, H, spp in cases:
+            for integ in (vr.INTEGRATOR_MS, vr.INTEGRATOR_SS):
+                imgs = []
+                for hier, trav, grid in ((0, 2, 1), (0, 1, 1), (1, 2, 1), (1, 1, 0), (0, 2, 0)):
+                    ctx.set_option("hierarchy", hier); ctx.set_option("trav", trav); ctx.set_option("light_grid", grid)
+                    setup(ctx, ob, scene, cam)
+                    img, st = ctx.render(vr.Context.params(integ, W, H, spp))
+                    imgs.append(img)
+                    assert np.array_equal(img, imgs[0]), (hier, trav, grid)
+    finally:
+        ctx.set_option("hierarchy", 0); ctx.set_option("trav", 2); ctx.set_option("light_grid", 1); ctx.set_option("light_grid_min_samples", 16e6)
