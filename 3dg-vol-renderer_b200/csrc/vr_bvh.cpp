@@ -278,8 +278,11 @@ void inflate_boxes(int n, float* lo, float* hi, const float* lam, BoxReach reach
     const double geom = (double)reach.R * (2.0 * (double)reach.R + (double)reach.X);
     const float pad_abs = 4e-6f * std::max(16.0f, reach.X);
     for (int i = 0; i < n; ++i) {
-        double rel = std::max(0.003, kappa * eps * (double)lam[i] * geom);
-        if (!(rel < 1.0)) rel = 1.0;            // beyond this the quadric test itself is noise; the box is doubled at most
+        // the FP32 quadric accepts squared Mahalanobis radii up to 9 + dq, dq ~ kappa * eps * lam * R * (2 R + X): the box of
+        // that ellipsoid is sqrt(1 + dq / 9) times the 3-sigma box (never less than +0.3 %, never more than x3)
+        const double dq = kappa * eps * (double)lam[i] * geom;
+        double rel = std::sqrt(1.0 + std::min(dq, 72.0) / 9.0) - 1.0;
+        if (!(rel >= 0.003)) rel = 0.003;
         for (int k = 0; k < 3; ++k) {
             const float l = lo[3 * (size_t)i + k], h = hi[3 * (size_t)i + k];
             const float c = 0.5f * (l + h), e = 0.5f * (h - l);

@@ -52,17 +52,19 @@ void build_bvh(int n, const float* lo, const float* hi, BvhBuildResult* out);
 // p itself carries the rounding of coordinates of magnitude X: another O(eps * lam * R * X).  A box that is to contain every
 // ray the FLOAT test accepts must therefore grow with the reach of the ray origins.  BoxReach states that reach:
 //   R = the farthest a ray origin can be from a point of the mixture, X = the largest coordinate magnitude of origins and
-//   mixture.  inflate_boxes grows the tight 3-sigma half extents h to h * (1 + max(0.003, kappa * eps * lam * R * (2 R + X)))
-//   + 4e-6 * max(16, X) (the absolute term covers the slab arithmetic of the traversal, vr_device.cuh).
+//   mixture.  inflate_boxes grows the tight 3-sigma half extents h to h * max(1.003, sqrt(1 + dq / 9)), dq = kappa * eps * lam *
+//   R * (2 R + X) the slack of the accepted squared radius, + 4e-6 * max(16, X) (the absolute term covers the slab
+//   arithmetic of the traversal, vr_device.cuh).
 struct BoxReach { float R, X; };
 // bounding box of the tight boxes -> bb_lo/bb_hi[3]; cam_pos = nullptr: no camera known yet (the reach then assumes ray
 // origins within 8 units of the mixture's bounding box)
 BoxReach box_reach(int n, const float* lo, const float* hi, const float* cam_pos, float* bb_lo, float* bb_hi);
 // the reach a camera at cam_pos needs over a mixture bounded by bb_lo/bb_hi (film-plane offsets of camera.h:45-73 included)
 BoxReach box_reach_of(const float* bb_lo, const float* bb_hi, const float* cam_pos);
-// kappa: tools/gather_sweep.py finds no missed component on 60 000 camera and interior rays of the C2 mixture even at 0, and no
-// measurable cost up to 0.06 (gpurun_out r2c2) -- 0.03 covers ~2.5 ulp of the discriminant
-constexpr double kBoxKappa = 0.03;
+// kappa: ulps of the discriminant covered.  tools/gather_sweep.py finds no missed component on 60 000 camera and interior rays
+// of the C2 mixture even without any slack, but rays from 100 units out (the quadric's error grows with the square of the
+// distance) do lose grazing pseudo-overlaps below ~1; 1.5 costs < 1 % at C2 (profiles/r02/gather_sweep_kappa.log)
+constexpr double kBoxKappa = 1.5;
 void inflate_boxes(int n, float* lo, float* hi, const float* lam, BoxReach reach, double kappa = kBoxKappa);
 
 }  // namespace vr

@@ -25,6 +25,14 @@ struct SceneDev {
 };
 
 constexpr int kStackDepth = 64;
+// Executed-work counters (hierarchy steps, quadric tests, erf / mu_t evaluations, solves) cost registers in the hottest loops
+// (-5 % at C2), so they are compiled only into the instrumented variant of the library (csrc/Makefile: libvolrender_b200_stats.so,
+// -DVR_WORK_COUNTERS), which bench.py loads for one untimed render to fill roofline.executed.
+#ifdef VR_WORK_COUNTERS
+#define VR_COUNT(stmt) stmt
+#else
+#define VR_COUNT(stmt)
+#endif
 constexpr float kShadowTauCutoff = 120.0f;  // expf(-x) == 0 for x > 103.98: exact early-out
 
 // ------------------------------------------------------------------------------------------
@@ -35,8 +43,9 @@ template <int CAP>
 struct LocalStore {
     float f[7][CAP];
     uint32_t u[3][CAP];
-    // executed work of the walk / solvers on this store (reported next to the algorithmic counts, bench.py roofline.executed)
+#ifdef VR_WORK_COUNTERS   // executed work of the walk / solvers on this store (bench.py roofline.executed)
     unsigned int n_erf = 0, n_mu = 0, n_sa = 0, n_it = 0;
+#endif
     __device__ __forceinline__ int cap() const { return CAP; }
     __device__ __forceinline__ float& F(int field, int s) { return f[field][s]; }
     __device__ __forceinline__ uint32_t& U(int field, int s) { return u[field][s]; }
@@ -44,7 +53,9 @@ struct LocalStore {
 struct ArenaStore {   // global memory, warp-interleaved: element (field, slot) of lane l at base[(field*cap+slot)*32 + l]
     float* base;
     int capacity;
+#ifdef VR_WORK_COUNTERS
     unsigned int n_erf = 0, n_mu = 0, n_sa = 0, n_it = 0;
+#endif
     __device__ __forceinline__ int cap() const { return capacity; }
     __device__ __forceinline__ float& F(int field, int s) { return base[((size_t)field * capacity + s) * 32]; }
     __device__ __forceinline__ uint32_t& U(int field, int s) {
@@ -257,7 +268,7 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return (v
 template <class St>
 __device__ __noinline__ float sum_depth_to(St& st, int na, float tt) {  // sum_k tau_k(ta, tt), float, active order
     float sum = 0.0f;
-    st.n_erf += (unsigned int)na;
+    VR_COUNT(st.n_erf += (unsigned int)na;)
     for (int k = 0; k < na; ++k) {
         const int s = (int)st.U(U_ACT, k);
         const DepthConst c = hit_const(st, s);
@@ -268,7 +279,7 @@ __device__ __noinline__ float sum_depth_to(St& st, int na, float tt) {  // sum_k
 template <class St>
 __device__ __noinline__ float solve_bisection(St& st, int na, float ta, float tb, float target) {  // :25-57
     float a = ta, b = tb;
-    ++st.n_it;
+    VR_COUNT(++st.n_it;)
     for (int i = 0; i < 15; ++i) {
         float mid = __fmul_rn(0.5f, __fadd_rn(a, b));
         float f = __fsub_rn(sum_depth_to(st, na, mid), target);
@@ -281,7 +292,7 @@ template <class St>
 __device__ __noinline__ float solve_newton(St& st, int na, float ta, float tb, float target) {  // :62-127
     const float tol = 1e-6f;
     const float a = ta, b = tb;
-    ++st.n_it;
+    VR_COUNT(++st.n_it;)
     float t = __fmul_rn(0.5f, __fadd_rn(a, b));
     for (int iter = 0; iter < 8; ++iter) {
         float f = __fsub_rn(sum_depth_to(st, na, fminf(t, b)), target);
@@ -314,7 +325,7 @@ __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, f
         const GaussRec g = load_gauss(S.gauss, st.U(U_GI, s));
         const RayQuad q = ray_quad(g, o, d);
         float t_an;
-        ++st.n_sa;
+        VR_COUNT(++st.n_sa;)
         if (solve_t_given_tau(g, q, ta, tb, remaining, &t_an)) return clampf(t_an, ta, tb);
     }
     if (DEFER) { *deferred = true; return ta; }
@@ -399,7 +410,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
         // optical depth of the segment [t_prev, t_evt] over the active set
         bool hit_target;
         float remaining;
-        st.n_erf += (unsigned int)na;
+        VR_COUNT(st.n_erf += (unsigned int)na;)
         if (ss) {
             float seg = 0.0f;
             for (int k = 0; k < na; ++k) {
@@ -424,7 +435,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
             if (!hit_target) acc = __dadd_rn(acc, seg);
         }
         if (hit_target) {
-            st.n_erf += (unsigned int)na;
+            VR_COUNT(st.n_erf += (unsigned int)na;)
             for (int k = 0; k < na; ++k)  // restore erf(arg(t_prev)) for the solver
                 st.F(F_ACTF, k) = erff_ni(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
             *na_out = na;
@@ -432,7 +443,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
         }
         if (take_enter) {
             const float F0 = erff_ni(erf_arg(hit_const(st, se), t_evt));
-            ++st.n_erf;
+            VR_COUNT(++st.n_erf;)
             int pos = na;
             if (ss) {  // FreeFlightGaussians rescans a bool vector in ascending index order (integrator.h:344-346)
                 const uint32_t oe = __ldg(S.orig + st.U(U_GI, se));
@@ -464,7 +475,7 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
 template <class St>
 __device__ float evaluate_albedo(const SceneDev& S, St& st, int na, f3 pos) {
     float sum_mu = 0.0f, sum_mu_alb = 0.0f;
-    st.n_mu += (unsigned int)na;
+    VR_COUNT(st.n_mu += (unsigned int)na;)
     for (int k = 0; k < na; ++k) {
         const GaussRec g = load_gauss(S.gauss, st.U(U_GI, (int)st.U(U_ACT, k)));
         const float mu = gauss_mu_t(g, pos);

@@ -97,8 +97,9 @@ __global__ void inflate_kernel(int n, float* __restrict__ lo, float* __restrict_
     const double eps = 5.9604644775390625e-08;   // 2^-24
     const double geom = (double)R * (2.0 * (double)R + (double)X);
     const float pad_abs = 4e-6f * fmaxf(16.0f, X);
-    double rel = fmax(0.003, ra.kappa * eps * (double)lam[i] * geom);
-    if (!(rel < 1.0)) rel = 1.0;
+    const double dq = ra.kappa * eps * (double)lam[i] * geom;          // inflate_boxes() of vr_bvh.cpp
+    double rel = sqrt(1.0 + fmin(dq, 72.0) / 9.0) - 1.0;
+    if (!(rel >= 0.003)) rel = 0.003;
     for (int k = 0; k < 3; ++k) {
         const float l = lo[3 * (size_t)i + k], h = hi[3 * (size_t)i + k];
         const float c = 0.5f * (l + h), e = 0.5f * (h - l);

@@ -73,20 +73,24 @@ __device__ __forceinline__ void wave_flush_counters(const RenderArgs& A, WaveCou
         cn.shadow += __shfl_down_sync(0xffffffffu, cn.shadow, o);
         cn.hits += __shfl_down_sync(0xffffffffu, cn.hits, o);
         cn.over += __shfl_down_sync(0xffffffffu, cn.over, o);
+#ifdef VR_WORK_COUNTERS
         cn.nodes += __shfl_down_sync(0xffffffffu, cn.nodes, o);
         cn.quads += __shfl_down_sync(0xffffffffu, cn.quads, o);
         cn.erf += __shfl_down_sync(0xffffffffu, cn.erf, o);
         cn.mu += __shfl_down_sync(0xffffffffu, cn.mu, o);
         cn.sa += __shfl_down_sync(0xffffffffu, cn.sa, o);
         cn.it += __shfl_down_sync(0xffffffffu, cn.it, o);
+#endif
     }
     if ((threadIdx.x & 31) == 0) {
+#ifdef VR_WORK_COUNTERS
         if (cn.nodes) atomicAdd(A.stats + ST_NODES, (unsigned long long)cn.nodes);
         if (cn.quads) atomicAdd(A.stats + ST_QUADRICS, (unsigned long long)cn.quads);
         if (cn.erf) atomicAdd(A.stats + ST_ERF, (unsigned long long)cn.erf);
         if (cn.mu) atomicAdd(A.stats + ST_MU, (unsigned long long)cn.mu);
         if (cn.sa) atomicAdd(A.stats + ST_SA, (unsigned long long)cn.sa);
         if (cn.it) atomicAdd(A.stats + ST_ITER, (unsigned long long)cn.it);
+#endif
         if (cn.scatter) atomicAdd(A.stats + ST_SCATTER_RAYS, (unsigned long long)cn.scatter);
         if (cn.shadow) atomicAdd(A.stats + ST_SHADOW_RAYS, (unsigned long long)cn.shadow);
         if (cn.hits) atomicAdd(A.stats + ST_HITS, (unsigned long long)cn.hits);
@@ -183,7 +187,9 @@ template <> struct TravShared<RAY_LIGHT> : TravShared<RAY_SHADOW> {};   // same 
 enum { T_FETCH = 0, T_TRAV, T_WAIT, T_DONE };
 
 struct TravLane {
+#ifdef VR_WORK_COUNTERS
     unsigned int n_nodes, n_quads, n_erf;   // executed work of this lane
+#endif
     int mode, cur, sp;
     int pushed;   // candidates this lane queued for its current ray; w.pending[lane] counts the ones already tested
     bool has_result;
@@ -195,7 +201,7 @@ struct TravLane {
 __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const WavePool& Q, TravShared<RAY_SCATTER>& w, int lane,
                                                       int q_begin, int nb, TravLane& tl) {
     if (lane < nb) {
-        ++tl.n_quads;
+        VR_COUNT(++tl.n_quads;)
         const uint32_t e = w.queue[q_begin + lane];
         const int owner = (int)(e >> 27);
         const uint32_t gi = e & 0x07ffffffu;
@@ -211,7 +217,7 @@ __device__ __forceinline__ void scatter_quadric_batch(const SceneDev& S, const W
                 if (slot < kWaveCap) {
                     pool_store_hit(Q, w.pid[owner], slot, t0, t1, gi);
                     if (t1 < tb) {
-                        tl.n_erf += 2u;
+                        VR_COUNT(tl.n_erf += 2u;)
                         // pruning only: CONSERVATIVE estimate of this component's full optical depth
                         // (fast intrinsics; 1.5x margin covers the FP32 slack of the exact expression)
                         const float dn = g.density * g.norm;
@@ -234,7 +240,7 @@ __device__ __forceinline__ void shadow_quadric_batch(const SceneDev& S, TravShar
     bool to_hq = false;
     uint32_t e = 0; float ha = 0.f, hb = 0.f;
     if (lane < nb) {
-        ++tl.n_quads;
+        VR_COUNT(++tl.n_quads;)
         e = w.queue[q_begin + lane];
         const int owner = (int)(e >> 27);
         const uint32_t gi = e & 0x07ffffffu;
@@ -260,7 +266,7 @@ __device__ __forceinline__ void shadow_quadric_batch(const SceneDev& S, TravShar
 // exact clipped optical depth of up to 32 shadow overlaps (gmm.h:563-571, gaussian.h:208-231)
 __device__ __forceinline__ void shadow_depth_batch(const SceneDev& S, TravShared<RAY_SHADOW>& w, int lane, int h_begin, int nb, TravLane& tl) {
     if (lane < nb) {
-        tl.n_erf += 2u;
+        VR_COUNT(tl.n_erf += 2u;)
         const uint32_t e = w.hq_id[h_begin + lane];
         const int owner = (int)(e >> 27);
         const uint32_t gi = e & 0x07ffffffu;
@@ -286,7 +292,7 @@ __device__ __forceinline__ void trav_rounds(const SceneDev& S, TravShared<KIND>&
         bool l0 = false, l1 = false, fin = false;
         uint32_t g0 = 0, g1 = 0;   // leaf-order indices of the candidates this lane queues in this round
         if (tl.mode == T_TRAV) {
-            ++tl.n_nodes;
+            VR_COUNT(++tl.n_nodes;)
             if constexpr (KIND == RAY_LIGHT) {
                 // candidates come from the cell list of the light's direction grid, nearest to the light first; the
                 // list ends for this ray at the first component that lies beyond the ray's origin (vr_lightgrid.h)
@@ -362,7 +368,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
     int stack[kStackDepth];
     TravLane tl;
     tl.mode = T_FETCH; tl.cur = 0; tl.sp = 0; tl.has_result = false; tl.tmax = 0.f; tl.pushed = 0;
-    tl.n_nodes = tl.n_quads = tl.n_erf = 0u;
+    VR_COUNT(tl.n_nodes = tl.n_quads = tl.n_erf = 0u;)
     int nQ = 0, nH = 0;
     unsigned int n_escaped = 0;
     bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
@@ -467,8 +473,10 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
         trav_rounds<KIND>(S, w, lane, tl, stack, nQ, !exhausted);
     }
     (void)n_escaped;
+#ifdef VR_WORK_COUNTERS
     WaveCounters cn = {0u, 0u, 0u, 0u, tl.n_nodes, tl.n_quads, tl.n_erf, 0u, 0u, 0u};
     wave_flush_counters(A, cn);
+#endif
 }
 
 // ------------------------------------------------------------------------------------------
@@ -494,6 +502,17 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
 #ifndef VR_T2_IDLE_L
 #define VR_T2_IDLE_L 8
 #endif
+// finished rays are flushed (result to the slot, slot to a work list: up to six warp-aggregated appends) and their lanes
+// refilled once this many wait -- or nothing traverses any more
+#ifndef VR_T2_FETCH_S
+#define VR_T2_FETCH_S 8
+#endif
+#ifndef VR_T2_FETCH_H
+#define VR_T2_FETCH_H 6
+#endif
+#ifndef VR_T2_FETCH_L
+#define VR_T2_FETCH_L 8
+#endif
 constexpr int kT2Slots = 4;
 template <int KIND> struct Trav2Shared {
     float ray[7][32];
@@ -508,7 +527,9 @@ template <int KIND> struct Trav2Shared {
 };
 enum { T2_FETCH = 0, T2_TRAV, T2_FULL, T2_WAIT, T2_DONE };
 struct Trav2Lane {
+#ifdef VR_WORK_COUNTERS
     unsigned int n_nodes, n_quads, n_erf;
+#endif
     int mode, cur, sp, nq;
     bool has_result;
     RaySetupQ rq;
@@ -534,7 +555,7 @@ __device__ __forceinline__ void trav2_phase(const SceneDev& S, const WavePool& Q
         bool to_hq = false;
         uint32_t e = 0; float ha = 0.f, hb = 0.f;
         if (it < total) {
-            ++tl.n_quads;
+            VR_COUNT(++tl.n_quads;)
             e = w.queue[it];
             const int owner = (int)(e >> 27);
             const uint32_t gi = e & 0x07ffffffu;
@@ -551,7 +572,7 @@ __device__ __forceinline__ void trav2_phase(const SceneDev& S, const WavePool& Q
                         if (slot < kWaveCap) {
                             pool_store_hit(Q, w.pid[owner], slot, t0, t1, gi);
                             if (t1 < tb) {
-                                tl.n_erf += 2u;
+                                VR_COUNT(tl.n_erf += 2u;)
                                 // pruning only: CONSERVATIVE estimate of this component's full optical depth (see wave_trav_kernel)
                                 const float dn = g.density * g.norm;
                                 const float inv4A = __fdividef(1.0f, 4.0f * q.A);
@@ -585,7 +606,7 @@ __device__ __forceinline__ void trav2_phase(const SceneDev& S, const WavePool& Q
         for (int base = 0; base < nH; base += 32) {
             const int it = base + lane;
             if (it < nH) {
-                tl.n_erf += 2u;
+                VR_COUNT(tl.n_erf += 2u;)
                 const uint32_t e = w.hq_id[it];
                 const int owner = (int)(e >> 27);
                 const uint32_t gi = e & 0x07ffffffu;
@@ -614,6 +635,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
     const unsigned int* __restrict__ list = KIND == RAY_SCATTER ? Q.listTs : (KIND == RAY_SHADOW ? Q.listTh : Q.listTl);
     unsigned int* cursor = &Q.cnt[KIND == RAY_SCATTER ? WC_CURSOR_S : (KIND == RAY_SHADOW ? WC_CURSOR_H : WC_CURSOR_L)];
     constexpr unsigned kIdle = KIND == RAY_SCATTER ? VR_T2_IDLE_S : (KIND == RAY_SHADOW ? VR_T2_IDLE_H : VR_T2_IDLE_L);
+    constexpr int kFetch = KIND == RAY_SCATTER ? VR_T2_FETCH_S : (KIND == RAY_SHADOW ? VR_T2_FETCH_H : VR_T2_FETCH_L);
     if (blockIdx.x == 0 && threadIdx.x < kPostClasses + 1) {   // lists consumed by the previous kernel of the chain are free again
         if (KIND == RAY_SCATTER) { if (threadIdx.x == 0) Q.cnt[WC_NC] = 0; }
         else if (KIND == RAY_SHADOW) Q.cnt[WC_NA + threadIdx.x] = 0;
@@ -621,7 +643,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
     int stack[kStackDepth];
     Trav2Lane tl;
     tl.mode = T2_FETCH; tl.cur = 0; tl.sp = 0; tl.nq = 0; tl.has_result = false; tl.tmax = 0.f; tl.tlimit = 0.f;
-    tl.n_nodes = tl.n_quads = tl.n_erf = 0u;
+    VR_COUNT(tl.n_nodes = tl.n_quads = tl.n_erf = 0u;)
     bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
     while (true) {
         // ---- node loop: one slab step (or two grid entries) per traversing lane and round, until kIdle of the lanes that still
@@ -631,7 +653,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
             const int keep_going = max(alive - (int)kIdle, 0);   // leave once at most this many lanes traverse
             while (true) {
                 if (tl.mode == T2_TRAV) {
-                    ++tl.n_nodes;
+                    VR_COUNT(++tl.n_nodes;)
                     bool more;
                     if constexpr (KIND == RAY_LIGHT) {
                         int pos = tl.cur;
@@ -679,9 +701,9 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
         }
         const unsigned mT = __ballot_sync(0xffffffffu, tl.mode == T2_TRAV);
         const unsigned mF = __ballot_sync(0xffffffffu, tl.mode == T2_FETCH);
-        if (mF) {
+        if (mF && (__popc(mF) >= kFetch || mT == 0)) {
             // ---- flush finished rays: result to the slot, slot to the list of its post kernel
-            const bool flush = tl.has_result;
+            const bool flush = tl.mode == T2_FETCH && tl.has_result;
             const unsigned int p = w.pid[lane];
             if constexpr (KIND == RAY_SCATTER) {
                 const int K = flush ? w.count[lane] : 0;
@@ -748,8 +770,10 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
         }
         if (mT == 0) break;  // nothing traverses, nothing to flush or fetch: every lane is done
     }
+#ifdef VR_WORK_COUNTERS
     WaveCounters cn = {0u, 0u, 0u, 0u, tl.n_nodes, tl.n_quads, tl.n_erf, 0u, 0u, 0u};
     wave_flush_counters(A, cn);
+#endif
 }
 
 // ------------------------------------------------------------------------------------------
@@ -923,10 +947,10 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     const float F0 = erff_ni(erf_arg(c, t0));
                     const float F1 = erff_ni(erf_arg(c, t1));
                     const float seg = __fmul_rn(c.K, __fsub_rn(F1, F0));
-                    cn.erf += 2u;
+                    VR_COUNT(cn.erf += 2u;)
                     if (seg > target_tau) {   // float and double comparisons agree: the conversion is exact
                         float t_an;
-                        ++cn.sa;
+                        VR_COUNT(++cn.sa;)
                         if (solve_t_given_tau(g, q, t0, t1, target_tau, &t_an)) { t = clampf(t_an, t0, t1); solved = true; }
                     } else {
                         solved = true;        // the ray leaves the component: t stays -1
@@ -934,7 +958,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     if (solved) {
                         if (t >= 0.0f) {       // evaluate_albedo over the one active component (gmm.h:128-143)
                             const float mu = gauss_mu_t(g, add3(o, scale3(t, d)));
-                            ++cn.mu;
+                            VR_COUNT(++cn.mu;)
                             const float a = __fdiv_rn(__fadd_rn(0.0f, __fmul_rn(mu, g.albedo)), __fadd_rn(0.0f, mu));
                             albedo = a < 0.0f ? 0.0f : (1.0f < a ? 1.0f : a);
                         }
@@ -991,7 +1015,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 const float albedo = t >= 0.0f ? evaluate_albedo(S, st, na, add3(o, scale3(t, d))) : 0.0f;
                 dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
                 }
-                cn.erf += st.n_erf; cn.mu += st.n_mu; cn.sa += st.n_sa; cn.it += st.n_it;
+                VR_COUNT(cn.erf += st.n_erf; cn.mu += st.n_mu; cn.sa += st.n_sa; cn.it += st.n_it;)
             }
         }
         if (FAST) wave_append(Q.listA + (size_t)1 * Q.P, &Q.cnt[WC_NA + 1], hand_over, p);

@@ -69,17 +69,19 @@ def build(force: bool = False) -> str:
     return LIB_PATH
 
 
-_lib = None
+_libs = {}
+STATS_LIB_PATH = os.path.join(HERE, "libvolrender_b200_stats.so")   # instrumented twin: executed-work counters (csrc/Makefile)
 
 
-def lib():
-    """Load the shared library (no compute call is made; works without a GPU)."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
-        raise FileNotFoundError(f"{LIB_PATH} is missing: run __graft_entry__.build() (there is no CPU fallback)")
-    L = C.CDLL(LIB_PATH)
+def lib(path: str | None = None):
+    """Load the shared library (no compute call is made; works without a GPU).  path: another build of the same library
+    (the instrumented twin STATS_LIB_PATH); default = the product library."""
+    path = path or LIB_PATH
+    if path in _libs:
+        return _libs[path]
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} is missing: run __graft_entry__.build() (there is no CPU fallback)")
+    L = C.CDLL(path)
     vp, ci, fp = C.c_void_p, C.c_int, C.c_void_p
     L.vr_create.argtypes = [C.POINTER(vp), ci]
     L.vr_destroy.argtypes = [vp]; L.vr_destroy.restype = None
@@ -128,7 +130,7 @@ def lib():
     L.vr_kat_fdiff.argtypes = [vp, ci, ci, fp, fp, fp, fp, fp]
     L.vr_kat_libm.argtypes = [vp, ci, fp, fp, fp, fp]
     L.vr_kat_erfinv.argtypes = [vp, ci, fp, fp]
-    _lib = L
+    _libs[path] = L
     return L
 
 
@@ -171,8 +173,8 @@ def camera_basis(kind: str, pos, look=None, view_dir=None, fov: float = 0.25 * n
 class Context:
     """One device context (vr_create .. vr_destroy)."""
 
-    def __init__(self, device: int = 0):
-        self.L = lib()
+    def __init__(self, device: int = 0, lib_path: str | None = None):
+        self.L = lib(lib_path)
         self.h = C.c_void_p()
         rc = self.L.vr_create(C.byref(self.h), device)
         if rc:

@@ -296,6 +296,7 @@ def main():
     ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
     ap.add_argument("--wave-slots", type=int, default=0)
     ap.add_argument("--wave-parts", type=int, default=0)
+    ap.add_argument("--trav", type=int, default=0, help="traversal kernels of the wavefront engine: 2 (default) wave_trav2_kernel, 1 wave_trav_kernel")
     ap.add_argument("--hierarchy", type=int, default=-1, help="0: hierarchy and light grids built on the device (default), 1: host binned-SAH builder")
     ap.add_argument("--box-kappa", type=float, default=-1.0, help="slack of the culling boxes (vr_bvh.h inflate_boxes), default = the library's")
     ap.add_argument("--light-grid-res", type=int, default=0, help="cells per cube-map face side of the per-light grids (default 256)")
@@ -355,6 +356,8 @@ def main():
         ctx.set_option("box_kappa", a.box_kappa)
     if a.hierarchy >= 0:
         ctx.set_option("hierarchy", a.hierarchy)
+    if a.trav:
+        ctx.set_option("trav", a.trav)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
     ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cam); ctx.set_gmm(scene)
     integ = vr.INTEGRATOR_SS if cfg["integrator"] == "ss" else vr.INTEGRATOR_MS
@@ -465,22 +468,34 @@ def main():
                      f"; FP32 peak = {n_sms} SMs x 128 x 2 x {sm_clock:.0f} MHz, MUFU peak = {n_sms} x 16 x clock (clock sampled under load); "
                      "time = device time of the step's wave kernels (CUDA events on the context's stream); hierarchy / grid "
                      "traversal is implementation overhead and is NOT counted as achieved work (see profiles/ for raw pipe utilisation)")
-    # EXECUTED work from the device's own counters (vr_render_stats): what the culling, the walk and the solvers really ran,
-    # in the same cost model (quadric 62 + constants 12 FLOP, erf 22, mu_t 28, analytic solve 40, vertex 40)
-    # plus 44 FLOP per hierarchy step (two child boxes: 12 FMA + 8 three-input min/max)
-    ns = float(stats["samples"]) if stats["samples"] else 1.0
-    ex = {k: stats[k] / ns for k in ("node_visits", "quadric_tests", "hits", "erf_evals", "mu_evals", "analytic_solves", "iterative_solves", "scatter_rays", "shadow_rays")}
-    ex_flop = (44 * ex["node_visits"] + 62 * ex["quadric_tests"] + 12 * ex["hits"] + 22 * ex["erf_evals"] + 28 * ex["mu_evals"] +
-               40 * ex["analytic_solves"] + 40 * ex["scatter_rays"])
-    ex_mufu = 3 * ex["quadric_tests"] + 2 * ex["hits"] + ex["erf_evals"] + ex["mu_evals"] + 4 * ex["analytic_solves"] + 5 * ex["scatter_rays"]
-    ex_f = ex_flop * samples_per_launch / (launch_ms * 1e-3) * 1e-12
-    ex_m = ex_mufu * samples_per_launch / (launch_ms * 1e-3) * 1e-12
-    roof["executed"] = dict(per_sample=ex, flop_per_sample=ex_flop, mufu_per_sample=ex_mufu,
-                            fp32=dict(achieved=ex_f, peak=peak_tflops, unit="TFLOP/s", frac=ex_f / peak_tflops),
-                            mufu=dict(achieved=ex_m, peak=peak_mufu, unit="Tops/s", frac=ex_m / peak_mufu),
-                            note="device counters of the wavefront kernels of the last timed step (overflow re-trace and drain, < 2 % of the samples, "
-                                 "not counted); the gap to the algorithmic figure above is culling (hierarchy steps, rejected quadric tests), "
-                                 "the gap to the raw pipe utilisation in profiles/ is control flow and divergence")
+    # EXECUTED work from the device's own counters: what the culling, the walk and the solvers really ran, in the same cost
+    # model (quadric 62 + constants 12 FLOP, erf 22, mu_t 28, analytic solve 40, vertex 40) plus 44 FLOP per
+    # hierarchy step (two child boxes: 12 FMA + 8 three-input min/max).  The counters cost registers in the hottest loops, so
+    # they live in the instrumented twin of the library, which renders the same image ONCE here, untimed.
+    try:
+        sctx = vr.Context(local_rank, lib_path=vr.STATS_LIB_PATH)
+        for name, val in (("engine", a.engine), ("trav", a.trav), ("hierarchy", a.hierarchy), ("box_kappa", a.box_kappa)):
+            if (name == "engine") or (val and val > 0) or (name == "hierarchy" and val == 0):
+                sctx.set_option(name, val)
+        sctx.set_lights(scene["lights"], ENV); sctx.set_camera(cam); sctx.set_gmm(scene)
+        sst = sctx.render_device(vr.Context.params(integ, W, H, min(spp, 64)))
+        sctx.close()
+        ns = float(sst["samples"]) if sst["samples"] else 1.0
+        ex = {k: sst[k] / ns for k in ("node_visits", "quadric_tests", "hits", "erf_evals", "mu_evals", "analytic_solves", "iterative_solves", "scatter_rays", "shadow_rays")}
+        ex_flop = (44 * ex["node_visits"] + 62 * ex["quadric_tests"] + 12 * ex["hits"] + 22 * ex["erf_evals"] + 28 * ex["mu_evals"] +
+                   40 * ex["analytic_solves"] + 40 * ex["scatter_rays"])
+        ex_mufu = 3 * ex["quadric_tests"] + 2 * ex["hits"] + ex["erf_evals"] + ex["mu_evals"] + 4 * ex["analytic_solves"] + 5 * ex["scatter_rays"]
+        ex_f = ex_flop * samples_per_launch / (launch_ms * 1e-3) * 1e-12
+        ex_m = ex_mufu * samples_per_launch / (launch_ms * 1e-3) * 1e-12
+        roof["executed"] = dict(per_sample=ex, flop_per_sample=ex_flop, mufu_per_sample=ex_mufu,
+                                fp32=dict(achieved=ex_f, peak=peak_tflops, unit="TFLOP/s", frac=ex_f / peak_tflops),
+                                mufu=dict(achieved=ex_m, peak=peak_mufu, unit="Tops/s", frac=ex_m / peak_mufu),
+                                note=f"device counters of the wavefront kernels, counted by libvolrender_b200_stats.so on one untimed render of the same image at "
+                                     f"{min(spp, 64)} spp (overflow re-trace and drain, < 2 % of the samples, not counted), applied to the timed rate; the gap to "
+                                     "the algorithmic figure above is culling (hierarchy steps, rejected quadric tests), the gap to the raw pipe utilisation "
+                                     "in profiles/ is control flow and divergence")
+    except Exception as e:
+        roof["executed"] = {"error": f"{type(e).__name__}: {e}"}
     cpu = None
     if not a.no_cpu_baseline:
         cpu = cpu_render_sample(cfg, scene)

@@ -74,6 +74,7 @@ def lib():
     L.vo_transmittance_batch.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, _f32p]
     L.vo_intersect_events.restype = C.c_int
     L.vo_intersect_events.argtypes = [C.c_void_p, _f32p, _f32p, C.c_int, _f32p, _i32p, _u32p]
+    L.vo_intersect_all.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, C.c_int, _i32p, _u32p]
     L.vo_render.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int,
                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_void_p,
                             C.c_void_p, C.c_int]
@@ -139,6 +140,13 @@ class Gmm:
         out = np.empty(o.shape[0], np.float32)
         lib().vo_transmittance_batch(self.h, o.shape[0], o, d, tmax, out)
         return out
+
+    def intersect_all(self, o, d, cap=64):
+        """brute force: per ray the components the FP32 quadric test accepts, no hierarchy -> (counts[n], idx[n, cap])"""
+        o = _c(o); d = _c(d)
+        cnt = np.zeros(o.shape[0], np.int32); idx = np.zeros((o.shape[0], cap), np.uint32)
+        lib().vo_intersect_all(self.h, o.shape[0], o, d, cap, cnt, idx)
+        return cnt, idx
 
     def events(self, o, d, cap=4096):
         t = np.empty(cap, np.float32); e = np.empty(cap, np.int32); idx = np.empty(cap, np.uint32)

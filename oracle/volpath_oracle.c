@@ -659,6 +659,23 @@ VO_EXPORT int vo_intersect_events(const vo_gmm* m, const float* o, const float* 
     return n;
 }
 
+/* every component the FP32 quadric test (gaussian.h:126-164) accepts for a batch of rays, WITHOUT any hierarchy: the set a
+ * culling structure must not lose members of.  idx[r * cap + k] = component indices (ascending), counts[r] = how many. */
+VO_EXPORT void vo_intersect_all(const vo_gmm* m, int nrays, const float* o3, const float* d3, int cap, int* counts, uint32_t* idx) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int r = 0; r < nrays; ++r) {
+        vo_ray ray;
+        ray.o = v3_make(o3[3 * r], o3[3 * r + 1], o3[3 * r + 2]);
+        ray.d = v3_make(d3[3 * r], d3[3 * r + 1], d3[3 * r + 2]);
+        int c = 0;
+        for (int g = 0; g < m->n; ++g) {
+            float t0, t1;
+            if (gauss_intersect(&m->g[g], &ray, &t0, &t1)) { if (c < cap) idx[(size_t)r * cap + c] = (uint32_t)g; ++c; }
+        }
+        counts[r] = c;
+    }
+}
+
 /* ------------------------------------------------------------------------- */
 /* Forward integrators -- include/integrator.h                                */
 /* ------------------------------------------------------------------------- */

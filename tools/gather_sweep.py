@@ -43,7 +43,7 @@ for i in range(n):
     _, _, idx = gm.events(o[i], d[i]); ref.append(frozenset(idx.tolist()))
 print(f"oracle sets: {time.time() - t0:.1f} s, mean overlaps per ray {np.mean([len(r) for r in ref]):.2f}", flush=True)
 p = vr.Context.params(vr.INTEGRATOR_MS, 1024, 1024, 16)
-for kappa in (0.0, 0.006, 0.012, 0.03, 0.06, 0.12):
+for kappa in (0.0, 0.5, 1.0, 1.5, 2.0, 4.0):
     ctx.set_option("box_kappa", kappa)
     ctx.set_gmm(scene)
     cnt, idx = ctx.kat_gather(o, d, cap=16)
