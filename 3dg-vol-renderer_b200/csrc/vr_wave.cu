@@ -493,44 +493,48 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
 // the overlap count change only inside a phase, so the node loop keeps them in registers.
 // Candidates, tests and sums are the same as wave_trav_kernel's (test_trav2_equals_trav: bit-identical images).
 // ------------------------------------------------------------------------------------------
+// leave the node loop when this many lanes do not traverse; sweep at C2 (profiles/r02/trav2_threshold_sweep.md):
+// 4 -> 229, 8 -> 268, 12 -> 279, 16 -> 289, 24 -> 288 Msamples/s
 #ifndef VR_T2_IDLE_S
-#define VR_T2_IDLE_S 8     // leave the node loop when this many lanes do not traverse (free-flight rays)
+#define VR_T2_IDLE_S 16
 #endif
 #ifndef VR_T2_IDLE_H
-#define VR_T2_IDLE_H 6
+#define VR_T2_IDLE_H 16
 #endif
 #ifndef VR_T2_IDLE_L
-#define VR_T2_IDLE_L 8
+#define VR_T2_IDLE_L 16
 #endif
 // finished rays are flushed (result to the slot, slot to a work list: up to six warp-aggregated appends) and their lanes
 // refilled once this many wait -- or nothing traverses any more
 #ifndef VR_T2_FETCH_S
-#define VR_T2_FETCH_S 8
+#define VR_T2_FETCH_S 12
 #endif
 #ifndef VR_T2_FETCH_H
-#define VR_T2_FETCH_H 6
+#define VR_T2_FETCH_H 12
 #endif
 #ifndef VR_T2_FETCH_L
-#define VR_T2_FETCH_L 8
+#define VR_T2_FETCH_L 12
 #endif
 constexpr int kT2Slots = 4;
+// 2.3 KB per warp: the traversal kernels live on L1 hits (hierarchy nodes, component records, the per-lane stacks in local
+// memory), and shared memory comes out of the same 256 KB -- at 4 KB per warp the L1 hit rate of the node loads fell from 82 to
+// 72 % and that of the stacks from 52 to 19 % (profiles/r02/trav2_first_ncu.md)
 template <int KIND> struct Trav2Shared {
     float ray[7][32];
     unsigned int pid[32];
-    int count[32];                   // free-flight: overlaps found
-    unsigned int t_bound[32];        // free-flight: pruning bound (float bits)
-    long long tau[32];               // shadow: fixed-point optical depth
+    union {
+        struct { int count[32]; unsigned int t_bound[32]; };   // free-flight: overlaps found, pruning bound (float bits)
+        long long tau[32];                                      // shadow: fixed-point optical depth
+    };
     uint32_t slot[kT2Slots][32];     // private candidate slots of the lanes
     uint32_t queue[kT2Slots * 32];   // compacted (owner << 27) | index
-    uint32_t hq_id[kT2Slots * 32];   // shadow: overlaps waiting for their depth
-    float hq_a[kT2Slots * 32], hq_b[kT2Slots * 32];
 };
 enum { T2_FETCH = 0, T2_TRAV, T2_FULL, T2_WAIT, T2_DONE };
 struct Trav2Lane {
 #ifdef VR_WORK_COUNTERS
     unsigned int n_nodes, n_quads, n_erf;
 #endif
-    int mode, cur, sp, nq;
+    int mode, cur, sp, nq, top;
     bool has_result;
     RaySetupQ rq;
     float tmax, tlimit;
@@ -549,14 +553,11 @@ __device__ __forceinline__ void trav2_phase(const SceneDev& S, const WavePool& Q
     }
     tl.nq = 0;
     __syncwarp();
-    int nH = 0;
     for (int base = 0; base < total; base += 32) {
         const int it = base + lane;
-        bool to_hq = false;
-        uint32_t e = 0; float ha = 0.f, hb = 0.f;
         if (it < total) {
             VR_COUNT(++tl.n_quads;)
-            e = w.queue[it];
+            const uint32_t e = w.queue[it];
             const int owner = (int)(e >> 27);
             const uint32_t gi = e & 0x07ffffffu;
             const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
@@ -584,41 +585,18 @@ __device__ __forceinline__ void trav2_phase(const SceneDev& S, const WavePool& Q
                         }
                     }
                 } else {
-                    if (w.tau[owner] <= tau_cutoff_fixed()) {
-                        ha = fmaxf(0.0f, t0); hb = fminf(w.ray[6][owner], t1);
-                        to_hq = hb > ha;
+                    // exact clipped optical depth of the overlap (gmm.h:563-571, gaussian.h:208-231), by the lane that tested it:
+                    // component record and quadric coefficients are in registers (a second, compacted pass would reload both)
+                    const float ha = fmaxf(0.0f, t0), hb = fminf(w.ray[6][owner], t1);
+                    if (hb > ha && w.tau[owner] <= tau_cutoff_fixed()) {
+                        VR_COUNT(tl.n_erf += 2u;)
+                        const DepthConst c = depth_const(g, q);
+                        const float F1 = erff_ni(erf_arg(c, hb));
+                        const float F0 = erff_ni(erf_arg(c, ha));
+                        const float tau = __fmul_rn(c.K, __fsub_rn(F1, F0));
+                        atomicAdd((unsigned long long*)&w.tau[owner], (unsigned long long)__double2ll_rn((double)tau * kTauFixed));
                     }
                 }
-            }
-        }
-        if constexpr (KIND != RAY_SCATTER) {
-            const unsigned m = __ballot_sync(0xffffffffu, to_hq);
-            if (to_hq) {
-                const int pos = nH + __popc(m & ((1u << lane) - 1u));
-                w.hq_id[pos] = e; w.hq_a[pos] = ha; w.hq_b[pos] = hb;
-            }
-            nH += __popc(m);
-        }
-    }
-    if constexpr (KIND != RAY_SCATTER) {
-        __syncwarp();
-        // exact clipped optical depth of the overlaps (gmm.h:563-571, gaussian.h:208-231), 32 at a time
-        for (int base = 0; base < nH; base += 32) {
-            const int it = base + lane;
-            if (it < nH) {
-                VR_COUNT(tl.n_erf += 2u;)
-                const uint32_t e = w.hq_id[it];
-                const int owner = (int)(e >> 27);
-                const uint32_t gi = e & 0x07ffffffu;
-                const f3 o = mk3(w.ray[0][owner], w.ray[1][owner], w.ray[2][owner]);
-                const f3 d = mk3(w.ray[3][owner], w.ray[4][owner], w.ray[5][owner]);
-                const GaussRec g = load_gauss(S.gauss, gi);
-                const RayQuad q = ray_quad(g, o, d);
-                const DepthConst c = depth_const(g, q);
-                const float F1 = erff_ni(erf_arg(c, w.hq_b[it]));
-                const float F0 = erff_ni(erf_arg(c, w.hq_a[it]));
-                const float tau = __fmul_rn(c.K, __fsub_rn(F1, F0));
-                atomicAdd((unsigned long long*)&w.tau[owner], (unsigned long long)__double2ll_rn((double)tau * kTauFixed));
             }
         }
     }
@@ -642,7 +620,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
     }
     int stack[kStackDepth];
     Trav2Lane tl;
-    tl.mode = T2_FETCH; tl.cur = 0; tl.sp = 0; tl.nq = 0; tl.has_result = false; tl.tmax = 0.f; tl.tlimit = 0.f;
+    tl.mode = T2_FETCH; tl.cur = 0; tl.sp = 0; tl.nq = 0; tl.top = 0; tl.has_result = false; tl.tmax = 0.f; tl.tlimit = 0.f;
     VR_COUNT(tl.n_nodes = tl.n_quads = tl.n_erf = 0u;)
     bool exhausted = false;  // warp-uniform: the wave has no more rays to hand out
     while (true) {
@@ -672,13 +650,16 @@ __global__ void VR_TRAV_BOUNDS wave_trav2_kernel(const __grid_constant__ RenderA
                         if (h1 && c1 < 0) w.slot[tl.nq++][lane] = (uint32_t)(~c1) >> 3;   // leaf's quantised box is unhittable)
                         const bool i0 = h0 && c0 >= 0, i1 = h1 && c1 >= 0;
                         more = true;
+                        // the newest stack entry lives in a register (tl.top): a pop takes it and only PREFETCHES the entry
+                        // below from local memory, which is first needed one node visit later (the stacks hit L1 half the time)
                         if (i0 && i1) {
                             const bool swap = tn1 < tn0;
-                            stack[tl.sp++] = swap ? c0 : c1;
+                            if (tl.sp > 0) stack[tl.sp - 1] = tl.top;
+                            tl.top = swap ? c0 : c1; ++tl.sp;
                             tl.cur = swap ? c1 : c0;
                         } else if (i0) tl.cur = c0;
                         else if (i1) tl.cur = c1;
-                        else if (tl.sp > 0) tl.cur = stack[--tl.sp];
+                        else if (tl.sp > 0) { tl.cur = tl.top; if (--tl.sp > 0) tl.top = stack[tl.sp - 1]; }
                         else more = false;
                     }
                     if (!more) tl.mode = T2_WAIT;
@@ -1281,7 +1262,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         else wave_trav_kernel<RAY_SHADOW><<<pt.grid_h, kBlockThreads, 0, st>>>(a, q);
         if (prof) cudaEventRecord(pe[6], st);
         if (a.scene.lg_mask) {
-            if (t2) wave_trav2_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
+            if (t2 && a.trav_version != 3) wave_trav2_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
             else wave_trav_kernel<RAY_LIGHT><<<pt.grid_l, kBlockThreads, 0, st>>>(a, q);
         }
         if (prof) cudaEventRecord(pe[4], st);

@@ -238,10 +238,10 @@ def test_far_camera_rebuilds_the_hierarchy(ctx, ob, vr, scenegen):
     assert f >= 0.95 and within(img, ref, 1e-2).all()
     assert abs(float(img.mean()) - float(ref.mean())) <= 1e-4 * float(ref.mean())
     # rays whose origins are far out: overlap sets through the wavefront traversal, transmittance through vr_transmittance.
-    # 170 units from a component the FP32 quadric's accepted squared radius is 9 +- ~10 (its error grows with lam * R^2): what
-    # it accepts beyond the true 3-sigma ellipsoid is rounding noise, and the reference's own hierarchy culls part of that
-    # noise too.  What must hold: nothing the device reports is rejected by the quadric (brute force, no hierarchy), and every
-    # component whose ellipsoid the ray REALLY crosses (double precision) is reported.
+    # 170 units from a component the FP32 quadric's accepted squared radius is 9 +- ~10 (its error grows with lam * R^2): it
+    # accepts rays that miss the 3-sigma ellipsoid and rejects rays that cross it, and a hierarchy with tighter boxes (the
+    # reference's, the oracle's) culls part of that noise.  The sharp statement is against BRUTE FORCE: the device reports
+    # exactly the components the FP32 quadric accepts when it is asked about every one of them -- culling loses nothing.
     rs = np.random.RandomState(3)
     o = (rs.uniform(-1, 1, size=(5000, 3)) * 100).astype(np.float32); o[:, 1] += 1
     t = rs.uniform(-1, 1, size=(5000, 3)).astype(np.float32); t[:, 1] += 1
@@ -249,28 +249,15 @@ def test_far_camera_rebuilds_the_hierarchy(ctx, ob, vr, scenegen):
     d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
     cnt, idx = ctx.kat_gather(o, d, cap=16)
     bc, bi = ob.Gmm(scene).intersect_all(o, d, cap=64)
-    m64 = scene["mean"].astype(np.float64); c6 = scene["cov6"].astype(np.float64)
-    cov = np.empty((len(m64), 3, 3)); cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2] = c6.T
-    cov[:, 1, 0], cov[:, 2, 0], cov[:, 2, 1] = cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 2]
-    M = np.linalg.inv(cov)
-    lost_true = spurious = noise_only = 0
+    lost = extra = checked = 0
     for i in range(5000):
-        if bc[i] > 16 or cnt[i] > 16:
+        if bc[i] > 16:
+            assert cnt[i] > 16
             continue
         got = set(idx[i, :cnt[i]].tolist()); brute = set(bi[i, :bc[i]].tolist())
-        spurious += len(got - brute)
-        p = o[i].astype(np.float64)[None, :] - m64; dd = d[i].astype(np.float64)
-        Md = M @ dd
-        A = Md @ dd; B = 2.0 * np.einsum("ij,ij->i", p, Md); C0 = np.einsum("ij,ijk,ik->i", p, M, p)
-        q = C0 - B * B / (4.0 * A)                                   # squared Mahalanobis distance of the line from the centre
-        front = (-B + np.sqrt(np.maximum(B * B - 4.0 * A * (C0 - 9.0), 0.0))) / (2.0 * A) >= 0.0
-        truly = set(np.nonzero((q < 9.0 * (1.0 - 1e-3)) & front)[0].tolist())
-        lost_true += len(truly - got)
-        noise_only += len(brute - got)
-    print(f"origins up to 100 units out: reported but rejected by the quadric {spurious}, true overlaps lost {lost_true}, "
-          f"rounding-noise pseudo-overlaps not reported {noise_only} (of {int(bc.sum())} accepted)")
-    assert spurious == 0 and lost_true == 0
-    assert noise_only <= 1e-3 * bc.sum()
+        lost += len(brute - got); extra += len(got - brute); checked += len(brute)
+    print(f"origins up to 100 units out: {checked} accepted (ray, component) pairs, lost to culling {lost}, reported but not accepted {extra}")
+    assert lost == 0 and extra == 0 and checked > 20000
     tmax = np.full(5000, np.inf, np.float32)
     np.testing.assert_allclose(ctx.transmittance(o, d, tmax), ob.Gmm(scene).transmittance(o, d, tmax), rtol=1e-5, atol=1e-7)
 
