@@ -74,6 +74,7 @@ def lib():
     L.vo_transmittance_batch.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, _f32p]
     L.vo_intersect_events.restype = C.c_int
     L.vo_intersect_events.argtypes = [C.c_void_p, _f32p, _f32p, C.c_int, _f32p, _i32p, _u32p]
+    L.vo_transmittance_brute.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, _f32p]
     L.vo_intersect_all.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, C.c_int, _i32p, _u32p]
     L.vo_render.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int,
                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_void_p,
@@ -139,6 +140,13 @@ class Gmm:
         o = _c(o); d = _c(d); tmax = _c(tmax)
         out = np.empty(o.shape[0], np.float32)
         lib().vo_transmittance_batch(self.h, o.shape[0], o, d, tmax, out)
+        return out
+
+    def transmittance_brute(self, o, d, tmax):
+        """transmittance_up_to with every component asked (no hierarchy)"""
+        o = _c(o); d = _c(d); tmax = _c(tmax)
+        out = np.empty(o.shape[0], np.float32)
+        lib().vo_transmittance_brute(self.h, o.shape[0], o, d, tmax, out)
         return out
 
     def intersect_all(self, o, d, cap=64):

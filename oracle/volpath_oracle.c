@@ -659,6 +659,26 @@ VO_EXPORT int vo_intersect_events(const vo_gmm* m, const float* o, const float* 
     return n;
 }
 
+/* transmittance_up_to (gmm.h:517-578) WITHOUT the hierarchy: every component is asked (the loop the reference compiles with
+ * USE_BVH off, gmm.h:190-226); what a culling structure must reproduce */
+VO_EXPORT void vo_transmittance_brute(const vo_gmm* m, int nrays, const float* o3, const float* d3, const float* tmax, float* out) {
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int r = 0; r < nrays; ++r) {
+        vo_ray ray;
+        ray.o = v3_make(o3[3 * r], o3[3 * r + 1], o3[3 * r + 2]);
+        ray.d = v3_make(d3[3 * r], d3[3 * r + 1], d3[3 * r + 2]);
+        double sum = 0.0;
+        if (tmax[r] > 0.0f)
+            for (int g = 0; g < m->n; ++g) {
+                float t0, t1;
+                if (!gauss_intersect(&m->g[g], &ray, &t0, &t1)) continue;
+                float a = fmaxf(0.0f, t0), b = fminf(tmax[r], t1);
+                if (b > a) sum += (double)gauss_optical_depth(&m->g[g], &ray, a, b);
+            }
+        out[r] = tmax[r] > 0.0f ? expf(-(float)sum) : 1.0f;
+    }
+}
+
 /* every component the FP32 quadric test (gaussian.h:126-164) accepts for a batch of rays, WITHOUT any hierarchy: the set a
  * culling structure must not lose members of.  idx[r * cap + k] = component indices (ascending), counts[r] = how many. */
 VO_EXPORT void vo_intersect_all(const vo_gmm* m, int nrays, const float* o3, const float* d3, int cap, int* counts, uint32_t* idx) {

@@ -294,9 +294,18 @@ def test_c3_transmittance_200k_components(ctx, ob, vr, scenegen):
     d = t - o
     d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
     tmax = np.where(rs.rand(n) < 0.5, np.inf, rs.uniform(0, 0.5, n)).astype(np.float32)
-    ref = ob.Gmm(scene).transmittance(o, d, tmax)
+    gm = ob.Gmm(scene)
+    ref = gm.transmittance(o, d, tmax)
     got = ctx.transmittance(o, d, tmax)
-    np.testing.assert_allclose(got, ref, rtol=1e-5, atol=1e-7)
+    ok = np.abs(got - ref) <= 1e-7 + 1e-5 * np.abs(ref)
+    print(f"C3 transmittance: {int((~ok).sum())} of {n} rays outside 1e-5 of the oracle's hierarchy walk")
+    assert ok.mean() >= 0.9999
+    # a ray that grazes a 3-sigma ellipsoid inside the rounding noise of the FP32 quadric is accepted or not depending on which
+    # boxes let the quadric see it (the oracle's hierarchy and ours differ there, and so does the reference's): the arbiter is
+    # the walk over EVERY component (gmm.h:190-226).  Every disagreeing ray and 1500 random ones must match it.
+    pick = np.unique(np.concatenate([np.nonzero(~ok)[0], rs.choice(n, 1500, replace=False)]))
+    brute = gm.transmittance_brute(o[pick], d[pick], tmax[pick])
+    np.testing.assert_allclose(got[pick], brute, rtol=1e-5, atol=1e-7)
     assert ((ref > 0.01) & (ref < 0.99)).mean() > 0.05
 
 
