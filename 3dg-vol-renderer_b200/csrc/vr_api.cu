@@ -23,6 +23,8 @@ vr::SceneDev vr_context::scene_dev() const {
     for (int k = 0; k < 3; ++k) { S.qorg[k] = qorg[k]; S.qcell[k] = qcell[k]; }
     S.lg_start = lg_start.as<uint32_t>(); S.lg_gi = lg_gi.as<uint32_t>(); S.lg_dmin = lg_dmin.as<float>();
     S.lg_res = lg_res; S.lg_mask = lg_valid ? lg_mask : 0u;
+    S.cg_start = cg_start.as<uint32_t>(); S.cg_gi = cg_gi.as<uint32_t>(); S.cg_dmin = cg_dmin.as<float>();
+    S.cg_res = 0;   // switched on per render (vr_render.cu) when the grid is valid for this camera
     S.orig = perm.as<uint32_t>();
     S.n = n;
     S.nl = nl;
@@ -109,7 +111,7 @@ void vr_destroy(vr_context* ctx) {
     ctx->comm_scratch.release();
     for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
                       &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->lam, &ctx->qnodes, &ctx->lg_start, &ctx->lg_gi,
-                      &ctx->lg_dmin, &ctx->lg_scratch, &ctx->spheres, &ctx->lpos, &ctx->lint,
+                      &ctx->lg_dmin, &ctx->lg_scratch, &ctx->cg_start, &ctx->cg_gi, &ctx->cg_dmin, &ctx->spheres, &ctx->lpos, &ctx->lint,
                       &ctx->image, &ctx->sampleL, &ctx->counters, &ctx->stats, &ctx->overflow_list, &ctx->arena,
                       &ctx->record_bits, &ctx->scratch, &ctx->wavepool})
         b->release();
@@ -134,12 +136,15 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "max_pass_samples")) { ctx->max_pass_samples = std::max(1.0, value); return VR_OK; }
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
+    if (!strcmp(name, "post_split")) { ctx->post_split = (int)value != 0; return VR_OK; }
     if (!strcmp(name, "trav")) { const int v = (int)value; ctx->trav_version = (v == 1 || v == 3) ? v : 2; return VR_OK; }   // 3: trav2 except the light-grid walk
     if (!strcmp(name, "hierarchy")) { ctx->hierarchy_builder = (int)value != 0; return VR_OK; }   // 0 device LBVH, 1 host binned SAH; next vr_set_gmm*
     if (!strcmp(name, "box_kappa")) { ctx->box_kappa = std::max(0.0, value); return VR_OK; }   // takes effect at the next vr_set_gmm*
     if (!strcmp(name, "light_grid")) { vr::cancel_light_grid_job(ctx); ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "light_grid_min_samples")) { ctx->light_grid_min_samples = value; return VR_OK; }
-    if (!strcmp(name, "light_grid_res")) { vr::cancel_light_grid_job(ctx); ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
+    if (!strcmp(name, "camera_grid")) { ctx->use_camera_grid = (int)value != 0; return VR_OK; }
+    if (!strcmp(name, "camera_grid_min_samples")) { ctx->camera_grid_min_samples = value; return VR_OK; }
+    if (!strcmp(name, "light_grid_res")) { ctx->cg_valid = false; vr::cancel_light_grid_job(ctx); ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "wave_parts")) { ctx->wave_parts = std::max(1, std::min(kMaxWaveParts, (int)value)); ctx->wavepool.release(); return VR_OK; }
     if (!strcmp(name, "wave_slots")) { ctx->wave_slots = std::max(0, (int)value); ctx->wavepool.release(); return VR_OK; }
     return fail(ctx, VR_ERR_INVALID_ARGUMENT, std::string("unknown option ") + name);
@@ -254,6 +259,7 @@ int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
     ctx->has_gmm = false;
     ctx->rec_valid = false;
     ctx->lg_valid = false;
+    ctx->cg_valid = false;
     ctx->h_box_lo.clear(); ctx->h_box_hi.clear(); ctx->h_leaf_of_orig.clear();
     const size_t m = (size_t)std::max(n, 1);
     VR_CUDA(ctx->gauss_orig.ensure(m * 48)); VR_CUDA(ctx->gauss_leaf.ensure(m * 48));
@@ -340,6 +346,18 @@ int fetch_host_boxes(vr_context* ctx) {
     VR_CUDA(cudaMemcpyAsync(ctx->h_box_hi.data(), ctx->box_hi.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaMemcpyAsync(ctx->h_leaf_of_orig.data(), ctx->leaf_of_orig.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     VR_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VR_OK;
+}
+
+// candidate grid of the camera rays: (re)built when the mixture or the pinhole changed; device builder only
+int ensure_camera_grid(vr_context* ctx) {
+    if (ctx->cam.kind != VR_CAMERA_PINHOLE || ctx->hierarchy_builder != 0 || ctx->n <= 0) { ctx->cg_ok = false; return VR_OK; }
+    if (ctx->cg_valid && memcmp(ctx->cg_pinhole, ctx->cam.pinhole, sizeof(float) * 3) == 0) return VR_OK;
+    NvtxRange range("vr.camera_grid");
+    int rc = build_camera_grid_device(ctx);
+    if (rc) return rc;
+    memcpy(ctx->cg_pinhole, ctx->cam.pinhole, sizeof(float) * 3);
+    ctx->cg_valid = true;
     return VR_OK;
 }
 

@@ -64,6 +64,12 @@ struct vr_context {
     std::vector<float> h_box_lo, h_box_hi, h_lpos;
     std::vector<uint32_t> h_leaf_of_orig;
     vr::DevBuf lg_start, lg_gi, lg_dmin, lg_scratch;
+    // direction grid around the pinhole of the camera: candidate lists of the camera rays (vr_lightgrid_dev.cu, wave_regen_kernel)
+    vr::DevBuf cg_start, cg_gi, cg_dmin;
+    bool cg_valid = false, cg_ok = false;          // built for the current mixture + camera / usable (pinhole not inside a component)
+    float cg_pinhole[3] = {0.f, 0.f, 0.f};
+    int use_camera_grid = 1;
+    double camera_grid_min_samples = 2.0e6;
     bool lg_valid = false;
     int lg_res = 256;
     uint32_t lg_mask = 0;
@@ -99,6 +105,7 @@ struct vr_context {
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
     int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
     int wave_slots = 0;                            // 0 = 32768 per SM (sweeps in profiles/r01_tuning.md, r01_v11/)
+    int post_split = 0;                            // wave_post_a_kernel per overlap-count class (vr_wave.cu)
     int trav_version = 2;                          // traversal kernels of the wavefront engine (vr_wave.cu): 2 wave_trav2_kernel, 1 wave_trav_kernel
     int wave_parts = 2;                            // independent parts (own pool + stream) a big pass is cut into
     cudaStream_t wave_streams[vr::kMaxWaveParts] = {nullptr, nullptr, nullptr, nullptr};
@@ -121,6 +128,8 @@ int render_device_impl(vr_context* c, const vr_render_params* p, vr_render_stats
 int set_gmm_from_device(vr_context* c, int n, const float* reach_RX = nullptr);   // reach_RX: minimum BoxReach {R, X} to build for
 int build_hierarchy_device(vr_context* c, int n, const float* reach_RX);          // vr_lbvh.cu
 int build_light_grids_device(vr_context* c);      // vr_lightgrid_dev.cu
+int build_camera_grid_device(vr_context* c);      // vr_lightgrid_dev.cu
+int ensure_camera_grid(vr_context* c);            // vr_api.cu
 int fetch_host_boxes(vr_context* c);               // vr_api.cu: inflated boxes + leaf order on the host (light-grid builder)
 int ensure_reach(vr_context* c, float R, float X);   // rebuilds the hierarchy when it was inflated for a smaller reach
 int ensure_camera_reach(vr_context* c);              // ... for the camera currently set

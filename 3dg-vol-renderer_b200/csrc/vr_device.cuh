@@ -16,6 +16,11 @@ struct SceneDev {
     const float* lg_dmin;
     int lg_res;
     uint32_t lg_mask;       // bit l: light l has a grid
+    // direction grid around the camera's pinhole (same layout, one table): candidates of the camera rays; cg_res = 0: none
+    const uint32_t* cg_start;
+    const uint32_t* cg_gi;
+    const float* cg_dmin;
+    int cg_res;
     const uint32_t* orig;   // leaf order -> original index
     int n;
     int nl;

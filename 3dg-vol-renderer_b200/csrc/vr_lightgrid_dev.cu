@@ -138,15 +138,15 @@ __global__ void lg_sort_kernel(size_t cells, const uint32_t* __restrict__ start,
     }
 }
 
-// Fills ctx->lg_start / lg_gi / lg_dmin / lg_mask from the device-resident boxes (ctx->box_lo/hi inflated, original order) and
-// ctx->leaf_of_orig.  Two synchronisations: the per-light sizes, and none after.
-int build_light_grids_device(vr_context* ctx) {
-    const int n = ctx->n, nl = ctx->nl, res = ctx->lg_res;
+// Direction grids around `nl` points (pos3) from the device-resident boxes (ctx->box_lo/hi inflated, original order) and
+// ctx->leaf_of_orig, into start / gi / dmin; *mask_out bit l: point l has a grid.  One synchronisation: the per-point sizes.
+static int build_point_grids(vr_context* ctx, int nl, const float* pos3, DevBuf& start_buf, DevBuf& gi_buf, DevBuf& dmin_buf, uint32_t* mask_out) {
+    const int n = ctx->n, res = ctx->lg_res;
     cudaStream_t s = ctx->stream;
     const size_t cells = (size_t)6 * res * res;
     const int ng = std::min(nl, 32);
-    ctx->lg_mask = 0;
-    VR_CUDA(ctx->lg_start.ensure((size_t)nl * (cells + 1) * 4));
+    *mask_out = 0;
+    VR_CUDA(start_buf.ensure((size_t)nl * (cells + 1) * 4));
     // scratch: rects n*6, nrect n, dmin n  per light | count / cursor cells+1 | info
     const size_t per_light = (size_t)n * (6 * sizeof(LgRect) + 4 + 4);
     VR_CUDA(ctx->lg_scratch.ensure((size_t)ng * per_light + (cells + 1) * 4 + 64 * sizeof(LgLightInfo) + 256));
@@ -164,7 +164,7 @@ int build_light_grids_device(vr_context* ctx) {
     for (int l = 0; l < ng; ++l) {
         LgLight L;
         double mabs = maxabs;
-        for (int k = 0; k < 3; ++k) { L.pos[k] = (double)ctx->h_lpos[(size_t)3 * l + k]; mabs = std::max(mabs, std::fabs(L.pos[k])); }
+        for (int k = 0; k < 3; ++k) { L.pos[k] = (double)pos3[(size_t)3 * l + k]; mabs = std::max(mabs, std::fabs(L.pos[k])); }
         const double pad = std::max(1e-4, 64.0 * 5.9604644775390625e-08 * (mabs + 1.0));
         lg_rects_kernel<<<nb, 128, 0, s>>>(n, ctx->box_lo.as<float>(), ctx->box_hi.as<float>(), L, pad, 0.05, res, rects_of(l), nrect_of(l), dmin_of(l), info + l);
     }
@@ -179,15 +179,15 @@ int build_light_grids_device(vr_context* ctx) {
         if (ok[(size_t)l]) total += (size_t)hinfo[(size_t)l].area;
     }
     if (total >= 0xfffffff0ull) { for (auto& o : ok) o = 0; total = 0; }
-    VR_CUDA(ctx->lg_gi.ensure(std::max<size_t>(total, 1) * 4));
-    VR_CUDA(ctx->lg_dmin.ensure(std::max<size_t>(total, 1) * 4));
+    VR_CUDA(gi_buf.ensure(std::max<size_t>(total, 1) * 4));
+    VR_CUDA(dmin_buf.ensure(std::max<size_t>(total, 1) * 4));
     size_t tmp_bytes = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, count, count, (int)(cells + 1), s);
     VR_CUDA(ctx->lbvh_tmp.ensure(std::max<size_t>(tmp_bytes, 16)));
     uint32_t entries_before = 0;
     const unsigned grid_cells = (unsigned)((cells + 1 + 255) / 256);
     for (int l = 0; l < nl; ++l) {
-        uint32_t* start = ctx->lg_start.as<uint32_t>() + (size_t)l * (cells + 1);
+        uint32_t* start = start_buf.as<uint32_t>() + (size_t)l * (cells + 1);
         if (!ok[(size_t)l]) {   // a light without a grid: every cell is empty
             lg_shift_kernel<<<grid_cells, 256, 0, s>>>(cells + 1, start, entries_before, 1);
             continue;
@@ -200,13 +200,28 @@ int build_light_grids_device(vr_context* ctx) {
         if (entries_before) lg_shift_kernel<<<grid_cells, 256, 0, s>>>(cells + 1, start, entries_before, 0);
         VR_CUDA(cudaMemsetAsync(count, 0, (cells + 1) * 4, s));   // reused as the fill cursors
         lg_fill_kernel<<<nb, 128, 0, s>>>(n, res, rects_of(l), nrect_of(l), dmin_of(l), ctx->leaf_of_orig.as<uint32_t>(), start, count,
-                                          ctx->lg_gi.as<uint32_t>(), ctx->lg_dmin.as<float>());
-        lg_sort_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, s>>>(cells, start, ctx->lg_gi.as<uint32_t>(), ctx->lg_dmin.as<float>());
+                                          gi_buf.as<uint32_t>(), dmin_buf.as<float>());
+        lg_sort_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, s>>>(cells, start, gi_buf.as<uint32_t>(), dmin_buf.as<float>());
         entries_before += (uint32_t)hinfo[(size_t)l].area;
-        ctx->lg_mask |= 1u << l;
+        *mask_out |= 1u << l;
     }
     VR_CUDA(cudaGetLastError());
     return VR_OK;
+}
+
+// per-light grids: ctx->lg_start / lg_gi / lg_dmin / lg_mask
+int build_light_grids_device(vr_context* ctx) {
+    return build_point_grids(ctx, ctx->nl, ctx->h_lpos.data(), ctx->lg_start, ctx->lg_gi, ctx->lg_dmin, &ctx->lg_mask);
+}
+
+// The same grid around the PINHOLE of a pinhole camera (camera.h:38-53): every camera ray passes through it, so the
+// components a camera ray can overlap beyond the pinhole are those of the cell of its direction, nearest first, and those it
+// can overlap between film plane and pinhole are in the cell of the opposite direction (vr_wave.cu wave_regen_kernel<true>).
+int build_camera_grid_device(vr_context* ctx) {
+    uint32_t mask = 0;
+    int rc = build_point_grids(ctx, 1, ctx->cam.pinhole, ctx->cg_start, ctx->cg_gi, ctx->cg_dmin, &mask);
+    ctx->cg_ok = rc == VR_OK && mask == 1u;
+    return rc;
 }
 
 }  // namespace vr

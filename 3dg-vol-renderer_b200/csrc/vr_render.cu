@@ -74,15 +74,21 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     const bool use_grids = ctx->engine == 0 && ctx->use_light_grid && (double)render_samples >= ctx->light_grid_min_samples;
     ctx->lg_speculate = use_grids;   // the next vr_set_gmm* builds the grids next to the hierarchy
     if (use_grids) { rc = ensure_light_grids(ctx); if (rc) return rc; }
+    // camera rays of a pinhole camera take their candidates from a direction grid around the pinhole (wave_regen_cam_kernel)
+    const bool want_cam_grid = ctx->engine == 0 && ctx->use_camera_grid && ctx->trav_version != 1 && ctx->cam.kind == VR_CAMERA_PINHOLE &&
+                               (double)render_samples >= ctx->camera_grid_min_samples;
+    if (want_cam_grid) { rc = ensure_camera_grid(ctx); if (rc) return rc; }
     RenderArgs A{};
     A.scene = ctx->scene_dev();
     if (!use_grids) A.scene.lg_mask = 0;
+    if (want_cam_grid && ctx->cg_valid && ctx->cg_ok) A.scene.cg_res = ctx->lg_res;
     A.cam = ctx->cam;
     A.W = W; A.H = H; A.spp = p->spp;
     A.nsq = (int)std::sqrt((double)p->spp);  // integrator.h:562
     if (A.nsq < 1) A.nsq = 1;
     A.integrator = p->integrator;
     A.trav_version = ctx->trav_version;
+    A.post_split = ctx->post_split;
     A.solver = p->solver;
     A.min_bounces = p->min_bounces;
     A.x0 = p->x0; A.y0 = p->y0; A.win_w = p->x1 - p->x0;

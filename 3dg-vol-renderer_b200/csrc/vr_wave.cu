@@ -820,6 +820,118 @@ __global__ void __launch_bounds__(256) wave_regen_kernel(const __grid_constant__
     }
 }
 
+// wave_regen_cam: wave_regen for a pinhole camera whose pinhole has a direction grid (vr_lightgrid_dev.cu
+// build_camera_grid_device) -- the per-tile culling of the camera rays.  Every camera ray passes through the pinhole P
+// (camera.h:45-53: origin on the film plane, direction towards P), so the components it can overlap beyond P are those of
+// the cube-map cell of its direction, NEAREST FIRST, and those between film plane and P are in the cell of the opposite
+// direction.  The lane that generates a camera ray therefore gathers its overlaps right here from that short sorted list
+// (integrator.h:593, gmm.h:457-515; the quadric test and the pruning bound are wave_trav2's) instead of sending the ray
+// through the hierarchy: the 32 lanes of a warp hold consecutive samples of ONE pixel, so they read the same list (one
+// broadcast load per entry) and take the same branches.  A ray that overlaps nothing (background) ends its path on the
+// spot and the lane takes the next sample.  Slots leave classified by overlap count, straight to wave_post_a.
+// Lists average ~4 entries of 8 bytes: staging them with cp.async.bulk (16-byte granules, an mbarrier round trip) cannot
+// pay; the broadcast loads hit L1.
+__global__ void __launch_bounds__(256) wave_regen_cam_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
+    const SceneDev& S = A.scene;
+    const unsigned int nC = Q.cnt[WC_NC];
+    if (blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NB] = 0;  // consumed by wave_post_b, the previous kernel of the chain
+    WaveCounters cn = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    const int lane = threadIdx.x & 31;
+    const unsigned int stride = gridDim.x * blockDim.x;
+    const unsigned int rounds = (nC + stride - 1) / stride;
+    const f3 P = mk3(A.cam.pinhole[0], A.cam.pinhole[1], A.cam.pinhole[2]);
+    for (unsigned int r = 0; r < rounds; ++r) {
+        const unsigned int i = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const unsigned int p = i < nC ? Q.listC[i] : 0u;
+        bool need = i < nC;      // this lane's slot still needs a path
+        int K_done = 0;          // overlaps of the path the slot got (0: none -- no samples left)
+        while (__any_sync(0xffffffffu, need)) {
+            // sample ids: one aggregated atomic per warp
+            const unsigned m = __ballot_sync(0xffffffffu, need);
+            unsigned int base = 0;
+            if (lane == __ffs(m) - 1) base = atomicAdd(&Q.cnt[WC_NEXT_SAMPLE], (unsigned int)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            const unsigned int idx = base + (unsigned int)__popc(m & ((1u << lane) - 1u));
+            if (need && idx >= A.work_count) need = false;
+            if (need) {
+                int x, y, si;
+                const unsigned int work = wave_global_work(A, idx);
+                lane_xy(A, work, &x, &y, &si);
+                Pcg rng; rng.seed(derive_path_seed(x, y, si), 1);
+                const int n = A.nsq;
+                const int sx = si % n, sy = si / n;
+                const float u = __fdiv_rn(__fadd_rn((float)x, __fdiv_rn(__fadd_rn((float)sx, rng.uniform()), (float)n)), (float)A.W);
+                const float v = __fdiv_rn(__fadd_rn((float)y, __fdiv_rn(__fadd_rn((float)sy, rng.uniform()), (float)n)), (float)A.H);
+                const RayOD ray = camera_ray(A.cam, u, v);
+                ++cn.scatter;
+                // ---- gather from the pinhole's grid
+                Pcg peek; peek.state = rng.state; peek.inc = 3;
+                const float target = -logf(__fsub_rn(1.0f, peek.uniform()));
+                const f3 o = ray.o, d = ray.d;
+                const float tP = (P.x - o.x) * d.x + (P.y - o.y) * d.y + (P.z - o.z) * d.z;   // the ray passes the pinhole at o + tP d
+                const size_t cells = (size_t)6 * S.cg_res * S.cg_res;
+                int K = 0;
+                float tb = CUDART_INF_F;
+#pragma unroll 1
+                for (int side = 0; side < 2; ++side) {   // 0: between film plane and pinhole (opposite direction), 1: beyond the pinhole
+                    const f3 vdir = side == 0 ? mk3(-d.x, -d.y, -d.z) : d;
+                    const uint32_t cell = light_grid_cell_dev(vdir, S.cg_res);
+                    (void)cells;
+                    uint32_t pos = __ldg(S.cg_start + cell);
+                    const uint32_t end = __ldg(S.cg_start + cell + 1);
+                    for (; pos < end; ++pos) {
+                        const float dm = __ldg(S.cg_dmin + pos);
+                        // entries are sorted by their box's distance from the pinhole: behind it nothing farther than the film
+                        // plane matters, beyond it nothing that starts behind the pruning bound (slack >> rounding of tP, dm)
+                        if (side == 0 ? (dm > fmaf(tP, 1.00001f, 1e-5f)) : (tP + dm > fmaf(tb, 1.00001f, 1e-5f))) break;
+                        const uint32_t gi = __ldg(S.cg_gi + pos);
+                        const GaussRec g = load_gauss(S.gauss, gi);
+                        const RayQuad q = ray_quad(g, o, d);
+                        float t0, t1;
+                        if (!quad_intersect(q, &t0, &t1) || t0 > tb) continue;
+                        if (K < kWaveCap) pool_store_hit(Q, p, K, t0, t1, gi);
+                        ++K;
+                        if (t1 < tb) {   // pruning only: conservative estimate of this component's full optical depth (wave_trav2)
+                            const float dn = g.density * g.norm;
+                            const float inv4A = __fdividef(1.0f, 4.0f * q.A);
+                            const float Kc = dn * sqrtf(6.2831853f * inv4A) * __expf(-0.5f * (q.C0 - q.B * q.B * inv4A));
+                            const float iden = rsqrtf(8.0f * q.A);
+                            const float full = Kc * (erff_ni((q.B + 2.0f * q.A * t1) * iden) - erff_ni((q.B + 2.0f * q.A * t0) * iden));
+                            if (full > 1.5f * target) tb = t1;
+                        }
+                    }
+                }
+                if (K == 0) {
+                    // nothing overlapped: the path ends with the environment (integrator.h:594-597) and the slot takes the next sample
+                    A.sampleL[work] = make_float4(__fadd_rn(0.0f, __fmul_rn(1.0f, S.env[0])), __fadd_rn(0.0f, __fmul_rn(1.0f, S.env[1])),
+                                                  __fadd_rn(0.0f, __fmul_rn(1.0f, S.env[2])), 0.0f);
+                } else {
+                    Q.ray[kSlotF4 * (size_t)p] = make_float4(o.x, o.y, o.z, target);
+                    Q.ray[kSlotF4 * (size_t)p + 1] = make_float4(d.x, d.y, d.z, __int_as_float(RAY_SCATTER));
+                    Q.ps01[kSlotF4 * (size_t)p] = make_float4(0.f, 0.f, 0.f, 1.0f);
+                    reinterpret_cast<uint4*>(Q.ps01)[kSlotF4 * (size_t)p + 1] = make_uint4((unsigned int)rng.state, (unsigned int)(rng.state >> 32), work, 0u);
+                    reinterpret_cast<int*>(Q.hit01 + kSlotF4 * (size_t)p)[0] = K;
+                    K_done = K;
+                    need = false;
+                }
+            }
+        }
+        const int cls = post_class(K_done);
+#pragma unroll
+        for (int c = 0; c < kPostClasses; ++c)
+            wave_append(Q.listA + (size_t)c * Q.P, &Q.cnt[WC_NA + c], K_done > 0 && cls == c, p);
+    }
+    wave_flush_counters(A, cn);
+    // listC is refilled by the next kernels (escaping rays in wave_trav, finished paths in the post kernels), so its counter is
+    // cleared here by the LAST block of this kernel to finish (every block has read nC by then)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned int t = atomicAdd(&Q.cnt[WC_TICKET], 1u);
+        if (t == gridDim.x - 1) { Q.cnt[WC_NC] = 0; Q.cnt[WC_TICKET] = 0; __threadfence(); }
+    }
+}
+
 // wave_post_a: integrator.h:593-678.  Slots arrive binned by overlap count (post_class).
 //   wave_post_a_kernel<1>      class 0 only (one overlap, the commonest case in sparse mixtures): a register-only
 //       path that performs the same operations in the same order as the general walk does for K = 1.  Small code,
@@ -870,18 +982,23 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
     return (light >= 0 && light < 32 && ((S.lg_mask >> light) & 1u)) ? DEST_TRAV_LIGHT : DEST_TRAV;
 }
 
-template <int MODE>   // 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots, 3 general, solves in place
+// MODE: 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots, 3 general, solves in place.
+// CLS (general modes only): -1 = classes 1..4 in one launch with a 16-entry overlap store; 1..4 = that class alone with a store
+// sized for it (2 / 4 / 8 / 16 entries: the store lives in local memory, 40 bytes per entry and thread)
+template <int MODE, int CLS = -1>
 __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
     constexpr bool FAST = MODE == 1;
-    constexpr int kFirst = MODE == 1 ? 0 : (MODE == 2 ? kPostClasses : 1);              // classes [kFirst, kLast)
-    constexpr int kLast = MODE == 1 ? 1 : (MODE == 2 ? kPostClasses + 1 : kPostClasses);
+    constexpr bool kOneClass = (MODE == 0 || MODE == 3) && CLS > 0;
+    constexpr int kFirst = MODE == 1 ? 0 : (MODE == 2 ? kPostClasses : (kOneClass ? CLS : 1));              // classes [kFirst, kLast)
+    constexpr int kLast = MODE == 1 ? 1 : (MODE == 2 ? kPostClasses + 1 : (kOneClass ? CLS + 1 : kPostClasses));
+    constexpr int kStoreCap = !kOneClass ? kWaveCap : (CLS == 1 ? 2 : (CLS == 2 ? 4 : (CLS == 3 ? 8 : kWaveCap)));
     unsigned int nA[kPostClasses + 1], base[kPostClasses + 2];
     base[kFirst] = 0;
 #pragma unroll
     for (int c = kFirst; c < kLast; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
     const unsigned int total = base[kLast];
-    if ((MODE == 0 || MODE == 3) && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;
+    if ((MODE == 0 || MODE == 3) && (!kOneClass || CLS == 1) && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;
     if (MODE != 1 && blockIdx.x == 0 && threadIdx.x == 0) {   // the host decides from these whether deferring pays (run_wavefront_pass)
         unsigned int sum = 0;
 #pragma unroll
@@ -964,7 +1081,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 dest = DEST_REGEN;
             } else {
                 cn.hits += (unsigned int)K;
-                LocalStore<kWaveCap> st;
+                LocalStore<kStoreCap> st;
 #pragma unroll 1
                 for (int s = 0; s < K; ++s) {  // exact depth constants (gaussian.h:208-231) of the gathered overlaps
                     float ht0, ht1; uint32_t gi;
@@ -1173,6 +1290,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         for (auto& row : occ) for (int& v : row) v = std::max(v, 1);
     });
     const bool t2 = a_all.trav_version != 1;
+    const bool post_split = a_all.post_split != 0;
     const int bps_s = occ[t2 ? 1 : 0][0], bps_h = occ[t2 ? 1 : 0][1], bps_l = occ[t2 ? 1 : 0][2];
     const char* prof_env = getenv("VR_WAVE_PROFILE");
     const bool prof = prof_env && prof_env[0] == '1';
@@ -1238,13 +1356,23 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     auto enqueue_iteration = [&](Part& pt) {
         const RenderArgs& a = pt.a; const WavePool& q = pt.q; cudaStream_t st = pt.st;
         if (prof) cudaEventRecord(pe[0], st);
-        wave_regen_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
+        if (a.scene.cg_res) wave_regen_cam_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);   // camera rays gathered from the pinhole's grid
+        else wave_regen_kernel<<<pt.grid_post256, 256, 0, st>>>(a, q);
         if (prof) cudaEventRecord(pe[1], st);
         if (t2) wave_trav2_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
         else wave_trav_kernel<RAY_SCATTER><<<pt.grid_s, kBlockThreads, 0, st>>>(a, q);
         if (prof) cudaEventRecord(pe[2], st);
         wave_post_a_kernel<1><<<pt.grid_post, 128, 0, st>>>(a, q);
-        if (pt.defer) {
+        if (post_split) {   // one launch per overlap-count class, each with an overlap store of its size
+            if (pt.defer) {
+                wave_post_a_kernel<0, 1><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<0, 2><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<0, 3><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<0, 4><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
+            } else {
+                wave_post_a_kernel<3, 1><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<3, 2><<<pt.grid_post, 128, 0, st>>>(a, q);
+                wave_post_a_kernel<3, 3><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<3, 4><<<pt.grid_post, 128, 0, st>>>(a, q);
+            }
+        } else if (pt.defer) {
             wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
             wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
         } else {
@@ -1283,7 +1411,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             Part& pt = part[i];
             if (pt.done) continue;
             any = true;
-            const unsigned int per_iter = 6u + (pt.defer ? 1u : 0u) + (pt.a.scene.lg_mask ? 1u : 0u);
+            const unsigned int per_iter = 6u + (pt.defer ? 1u : 0u) + (pt.a.scene.lg_mask ? 1u : 0u) + (post_split ? 3u : 0u);
             if (use_graph) {
                 WaveGraphCache::Entry& en = graphs->e[i][pt.defer ? 1 : 0];
                 WaveGraphKey key;

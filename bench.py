@@ -297,6 +297,8 @@ def main():
     ap.add_argument("--wave-slots", type=int, default=0)
     ap.add_argument("--wave-parts", type=int, default=0)
     ap.add_argument("--trav", type=int, default=0, help="traversal kernels of the wavefront engine: 2 (default) wave_trav2_kernel, 1 wave_trav_kernel")
+    ap.add_argument("--camera-grid", type=int, default=-1, help="camera rays gathered from the pinhole's direction grid (default 1)")
+    ap.add_argument("--post-split", type=int, default=-1, help="wave_post_a: 1 one launch per overlap-count class, 0 one launch for all")
     ap.add_argument("--hierarchy", type=int, default=-1, help="0: hierarchy and light grids built on the device (default), 1: host binned-SAH builder")
     ap.add_argument("--box-kappa", type=float, default=-1.0, help="slack of the culling boxes (vr_bvh.h inflate_boxes), default = the library's")
     ap.add_argument("--light-grid-res", type=int, default=0, help="cells per cube-map face side of the per-light grids (default 256)")
@@ -358,6 +360,10 @@ def main():
         ctx.set_option("hierarchy", a.hierarchy)
     if a.trav:
         ctx.set_option("trav", a.trav)
+    if a.post_split >= 0:
+        ctx.set_option("post_split", a.post_split)
+    if a.camera_grid >= 0:
+        ctx.set_option("camera_grid", a.camera_grid)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
     ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cam); ctx.set_gmm(scene)
     integ = vr.INTEGRATOR_SS if cfg["integrator"] == "ss" else vr.INTEGRATOR_MS

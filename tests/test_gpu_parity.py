@@ -2,9 +2,11 @@
 (a) golden vectors emitted by the unmodified reference and (b) the pinned C oracle on seeded inputs.
 
 Tolerances (BASELINE.json north_star): per-pixel radiance 1e-4 relative with identical sample
-streams, analytic transmittance 1e-5; integer work (PCG stream, recorded sets) bit-exact.  A small
-fraction of pixels may differ through single-sample decision flips: the bound is on
-the fraction of pixels inside the tolerance, stated in each test."""
+streams, analytic transmittance 1e-5; integer work (PCG stream, recorded sets) bit-exact.  A few pixels in
+a thousand hold a sample whose value an FP32 implementation with another libm legitimately moves by more
+than 1e-4 (the medium is optically thick: see tests/test_gpu_parity_r2.py, where every such sample is
+attributed): every image test states its bar on the fraction of pixels inside the tolerance -- 99.5 %,
+measured 99.6-100 % -- bounds the worst pixel, and prints what was achieved."""
 from __future__ import annotations
 
 import ctypes as C
@@ -58,6 +60,17 @@ def setup(ctx, ob, vr, scenegen, scene_name, cam_name, scene=None):
 
 def frac_within(a, b, rtol, atol=1e-6):
     return float((np.abs(a - b) <= atol + rtol * np.abs(b)).all(axis=-1).mean())
+
+
+def check_pixels(what, img, ref, rtol, bar, worst=1e-2, atol=1e-6):
+    """fraction of pixels within rtol (printed: pytest -s shows what was achieved, not only that the bar held) and a bound on
+    the worst pixel: an image with a few badly wrong pixels does not pass.  Which samples may differ, and why, is established
+    sample by sample in tests/test_gpu_parity_r2.py::test_per_sample_attribution."""
+    f = frac_within(img, ref, rtol, atol)
+    w = float((np.abs(img - ref) / np.maximum(np.abs(ref), 1e-3)).max())
+    print(f"{what}: pixels within {rtol:g}: {f:.5f} (bar {bar}), worst pixel {w:.2e}")
+    assert f >= bar, (what, f)
+    assert w <= worst, (what, w)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -181,20 +194,21 @@ RENDERS = [("two_gauss", "pin", 16), ("two_gauss", "ortho", 4), ("rand50", "pin"
 @pytest.mark.parametrize("sc,cam,spp", RENDERS)
 @pytest.mark.parametrize("integ", ["ss", "ms"])
 def test_render_matches_reference(ctx, ob, vr, golden, scenegen, sc, cam, spp, integ):
-    """>= 98% of pixels within 1e-4 relative of the reference's float image; mean within 1e-3."""
+    """>= 99.5 % of pixels within 1e-4 relative of the reference's float image (measured: 99.6-100 %), none off by more than 1 %;
+    image mean within 2e-3"""
     setup(ctx, ob, vr, scenegen, sc, cam)
     ref = golden[f"render/{sc}/{cam}/{integ}/{spp}"]
     p = vr.Context.params(vr.INTEGRATOR_SS if integ == "ss" else vr.INTEGRATOR_MS, 32, 32, spp)
     img, st = ctx.render(p)
     assert st["samples"] == 32 * 32 * spp
-    assert frac_within(img, ref, 1e-4) >= 0.98, frac_within(img, ref, 1e-4)
+    check_pixels(f"{sc}/{cam}/{integ}/{spp}", img, ref, 1e-4, 0.995)
     assert abs(float(img.mean()) - float(ref.mean())) <= 2e-3 * float(ref.mean())
 
 
 def test_render_min_bounces(ctx, ob, vr, golden, scenegen):
     setup(ctx, ob, vr, scenegen, "rand50", "pin")
     img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 16, min_bounces=1))
-    assert frac_within(img, golden["render/rand50/pin/ms/16/minb1"], 1e-4) >= 0.98
+    check_pixels("rand50 min_bounces 1", img, golden["render/rand50/pin/ms/16/minb1"], 1e-4, 0.995)
 
 
 @pytest.mark.parametrize("solver", [0, 1, 2, 3, 4])
@@ -203,7 +217,7 @@ def test_render_all_solvers_vs_oracle(ctx, ob, vr, scenegen, solver):
     scene, oc = setup(ctx, ob, vr, scenegen, "rand300", "pin2")
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 48, 48, 9, solver=solver)
     img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 48, 48, 9, solver=solver))
-    assert frac_within(img, ref, 1e-4) >= 0.98
+    check_pixels(f"solver {solver}", img, ref, 1e-4, 0.995)
 
 
 @pytest.mark.parametrize("integ", ["ss", "ms"])
@@ -214,7 +228,7 @@ def test_render_vs_oracle_2k_nonuniform(ctx, ob, vr, scenegen, integ):
     it_g = vr.INTEGRATOR_SS if integ == "ss" else vr.INTEGRATOR_MS
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, it_o, 96, 96, 16)
     img, _ = ctx.render(vr.Context.params(it_g, 96, 96, 16))
-    assert frac_within(img, ref, 1e-4) >= 0.98
+    check_pixels(f"2k nonuniform {integ}", img, ref, 1e-4, 0.995)
 
 
 def test_render_overflow_path_vs_oracle(ctx, ob, vr, scenegen):
@@ -225,7 +239,7 @@ def test_render_overflow_path_vs_oracle(ctx, ob, vr, scenegen):
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 24, 24, 4)
     img, st = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 4))
     assert st["overflow_samples"] > 0
-    assert frac_within(img, ref, 2e-4) >= 0.97
+    check_pixels("overflow path (300 wide components)", img, ref, 1e-4, 0.99)
     ctx.set_option("hit_capacity", 40)   # too small on purpose: must fail loudly, not silently drop overlaps
     with pytest.raises(vr.VolRenderError) as e:
         ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 4))
@@ -240,7 +254,8 @@ def test_recorded_sets_match_reference(ctx, ob, vr, golden, scenegen):
         ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, spp, record=True))
         cnt, idx = ctx.recorded(32, 32, 256)
         same = sum(set(r.tolist()) == set(idx[p, :cnt[p]].tolist()) for p, r in enumerate(ref))
-        assert same / len(ref) >= 0.98
+        print(f"{sc}/{cam}: pixels with the reference's recorded set {same / len(ref):.5f}")
+        assert same / len(ref) >= 0.99
 
 
 def test_light_grid_is_only_a_candidate_source(ctx, ob, vr, scenegen):
@@ -323,7 +338,7 @@ def test_empty_and_tiny_scenes(ctx, ob, vr, scenegen):
         ctx.set_lights(lights, ENV)
         ref = ob.render(ob.Gmm(one), lights, ENV, oc, ob.INTEGRATOR_MS, 32, 32, 4)
         img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 4))
-        assert frac_within(img, ref, 1e-4) >= 0.98
+        check_pixels(f"one component, {len(lights)} lights", img, ref, 1e-4, 0.995)
 
 
 def test_window_and_row_partition_are_exact(ctx, ob, vr, scenegen):
@@ -382,7 +397,7 @@ def test_full_size_config1_properties(ctx, ob, vr, scenegen):
     assert st["samples"] == 512 * 512 * 64
     win = (240, 200, 272, 232)
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_SS, 512, 512, 64, window=win)
-    assert frac_within(a[200:232, 240:272], ref[200:232, 240:272], 1e-4) >= 0.98
+    check_pixels("C1 full size, 32x32 window", a[200:232, 240:272], ref[200:232, 240:272], 1e-4, 0.995)
 
 
 @pytest.mark.parametrize("integ", ["ms", "ss"])
@@ -400,8 +415,8 @@ def test_single_kernel_engine_cross_check(ctx, ob, vr, scenegen, integ):
         single, _ = ctx.render(vr.Context.params(it_v, 48, 48, 16))
     finally:
         ctx.set_option("engine", 0)
-    assert frac_within(single, ref, 1e-4) >= 0.98
-    assert frac_within(single, wave, 1e-5) >= 0.99
+    check_pixels(f"single-kernel engine {integ} vs oracle", single, ref, 1e-4, 0.995)
+    check_pixels(f"single-kernel engine {integ} vs wavefront", single, wave, 1e-5, 0.99)
 
 
 def test_full_size_config2_properties(ctx, ob, vr, scenegen):
@@ -421,7 +436,7 @@ def test_full_size_config2_properties(ctx, ob, vr, scenegen):
     assert np.array_equal(halves, a)
     win = (500, 600, 516, 616)   # x0, y0, x1, y1: 16 x 16 pixels in the dense lower half of the mixture
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 1024, 1024, 256, window=win)
-    assert frac_within(a[600:616, 500:516], ref[600:616, 500:516], 1e-4) >= 0.97
+    check_pixels("C2 full size, 16x16 window", a[600:616, 500:516], ref[600:616, 500:516], 1e-4, 0.995)
     # the same window rendered alone (a small render: no grids, one part) is the same image
     w, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 1024, 1024, 256, window=win))
     assert np.array_equal(w[600:616, 500:516], a[600:616, 500:516])
@@ -443,11 +458,15 @@ def test_unpack_params_vs_oracle(ctx, ob, golden):
 
 
 def test_adam_step_bit_exact(ctx, ob, golden):
+    """AdamOptimizer::step (optimizer.h:30-41) on the reference's own gradient / parameter vectors: absolute 1e-7 (one ulp of a
+    parameter of magnitude ~1 where the host's powf / sqrtf of the bias correction round differently); the bit-identical
+    fraction is printed"""
     g = golden["sfd/iter0/12"]
     D = g.size
     p = golden["sfd/iter0/10"].copy(); m = np.zeros(D, np.float32); v = np.zeros(D, np.float32)
     t = ctx.adam_step(p, g, m, v, 0)
     assert t == 1
+    print(f"Adam step 1: parameters bit-identical to the reference's {(p.view(np.uint32) == golden['sfd/iter0/13'].view(np.uint32)).mean():.5f}")
     np.testing.assert_allclose(p, golden["sfd/iter0/13"], rtol=0, atol=1e-7)
     g1 = golden["sfd/iter1/12"]
     p = golden["sfd/iter1/10"].copy()
@@ -471,7 +490,7 @@ def test_sfd_iterations_vs_reference(ctx, ob, vr, golden, scenegen):
         # base image of the unpacked scene vs the reference's (rendered through vr_set_gmm_params)
         ctx.set_gmm_params(params)
         base, _ = ctx.render(rp)
-        assert frac_within(base, golden[f"sfd/iter{it}/15"].reshape(H, W, 3), 1e-3) >= 0.97
+        check_pixels(f"SFD iteration {it} base image (through vr_set_gmm_params)", base, golden[f"sfd/iter{it}/15"].reshape(H, W, 3), 1e-4, 0.99)
         ctx.sfd_begin(params, eps, lr=0.01)
         ctx.sfd_set_target(golden["sfd/target"])
         F, loss_sum, npx = ctx.sfd_fdiff(rp, signs[it])
@@ -542,7 +561,7 @@ def test_spheres_vs_oracle(ctx, ob, vr, golden, scenegen, name):
     ctx.set_camera(cd); ctx.set_smm(smm); ctx.set_lights(smm["lights"], ENV)
     ref = ob.render_spheres(smm, ENV, oc, 48, 48, 0.01, 5)
     img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MARCH_SPHERES, 48, 48, 1, march_step=0.01, env_samples=5))
-    assert frac_within(img, ref, 1e-4) >= 0.99
+    check_pixels(f"spheres {name} vs oracle", img, ref, 1e-4, 0.995)
     gold = golden[f"spheres/{name}/ortho"]
     assert abs(float(img.mean()) - float(gold.mean())) < 0.01 * float(gold.mean())
 
@@ -563,14 +582,14 @@ def test_validation_integrators(ctx, ob, vr, scenegen, golden_march, sc, integ, 
     if integ == "test":
         assert np.array_equal(img, ref)
     else:
-        assert frac_within(img, ref, 1e-4, atol=1e-7) >= 0.98
+        check_pixels(f"{integ} {sc} black environment vs reference", img, ref, 1e-4, 0.995, atol=1e-7)
     ctx.set_lights(scene["lights"], ENV)
     img, st = ctx.render(p)
     orc = ob.render_march(ob.Gmm(scene), scene["lights"], ENV, oc, wh, wh, mode - 3, float(step), env_samples)
     if integ == "test":
         assert np.array_equal(img, orc)
     else:
-        assert frac_within(img, orc, 1e-4) >= 0.98
+        check_pixels(f"{integ} {sc} sky vs oracle", img, orc, 1e-4, 0.995)
         assert st["kernel_launches"] == 1
     # row partition: the two halves of an interleaved split reproduce the whole image
     parts = np.zeros_like(img)

@@ -300,12 +300,16 @@ def test_c3_transmittance_200k_components(ctx, ob, vr, scenegen):
     ok = np.abs(got - ref) <= 1e-7 + 1e-5 * np.abs(ref)
     print(f"C3 transmittance: {int((~ok).sum())} of {n} rays outside 1e-5 of the oracle's hierarchy walk")
     assert ok.mean() >= 0.9999
-    # a ray that grazes a 3-sigma ellipsoid inside the rounding noise of the FP32 quadric is accepted or not depending on which
-    # boxes let the quadric see it (the oracle's hierarchy and ours differ there, and so does the reference's): the arbiter is
-    # the walk over EVERY component (gmm.h:190-226).  Every disagreeing ray and 1500 random ones must match it.
+    # Who is right where they differ?  The arbiter for CULLING is the walk over EVERY component (gmm.h:190-226): on every
+    # disagreeing ray and 1500 random ones it gives the oracle's value (so nothing was culled away on either side), and the
+    # device stays within 1e-4 of it.  What is left (measured: 4 rays of 100 000, up to 2.9e-5) is the FP32 cancellation in
+    # K * (erf(b) - erf(a)) for a clipped interval inside a dense component (K up to ~10^3): one ulp of erff -- CUDA's and
+    # glibc's differ in the last bit -- is 6e-5 of optical depth there.
     pick = np.unique(np.concatenate([np.nonzero(~ok)[0], rs.choice(n, 1500, replace=False)]))
     brute = gm.transmittance_brute(o[pick], d[pick], tmax[pick])
-    np.testing.assert_allclose(got[pick], brute, rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(ref[pick], brute, rtol=2e-6, atol=1e-7)
+    np.testing.assert_allclose(got[pick], brute, rtol=1e-4, atol=1e-7)
+    assert (np.abs(got[pick] - brute) <= 1e-7 + 1e-5 * np.abs(brute)).mean() >= 0.995
     assert ((ref > 0.01) & (ref < 0.99)).mean() > 0.05
 
 
@@ -478,21 +482,37 @@ def test_comm_allreduce_is_exact_on_every_path(ctx, vr, ob, golden, scenegen):
 # ------------------------------------------------------------------------------------------------
 def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scenegen):
     """wave_trav2_kernel (private candidate slots, phases) against wave_trav_kernel (shared queue), the device-built LBVH and
-    light grids against the host binned-SAH tree and host grids: candidates come in another order and from another tree,
-    the quadric test decides and the sums are order independent -> images identical bit for bit, with and without grids,
-    both integrators, also on the heavy-overlap scene whose rays overflow the per-slot overlap records."""
+    light grids against the host binned-SAH tree and host grids, camera rays gathered from the pinhole's direction grid
+    (wave_regen_cam_kernel) against camera rays sent through the hierarchy: candidates come in another order and from
+    another structure, the quadric test decides and the sums are order independent -> images identical bit for bit, with
+    and without grids, both integrators, also on the heavy-overlap scene whose rays overflow the per-slot overlap records."""
     cases = [(file_scene(scenegen, "rand2k"), "pin", 96, 64, 16), (file_scene(scenegen, "rand300"), "pin2", 64, 64, 9),
              (scenegen.generate(3000, 11, nonuniform=True, diameter_range=(0.02, 0.09)), "pin", 128, 96, 16)]
-    ctx.set_option("light_grid_min_samples", 0)
+    ctx.set_option("light_grid_min_samples", 0); ctx.set_option("camera_grid_min_samples", 0)
     try:
         for scene, cam, W, H, spp in cases:
             for integ in (vr.INTEGRATOR_MS, vr.INTEGRATOR_SS):
                 imgs = []
-                for hier, trav, grid in ((0, 2, 1), (0, 1, 1), (1, 2, 1), (1, 1, 0), (0, 2, 0)):
+                for hier, trav, grid, cgrid, split in ((0, 2, 1, 1, 0), (0, 2, 1, 0, 0), (0, 1, 1, 0, 0), (1, 2, 1, 0, 1), (1, 1, 0, 0, 0), (0, 2, 0, 1, 1)):
                     ctx.set_option("hierarchy", hier); ctx.set_option("trav", trav); ctx.set_option("light_grid", grid)
+                    ctx.set_option("camera_grid", cgrid); ctx.set_option("post_split", split)
                     setup(ctx, ob, scene, cam)
                     img, st = ctx.render(vr.Context.params(integ, W, H, spp))
                     imgs.append(img)
-                    assert np.array_equal(img, imgs[0]), (hier, trav, grid)
+                    assert np.array_equal(img, imgs[0]), (hier, trav, grid, cgrid, split)
+        # the camera inside the mixture: the pinhole sits in a component's box -> no camera grid, same image
+        scene = file_scene(scenegen, "rand300")
+        oc = ob.make_camera("pinhole", (0.1, 1.0, 2.6), look=(0, 1, 0), fov=0.9)
+        cd = dict(kind=int(oc.kind), pos=np.array(oc.pos[:], np.float32), view=np.array(oc.view[:], np.float32), right=np.array(oc.right[:], np.float32),
+                  up=np.array(oc.up[:], np.float32), pinhole=np.array(oc.pinhole[:], np.float32))
+        pair = []
+        for cgrid in (1, 0):
+            ctx.set_option("camera_grid", cgrid)
+            ctx.set_gmm(scene); ctx.set_lights(scene["lights"], ENV); ctx.set_camera(cd)
+            pair.append(ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 64, 64, 16))[0])
+        assert np.array_equal(pair[0], pair[1])
+        ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 64, 64, 16)
+        assert within(pair[0], ref, 1e-4).mean() >= 0.99
     finally:
         ctx.set_option("hierarchy", 0); ctx.set_option("trav", 2); ctx.set_option("light_grid", 1); ctx.set_option("light_grid_min_samples", 16e6)
+        ctx.set_option("camera_grid", 1); ctx.set_option("camera_grid_min_samples", 2e6); ctx.set_option("post_split", 0)
