@@ -36,11 +36,19 @@ struct RenderArgs {
     uint32_t* record_bits;        // per image pixel bitmap of contributing Gaussians (or nullptr)
     int record_words;
     unsigned long long* stats;
-    unsigned int* overflow_list;
-    unsigned int* overflow_count;
+    unsigned int* overflow_list;  // samples to re-trace with the large-capacity store; overflow_cap entries
+    unsigned int* overflow_count; // may run past overflow_cap: the host then fails the render instead of dropping samples
+    unsigned int overflow_cap;
     float* arena;                 // re-trace kernel: kArenaFields * arena_cap * 32 floats per warp
     int arena_cap;
 };
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void overflow_push(const RenderArgs& A, unsigned int sample) {
+    const unsigned int at = atomicAdd(A.overflow_count, 1u);
+    if (at < A.overflow_cap) A.overflow_list[at] = sample;
+}
+#endif
 
 // ---- wavefront engine (vr_wave.cu): a pool of P path slots whose state lives in global memory
 // (sized to stay resident in the 126 MB L2), advanced one ray per iteration by four small kernels.

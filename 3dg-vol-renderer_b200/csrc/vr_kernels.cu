@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(kBlockThreads) path_kernel(const __grid_consta
                     atomicAdd(A.stats + ST_ERRORS, 1ULL);  // even the large store overflowed: reported as VR_ERR_HIT_OVERFLOW
                     A.sampleL[ps.work] = make_float4(0.f, 0.f, 0.f, -1.f);
                 } else {
-                    A.overflow_list[atomicAdd(A.overflow_count, 1u)] = ps.work;  // re-traced from scratch by the arena kernel
+                    overflow_push(A, ps.work);  // re-traced from scratch by the arena kernel
                     ++n_over;
                 }
                 alive = false;
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(kBlockThreads) wave_drain_kernel(const __grid_
         if (r == 1) {
             A.sampleL[ps.work] = make_float4(ps.L0, ps.L1, ps.L2, (float)ps.bounce);
         } else {       // more overlaps than the local store holds: the whole sample is re-traced by the arena kernel
-            A.overflow_list[atomicAdd(A.overflow_count, 1u)] = ps.work + A.work_base;
+            overflow_push(A, ps.work + A.work_base);
             ++n_over;
         }
     }

@@ -10,8 +10,10 @@
 //   Eigen squaredNorm() = e0 + (e1 + e2)  (Core/Redux.h)
 //   Eigen 3x3 * 3x1     = row . v as e0 + (e1 + e2), plain mul/add
 // sinf/cosf/acosf are ports of the algorithms glibc 2.39 runs on the reference's host (they are
-// not correctly rounded, so CUDA's or a double-rounded version disagrees in 1-8% of arguments);
-// tests/test_libm_ports.py pins them bit-for-bit against the host libm over all 2^24 inputs.
+// not correctly rounded, so CUDA's or a double-rounded version disagrees in 1-8% of arguments; provenance: NOTICE).
+// tests/test_gpu_parity_r2.py::test_libm_ports_on_every_argument_the_renderer_can_produce compares them with the
+// host libm on all 2^24 arguments of each call site: acosf bit for bit, sinf / cosf within one ulp on every argument
+// and bit for bit on > 99.99 % (the host picks an FMA or a non-FMA build of the same polynomials at run time).
 #pragma once
 #include <cuda_runtime.h>
 #include <math_constants.h>

@@ -127,7 +127,10 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             A.pixel_base = (unsigned int)p0;
             A.work_count = pass_pixels * (unsigned int)p->spp;
             A.worklist = nullptr;
-            VR_CUDA(ctx->overflow_list.ensure((size_t)A.work_count * 4));
+            // overflow samples are a fraction of a per cent even in heavy overlap (0.13 % at C3): 16 M entries (64 MB) bound the
+            // list; a pass that needs more fails loudly below (shrink max_pass_samples) instead of dropping samples
+            A.overflow_cap = (unsigned int)std::min<unsigned long long>(A.work_count, 1ull << 24);
+            VR_CUDA(ctx->overflow_list.ensure((size_t)A.overflow_cap * 4));
             A.overflow_list = ctx->overflow_list.as<unsigned int>();
             VR_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(unsigned int) * 4, s));
             VR_CUDA(cudaEventRecord(ctx->ev[2], s));
@@ -151,6 +154,8 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
             VR_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(unsigned int) * 4, cudaMemcpyDeviceToHost, s));
             VR_CUDA(cudaStreamSynchronize(s));
             const unsigned int n_over = ctx->h_counters[1];
+            if (n_over > A.overflow_cap)
+                return fail(ctx, VR_ERR_HIT_OVERFLOW, "more than 16 M samples of one pass overflowed the per-slot overlap records; lower max_pass_samples");
             if (n_over > 0) {  // samples whose rays overlapped more than kLocalCap components: re-trace with the arena store
                 NvtxRange range_over("vr.render.overflow_retrace");
                 overflow_total += n_over;

@@ -208,7 +208,7 @@ static __device__ __noinline__ void lane_post_a(const RenderArgs& A, WarpShared&
     const SceneDev& S = A.scene;
     const int K = w.count[lane];
     if (K > kSmemCap) {  // more overlaps than the shared-memory list holds: the whole sample is re-traced by the arena kernel
-        A.overflow_list[atomicAdd(A.overflow_count, 1u)] = ls.work;
+        overflow_push(A, ls.work);
         ++cn.over;
         ls.mode = M_REGEN;
         return;

@@ -1076,7 +1076,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     hand_over = true;   // untouched: the general kernel redoes it
                 }
             } else if (K > kWaveCap) {  // more overlaps than a slot holds: the whole sample is re-traced by the arena kernel
-                A.overflow_list[atomicAdd(A.overflow_count, 1u)] = s1.z + A.work_base;
+                overflow_push(A, s1.z + A.work_base);
                 ++cn.over;
                 dest = DEST_REGEN;
             } else {
@@ -1333,7 +1333,11 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         pt.st = parts > 1 ? part_streams[i] : s;
         pt.h = h_cnt_all + kWaveCounters * i;
         pt.done = false;
-        if (cudaEventCreateWithFlags(&pt.ev, cudaEventDisableTiming) != cudaSuccess) return -1;
+        if (cudaEventCreateWithFlags(&pt.ev, cudaEventDisableTiming) != cudaSuccess) {
+            for (int k = 0; k < i; ++k) cudaEventDestroy(part[k].ev);   // the events made so far
+            cudaEventDestroy(fork);
+            return -1;
+        }
         if (parts > 1) cudaStreamWaitEvent(pt.st, fork, 0);
         const unsigned int slots = (unsigned int)std::min<unsigned long long>((unsigned long long)pt.q.P, pt.a.work_count);
         wave_init_kernel<<<(std::max(slots, (unsigned int)kWaveCounters) + 255) / 256, 256, 0, pt.st>>>(pt.q, slots);
@@ -1425,7 +1429,9 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
                     cudaGraph_t g = nullptr;
                     if (cudaStreamBeginCapture(pt.st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { failed = true; break; }
                     for (int b = 0; b < kBatch; ++b) enqueue_iteration(pt);
-                    if (cudaStreamEndCapture(pt.st, &g) != cudaSuccess || cudaGraphInstantiate(&en.exec, g, 0) != cudaSuccess) { failed = true; en.exec = nullptr; }
+                    // EndCapture is called whatever happened inside the capture: a stream must never be left capturing
+                    const cudaError_t ce = cudaStreamEndCapture(pt.st, &g);
+                    if (ce != cudaSuccess || g == nullptr || cudaGraphInstantiate(&en.exec, g, 0) != cudaSuccess) { failed = true; en.exec = nullptr; }
                     if (g) cudaGraphDestroy(g);
                     if (failed) break;
                     memcpy((void*)&en.key, (const void*)&key, sizeof(key));
@@ -1472,7 +1478,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
                 }
             }
         }
-        if (iters > (1 << 24)) break;
+        if (iters > (1 << 24)) { failed = true; break; }   // a pass that does not end is an error, not a result
     }
     for (int i = 0; i < parts; ++i) {
         if (parts > 1) { cudaEventRecord(part[i].ev, part[i].st); cudaStreamWaitEvent(s, part[i].ev, 0); }   // join

@@ -62,15 +62,18 @@ def frac_within(a, b, rtol, atol=1e-6):
     return float((np.abs(a - b) <= atol + rtol * np.abs(b)).all(axis=-1).mean())
 
 
-def check_pixels(what, img, ref, rtol, bar, worst=1e-2, atol=1e-6):
+def check_pixels(what, img, ref, rtol, bar, spp=1, atol=1e-6):
     """fraction of pixels within rtol (printed: pytest -s shows what was achieved, not only that the bar held) and a bound on
-    the worst pixel: an image with a few badly wrong pixels does not pass.  Which samples may differ, and why, is established
-    sample by sample in tests/test_gpu_parity_r2.py::test_per_sample_attribution."""
+    the worst pixel: a pixel outside the tolerance holds a sample that an FP32 implementation legitimately moves (or, once in
+    ~10^4 samples, that takes another branch than the reference's libm made it take), so it may be off by a fraction of ONE
+    sample's value -- never by more than the brightest pixel's worth of one sample, max(ref) / spp.  Which samples may differ,
+    and why, is established sample by sample in tests/test_gpu_parity_r2.py::test_per_sample_attribution."""
     f = frac_within(img, ref, rtol, atol)
-    w = float((np.abs(img - ref) / np.maximum(np.abs(ref), 1e-3)).max())
-    print(f"{what}: pixels within {rtol:g}: {f:.5f} (bar {bar}), worst pixel {w:.2e}")
+    w = float(np.abs(img - ref).max())
+    lim = float(np.abs(ref).max()) / spp + 1e-6
+    print(f"{what}: pixels within {rtol:g}: {f:.5f} (bar {bar}), largest deviation {w:.2e} (one sample of the brightest pixel: {lim:.2e})")
     assert f >= bar, (what, f)
-    assert w <= worst, (what, w)
+    assert w <= lim, (what, w, lim)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -201,14 +204,14 @@ def test_render_matches_reference(ctx, ob, vr, golden, scenegen, sc, cam, spp, i
     p = vr.Context.params(vr.INTEGRATOR_SS if integ == "ss" else vr.INTEGRATOR_MS, 32, 32, spp)
     img, st = ctx.render(p)
     assert st["samples"] == 32 * 32 * spp
-    check_pixels(f"{sc}/{cam}/{integ}/{spp}", img, ref, 1e-4, 0.995)
+    check_pixels(f"{sc}/{cam}/{integ}/{spp}", img, ref, 1e-4, 0.995, spp)
     assert abs(float(img.mean()) - float(ref.mean())) <= 2e-3 * float(ref.mean())
 
 
 def test_render_min_bounces(ctx, ob, vr, golden, scenegen):
     setup(ctx, ob, vr, scenegen, "rand50", "pin")
     img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 16, min_bounces=1))
-    check_pixels("rand50 min_bounces 1", img, golden["render/rand50/pin/ms/16/minb1"], 1e-4, 0.995)
+    check_pixels("rand50 min_bounces 1", img, golden["render/rand50/pin/ms/16/minb1"], 1e-4, 0.995, 16)
 
 
 @pytest.mark.parametrize("solver", [0, 1, 2, 3, 4])
@@ -217,7 +220,7 @@ def test_render_all_solvers_vs_oracle(ctx, ob, vr, scenegen, solver):
     scene, oc = setup(ctx, ob, vr, scenegen, "rand300", "pin2")
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 48, 48, 9, solver=solver)
     img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 48, 48, 9, solver=solver))
-    check_pixels(f"solver {solver}", img, ref, 1e-4, 0.995)
+    check_pixels(f"solver {solver}", img, ref, 1e-4, 0.995, 9)
 
 
 @pytest.mark.parametrize("integ", ["ss", "ms"])
@@ -228,7 +231,7 @@ def test_render_vs_oracle_2k_nonuniform(ctx, ob, vr, scenegen, integ):
     it_g = vr.INTEGRATOR_SS if integ == "ss" else vr.INTEGRATOR_MS
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, it_o, 96, 96, 16)
     img, _ = ctx.render(vr.Context.params(it_g, 96, 96, 16))
-    check_pixels(f"2k nonuniform {integ}", img, ref, 1e-4, 0.995)
+    check_pixels(f"2k nonuniform {integ}", img, ref, 1e-4, 0.995, 16)
 
 
 def test_render_overflow_path_vs_oracle(ctx, ob, vr, scenegen):
@@ -239,7 +242,7 @@ def test_render_overflow_path_vs_oracle(ctx, ob, vr, scenegen):
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 24, 24, 4)
     img, st = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 4))
     assert st["overflow_samples"] > 0
-    check_pixels("overflow path (300 wide components)", img, ref, 1e-4, 0.99)
+    check_pixels("overflow path (300 wide components)", img, ref, 1e-4, 0.99, 4)
     ctx.set_option("hit_capacity", 40)   # too small on purpose: must fail loudly, not silently drop overlaps
     with pytest.raises(vr.VolRenderError) as e:
         ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, 4))
@@ -338,7 +341,7 @@ def test_empty_and_tiny_scenes(ctx, ob, vr, scenegen):
         ctx.set_lights(lights, ENV)
         ref = ob.render(ob.Gmm(one), lights, ENV, oc, ob.INTEGRATOR_MS, 32, 32, 4)
         img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 32, 32, 4))
-        check_pixels(f"one component, {len(lights)} lights", img, ref, 1e-4, 0.995)
+        check_pixels(f"one component, {len(lights)} lights", img, ref, 1e-4, 0.995, 4)
 
 
 def test_window_and_row_partition_are_exact(ctx, ob, vr, scenegen):
@@ -397,7 +400,7 @@ def test_full_size_config1_properties(ctx, ob, vr, scenegen):
     assert st["samples"] == 512 * 512 * 64
     win = (240, 200, 272, 232)
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_SS, 512, 512, 64, window=win)
-    check_pixels("C1 full size, 32x32 window", a[200:232, 240:272], ref[200:232, 240:272], 1e-4, 0.995)
+    check_pixels("C1 full size, 32x32 window", a[200:232, 240:272], ref[200:232, 240:272], 1e-4, 0.995, 64)
 
 
 @pytest.mark.parametrize("integ", ["ms", "ss"])
@@ -415,8 +418,8 @@ def test_single_kernel_engine_cross_check(ctx, ob, vr, scenegen, integ):
         single, _ = ctx.render(vr.Context.params(it_v, 48, 48, 16))
     finally:
         ctx.set_option("engine", 0)
-    check_pixels(f"single-kernel engine {integ} vs oracle", single, ref, 1e-4, 0.995)
-    check_pixels(f"single-kernel engine {integ} vs wavefront", single, wave, 1e-5, 0.99)
+    check_pixels(f"single-kernel engine {integ} vs oracle", single, ref, 1e-4, 0.995, 16)
+    check_pixels(f"single-kernel engine {integ} vs wavefront", single, wave, 1e-5, 0.99, 16)
 
 
 def test_full_size_config2_properties(ctx, ob, vr, scenegen):
@@ -436,7 +439,7 @@ def test_full_size_config2_properties(ctx, ob, vr, scenegen):
     assert np.array_equal(halves, a)
     win = (500, 600, 516, 616)   # x0, y0, x1, y1: 16 x 16 pixels in the dense lower half of the mixture
     ref = ob.render(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 1024, 1024, 256, window=win)
-    check_pixels("C2 full size, 16x16 window", a[600:616, 500:516], ref[600:616, 500:516], 1e-4, 0.995)
+    check_pixels("C2 full size, 16x16 window", a[600:616, 500:516], ref[600:616, 500:516], 1e-4, 0.995, 256)
     # the same window rendered alone (a small render: no grids, one part) is the same image
     w, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 1024, 1024, 256, window=win))
     assert np.array_equal(w[600:616, 500:516], a[600:616, 500:516])
@@ -490,7 +493,7 @@ def test_sfd_iterations_vs_reference(ctx, ob, vr, golden, scenegen):
         # base image of the unpacked scene vs the reference's (rendered through vr_set_gmm_params)
         ctx.set_gmm_params(params)
         base, _ = ctx.render(rp)
-        check_pixels(f"SFD iteration {it} base image (through vr_set_gmm_params)", base, golden[f"sfd/iter{it}/15"].reshape(H, W, 3), 1e-4, 0.99)
+        check_pixels(f"SFD iteration {it} base image (through vr_set_gmm_params)", base, golden[f"sfd/iter{it}/15"].reshape(H, W, 3), 1e-4, 0.99, 16)
         ctx.sfd_begin(params, eps, lr=0.01)
         ctx.sfd_set_target(golden["sfd/target"])
         F, loss_sum, npx = ctx.sfd_fdiff(rp, signs[it])
