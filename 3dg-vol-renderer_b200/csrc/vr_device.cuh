@@ -314,11 +314,12 @@ __device__ __noinline__ float solve_newton(St& st, int na, float ta, float tb, f
     }
     return solve_bisection(st, na, ta, tb, target);
 }
-// DEFER: the iterative solvers are not run here; *deferred is set instead and the caller redoes the whole walk later
-// among other deferred paths (wave_post_a_kernel<2>), where a warp's lanes iterate together
+// DEFER: the iterative solvers are not run here; *deferred is set instead, the segment [ta, tb] and the remaining depth
+// go to *ds, and the caller hands the slot to wave_post_a_kernel<4> (or <2>), where a warp's lanes iterate together
+struct DeferState { float ta, tb, remaining; };
 template <bool DEFER, class St>
 __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, float ta, float tb, float remaining,
-                                int solver, uint64_t key, bool* deferred) {  // :150-187
+                                int solver, uint64_t key, bool* deferred, DeferState* ds = nullptr) {  // :150-187
     if (solver == 4) {  // UNIFORM (:131-137): t = ta + u (tb - ta); the reference's u comes from a random_device-seeded
                         // generator (parity unpinned), ours is hashed from the path's PCG state after the target draw,
                         // like the oracle's solve_uniform
@@ -333,7 +334,11 @@ __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, f
         VR_COUNT(++st.n_sa;)
         if (solve_t_given_tau(g, q, ta, tb, remaining, &t_an)) return clampf(t_an, ta, tb);
     }
-    if (DEFER) { *deferred = true; return ta; }
+    if (DEFER) {
+        *deferred = true;
+        if (ds) { ds->ta = ta; ds->tb = tb; ds->remaining = remaining; }
+        return ta;
+    }
     if (solver == 0 || solver == 2) return solve_newton(st, na, ta, tb, remaining);
     return solve_bisection(st, na, ta, tb, remaining);
 }
@@ -403,7 +408,7 @@ __device__ __forceinline__ bool next_event(const SceneDev& S, St& st, int K, int
 
 template <bool DEFER = false, class St>
 __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float target_tau, int solver, bool ss,
-                             int* na_out, uint64_t key, bool* deferred = nullptr) {
+                             int* na_out, uint64_t key, bool* deferred = nullptr, DeferState* ds = nullptr) {
     sort_entries(S, st, K);
     double acc = 0.0;
     float accf = 0.0f;
@@ -440,11 +445,13 @@ __device__ float free_flight(const SceneDev& S, St& st, int K, f3 o, f3 d, float
             if (!hit_target) acc = __dadd_rn(acc, seg);
         }
         if (hit_target) {
-            VR_COUNT(st.n_erf += (unsigned int)na;)
-            for (int k = 0; k < na; ++k)  // restore erf(arg(t_prev)) for the solver
-                st.F(F_ACTF, k) = erff_ni(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
+            if (!DEFER) {   // (a deferred solve restores them itself; the analytic and the uniform one do not read them)
+                VR_COUNT(st.n_erf += (unsigned int)na;)
+                for (int k = 0; k < na; ++k)  // restore erf(arg(t_prev)) for the solver
+                    st.F(F_ACTF, k) = erff_ni(erf_arg(hit_const(st, (int)st.U(U_ACT, k)), t_prev));
+            }
             *na_out = na;
-            return solve_distance<DEFER>(S, st, na, o, d, t_prev, t_evt, remaining, solver, key, deferred);
+            return solve_distance<DEFER>(S, st, na, o, d, t_prev, t_evt, remaining, solver, key, deferred, ds);
         }
         if (take_enter) {
             const float F0 = erff_ni(erf_arg(hit_const(st, se), t_evt));

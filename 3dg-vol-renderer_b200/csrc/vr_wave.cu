@@ -982,7 +982,9 @@ __device__ __forceinline__ int post_a_finish(const RenderArgs& A, const WavePool
     return (light >= 0 && light < 32 && ((S.lg_mask >> light) & 1u)) ? DEST_TRAV_LIGHT : DEST_TRAV;
 }
 
-// MODE: 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots, 3 general, solves in place.
+// MODE: 0 general (defers iterative solves), 1 fast K = 1, 2 deferred slots (walk redone), 3 general, solves in place,
+//       4 deferred slots resumed from the state MODE 0 left in the slot: the segment [ta, tb], the remaining depth and the
+//       active list in the reference's order (ps2 is free between the free-flight ray and the shadow ray).
 // CLS (general modes only): -1 = classes 1..4 in one launch with a 16-entry overlap store; 1..4 = that class alone with a store
 // sized for it (2 / 4 / 8 / 16 entries: the store lives in local memory, 40 bytes per entry and thread)
 template <int MODE, int CLS = -1>
@@ -990,8 +992,9 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
     const SceneDev& S = A.scene;
     constexpr bool FAST = MODE == 1;
     constexpr bool kOneClass = (MODE == 0 || MODE == 3) && CLS > 0;
-    constexpr int kFirst = MODE == 1 ? 0 : (MODE == 2 ? kPostClasses : (kOneClass ? CLS : 1));              // classes [kFirst, kLast)
-    constexpr int kLast = MODE == 1 ? 1 : (MODE == 2 ? kPostClasses + 1 : (kOneClass ? CLS + 1 : kPostClasses));
+    constexpr bool kDeferred = MODE == 2 || MODE == 4;
+    constexpr int kFirst = MODE == 1 ? 0 : (kDeferred ? kPostClasses : (kOneClass ? CLS : 1));              // classes [kFirst, kLast)
+    constexpr int kLast = MODE == 1 ? 1 : (kDeferred ? kPostClasses + 1 : (kOneClass ? CLS + 1 : kPostClasses));
     constexpr int kStoreCap = !kOneClass ? kWaveCap : (CLS == 1 ? 2 : (CLS == 2 ? 4 : (CLS == 3 ? 8 : kWaveCap)));
     unsigned int nA[kPostClasses + 1], base[kPostClasses + 2];
     base[kFirst] = 0;
@@ -1003,7 +1006,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
         unsigned int sum = 0;
 #pragma unroll
         for (int c = kFirst; c < kLast; ++c) sum += nA[c];
-        Q.cnt[MODE == 2 ? WC_SUM_DEFERRED : WC_SUM_GENERAL] += sum;
+        Q.cnt[kDeferred ? WC_SUM_DEFERRED : WC_SUM_GENERAL] += sum;
     }  // consumed by wave_trav<scatter>
     WaveCounters cn = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     const unsigned int stride = gridDim.x * blockDim.x;
@@ -1075,6 +1078,45 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 } else {
                     hand_over = true;   // untouched: the general kernel redoes it
                 }
+            } else if (MODE == 4) {
+                // ---- resume an iterative solve (distance_solvers.h:25-127) from the saved state: only the active components
+                //      are loaded, in list order; constants and erf(arg(ta)) are recomputed from the same inputs, bit for bit
+                const float4 d0 = Q.ps2[kSlotF4 * (size_t)p], d1 = Q.ps2[kSlotF4 * (size_t)p + 1];
+                const uint64_t order = (uint64_t)__float_as_uint(d0.x) | ((uint64_t)__float_as_uint(d0.y) << 32);
+                const float ta = d1.x, tb = d1.y, remaining = d1.z;
+                const int na = __float_as_int(d1.w);
+                cn.hits += (unsigned int)K;
+                LocalStore<kWaveCap> st;
+                VR_COUNT(st.n_erf += (unsigned int)na;)
+#pragma unroll 1
+                for (int k = 0; k < na; ++k) {
+                    float ht0, ht1; uint32_t gi;
+                    pool_load_hit(Q, p, (int)((order >> (4 * k)) & 15u), h0, &ht0, &ht1, &gi);
+                    const GaussRec g = load_gauss(S.gauss, gi);
+                    const DepthConst c = depth_const(g, ray_quad(g, o, d));
+                    st.F(F_A, k) = c.A; st.F(F_B, k) = c.B; st.F(F_K, k) = c.K; st.F(F_DEN, k) = c.den;
+                    st.F(F_ACTF, k) = erff_ni(erf_arg(c, ta));
+                    st.U(U_GI, k) = gi; st.U(U_ACT, k) = (uint32_t)k;
+                }
+                const float t = (A.solver == 0 || A.solver == 2) ? solve_newton(st, na, ta, tb, remaining) : solve_bisection(st, na, ta, tb, remaining);
+                if (A.record_bits) {  // integrator.h:616-644 (t >= 0 here)
+                    int x, y, si;
+                    lane_xy(A, s1.z, &x, &y, &si);
+                    uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
+                    const float tlim = __fadd_rn(t, 1e-6f);
+                    for (int s = 0; s < K; ++s) {
+                        float ht0, ht1; uint32_t gi;
+                        pool_load_hit(Q, p, s, h0, &ht0, &ht1, &gi);
+                        if (t < 0.0f || ht0 <= tlim) {
+                            const uint32_t orig = __ldg(S.orig + gi);
+                            const uint32_t bit = 1u << (orig & 31u);
+                            if (!(row[orig >> 5] & bit)) atomicOr(row + (orig >> 5), bit);
+                        }
+                    }
+                }
+                const float albedo = t >= 0.0f ? evaluate_albedo(S, st, na, add3(o, scale3(t, d))) : 0.0f;
+                dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
+                VR_COUNT(cn.erf += st.n_erf; cn.mu += st.n_mu; cn.sa += st.n_sa; cn.it += st.n_it;)
             } else if (K > kWaveCap) {  // more overlaps than a slot holds: the whole sample is re-traced by the arena kernel
                 overflow_push(A, s1.z + A.work_base);
                 ++cn.over;
@@ -1093,9 +1135,14 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                     st.U(U_GI, s) = gi;
                 }
                 int na = 0;
-                const float t = free_flight<MODE == 0>(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state, &deferred);
+                DeferState ds;
+                const float t = free_flight<MODE == 0>(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state, &deferred, &ds);
                 if (deferred) {
-                    cn.hits -= (unsigned int)K;   // counted when the slot is redone
+                    cn.hits -= (unsigned int)K;   // counted when the slot is finished
+                    uint64_t order = 0;            // the active list in the reference's order, four bits per entry
+                    for (int k = 0; k < na; ++k) order |= (uint64_t)(st.U(U_ACT, k) & 15u) << (4 * k);
+                    Q.ps2[kSlotF4 * (size_t)p] = make_float4(__uint_as_float((unsigned int)order), __uint_as_float((unsigned int)(order >> 32)), 0.f, 0.f);
+                    Q.ps2[kSlotF4 * (size_t)p + 1] = make_float4(ds.ta, ds.tb, ds.remaining, __int_as_float(na));
                 } else {
                 if (A.record_bits) {  // integrator.h:616-644
                     int x, y, si;
@@ -1291,6 +1338,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     });
     const bool t2 = a_all.trav_version != 1;
     const bool post_split = a_all.post_split != 0;
+    const bool resume = a_all.post_defer == 2;   // deferred solves resumed from the state in the slot (no second walk)
     const int bps_s = occ[t2 ? 1 : 0][0], bps_h = occ[t2 ? 1 : 0][1], bps_l = occ[t2 ? 1 : 0][2];
     const char* prof_env = getenv("VR_WAVE_PROFILE");
     const bool prof = prof_env && prof_env[0] == '1';
@@ -1307,6 +1355,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     const auto tl0 = std::chrono::steady_clock::now();
     static const bool drain_on = !(getenv("VR_WAVE_DRAIN") && getenv("VR_WAVE_DRAIN")[0] == '0');
     static const unsigned int drain_div = getenv("VR_WAVE_DRAIN_DIV") ? (unsigned int)std::max(1, atoi(getenv("VR_WAVE_DRAIN_DIV"))) : 8u;   // hand-over below P / drain_div live paths
+    static const unsigned int drain_max = getenv("VR_WAVE_DRAIN_MAX") ? (unsigned int)std::max(1, atoi(getenv("VR_WAVE_DRAIN_MAX"))) : 32768u;   // ... and below this many: per bounce the drain kernel is ~10x slower than the wave kernels, so it only gets the stragglers (profiles/r02/drain_sweep.md)
     static const int defer_env = getenv("VR_WAVE_DEFER") ? atoi(getenv("VR_WAVE_DEFER")) : -1;   // 0 / 1 force, default adaptive
     // the parts own interleaved rows of the pass (neighbouring rows cost the same, halves of an image do not: with
     // contiguous halves one part of a C2 pass ran alone for its last 8 %)
@@ -1325,7 +1374,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
         unsigned int part_pixels = owned * chunk;
         if (owned && (n_chunks - 1u) % (unsigned int)parts == (unsigned int)i) part_pixels -= n_chunks * chunk - pass_pixels;
         pt.a = a_all;
-        pt.defer = defer_env != 0;
+        pt.defer = defer_env >= 0 ? defer_env != 0 : a_all.post_defer != 0;
         pt.a.work_base = 0;
         pt.a.work_count = part_pixels * (unsigned int)a_all.spp;
         pt.a.wave_part = (unsigned int)i; pt.a.wave_parts = (unsigned int)parts; pt.a.wave_chunk = chunk;
@@ -1371,14 +1420,16 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             if (pt.defer) {
                 wave_post_a_kernel<0, 1><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<0, 2><<<pt.grid_post, 128, 0, st>>>(a, q);
                 wave_post_a_kernel<0, 3><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<0, 4><<<pt.grid_post, 128, 0, st>>>(a, q);
-                wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
+                if (resume) wave_post_a_kernel<4><<<pt.grid_post, 128, 0, st>>>(a, q);
+                else wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
             } else {
                 wave_post_a_kernel<3, 1><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<3, 2><<<pt.grid_post, 128, 0, st>>>(a, q);
                 wave_post_a_kernel<3, 3><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<3, 4><<<pt.grid_post, 128, 0, st>>>(a, q);
             }
         } else if (pt.defer) {
             wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
-            wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
+            if (resume) wave_post_a_kernel<4><<<pt.grid_post, 128, 0, st>>>(a, q);
+            else wave_post_a_kernel<2><<<pt.grid_post, 128, 0, st>>>(a, q);
         } else {
             wave_post_a_kernel<3><<<pt.grid_post, 128, 0, st>>>(a, q);
         }
@@ -1459,7 +1510,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             // after wave_post_b: rays left = listTs + slots waiting for a new sample
             // deferring the iterative solves redoes those slots' walk: it pays while they are few (sparse mixtures: 8 % of the
             // general slots at C2), not when a third of all slots need one (C3, heavy overlap)
-            if (defer_env < 0 && pt.defer && pt.h[WC_SUM_GENERAL] > 4096u && 5ull * pt.h[WC_SUM_DEFERRED] > pt.h[WC_SUM_GENERAL]) pt.defer = false;
+            if (defer_env < 0 && !resume && pt.defer && pt.h[WC_SUM_GENERAL] > 4096u && 5ull * pt.h[WC_SUM_DEFERRED] > pt.h[WC_SUM_GENERAL]) pt.defer = false;
             if (timeline)
                 fprintf(stderr, "[timeline] part %d iter %d t %.3f ms live %u issued %u of %u\n", i, iters,
                         std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tl0).count(), pt.h[WC_NTS], std::min(pt.h[WC_NEXT_SAMPLE], pt.a.work_count), pt.a.work_count);
@@ -1467,7 +1518,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             if (pt.h[WC_NTS] == 0 && (pt.h[WC_NC] == 0 || !more_samples)) pt.done = true;
             // every sample is out and few paths are left: finish them in one kernel instead of ~100 more iterations
             // that are bounded by their own latency (see wave_drain_kernel)
-            else if (drain_on && !more_samples && pt.h[WC_NTS] <= (unsigned int)pt.q.P / drain_div) {
+            else if (drain_on && !more_samples && pt.h[WC_NTS] <= std::min((unsigned int)pt.q.P / drain_div, drain_max)) {
                 { NvtxRange r("vr.wave.drain"); launch_wave_drain(pt.a, pt.q, pt.h[WC_NTS], pt.st); }
                 ++*launches;
                 pt.done = true;

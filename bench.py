@@ -207,7 +207,7 @@ def run_inverse(a, cfg, scene, workload, rank, world, local_rank, steps=None, wa
     for v in my_views:
         ctx.set_camera(cams[v])
         targets[v], _ = ctx.render(rp_full)
-    ctx.sfd_begin(p_start, eps, lr=1e-2)
+    ctx.sfd_begin(p_start, eps, lr=a.lr)
     for v in my_views:
         ctx.sfd_set_target_view(v, targets[v])               # resident: one H2D per view for the whole fit
     sign_rs = np.random.RandomState(4321)      # same stream on every rank: the sign vectors are shared
@@ -266,7 +266,7 @@ def run_inverse(a, cfg, scene, workload, rank, world, local_rank, steps=None, wa
         "metric": "inverse-render iters/sec", "value": 1e3 / ms_per_step, "unit": "iterations/s", "n_gpus": world, "steps": steps,
         "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload, "views": n_views, "image": [W, H], "spp": spp, "S": S, "parameters": D,
+        "config": {"workload": workload, "views": n_views, "image": [W, H], "spp": spp, "S": S, "parameters": D, "lr": a.lr,
                    "partition": f"views round-robin over {world} rank(s)" if n_views >= world else f"rows interleaved over {world} rank(s)",
                    "collective": ("ncclAllReduce(SUM, int64, S*N+2) of the fixed-point F_diff sums per iteration, enqueued by "
                                   "libvolrender_b200.so on the context's stream (vr_sfd_allreduce)") if nccl_in_library else "none (1 rank)",
@@ -293,12 +293,14 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-inverse", action="store_true", help="c2: skip the short C4 (inverse rendering) run reported under 'inverse'")
     ap.add_argument("--inverse-steps", type=int, default=2, help="timed SFD + Adam iterations of that run (after 1 warm-up iteration)")
+    ap.add_argument("--lr", type=float, default=1e-2, help="c4: Adam learning rate (default = the reference's SFDDConfig::lr, inverse_integrator.h:56)")
     ap.add_argument("--engine", type=int, default=0, help="0 wavefront (default), 1 warp-scheduled single kernel")
     ap.add_argument("--wave-slots", type=int, default=0)
     ap.add_argument("--wave-parts", type=int, default=0)
     ap.add_argument("--trav", type=int, default=0, help="traversal kernels of the wavefront engine: 2 (default) wave_trav2_kernel, 1 wave_trav_kernel")
     ap.add_argument("--camera-grid", type=int, default=-1, help="camera rays gathered from the pinhole's direction grid (default 1)")
     ap.add_argument("--post-split", type=int, default=-1, help="wave_post_a: 1 one launch per overlap-count class, 0 one launch for all")
+    ap.add_argument("--post-defer", type=int, default=-1, help="iterative free-flight solves: 0 in place, 1 deferred with the walk redone, 2 deferred and resumed from saved state (default)")
     ap.add_argument("--hierarchy", type=int, default=-1, help="0: hierarchy and light grids built on the device (default), 1: host binned-SAH builder")
     ap.add_argument("--box-kappa", type=float, default=-1.0, help="slack of the culling boxes (vr_bvh.h inflate_boxes), default = the library's")
     ap.add_argument("--light-grid-res", type=int, default=0, help="cells per cube-map face side of the per-light grids (default 256)")
@@ -362,6 +364,8 @@ def main():
         ctx.set_option("trav", a.trav)
     if a.post_split >= 0:
         ctx.set_option("post_split", a.post_split)
+    if a.post_defer >= 0:
+        ctx.set_option("post_defer", a.post_defer)
     if a.camera_grid >= 0:
         ctx.set_option("camera_grid", a.camera_grid)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)

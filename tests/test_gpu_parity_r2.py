@@ -32,6 +32,9 @@ def vr():
 @pytest.fixture(scope="module")
 def ctx(vr):
     c = vr.Context(0)   # raises without a GPU: no fallback
+    for name in ("post_defer", "trav", "camera_grid"):   # VR_TEST_OPT_<name>=v runs the whole file with that option (bisecting a regression)
+        if os.environ.get("VR_TEST_OPT_" + name):
+            c.set_option(name, float(os.environ["VR_TEST_OPT_" + name]))
     yield c
     c.close()
 
@@ -483,7 +486,8 @@ def test_comm_allreduce_is_exact_on_every_path(ctx, vr, ob, golden, scenegen):
 def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scenegen):
     """wave_trav2_kernel (private candidate slots, phases) against wave_trav_kernel (shared queue), the device-built LBVH and
     light grids against the host binned-SAH tree and host grids, camera rays gathered from the pinhole's direction grid
-    (wave_regen_cam_kernel) against camera rays sent through the hierarchy: candidates come in another order and from
+    (wave_regen_cam_kernel) against camera rays sent through the hierarchy, iterative free-flight solves in place / deferred
+    with the walk redone / deferred and resumed from the state saved in the slot: candidates come in another order and from
     another structure, the quadric test decides and the sums are order independent -> images identical bit for bit, with
     and without grids, both integrators, also on the heavy-overlap scene whose rays overflow the per-slot overlap records."""
     cases = [(file_scene(scenegen, "rand2k"), "pin", 96, 64, 16), (file_scene(scenegen, "rand300"), "pin2", 64, 64, 9),
@@ -493,13 +497,14 @@ def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scen
         for scene, cam, W, H, spp in cases:
             for integ in (vr.INTEGRATOR_MS, vr.INTEGRATOR_SS):
                 imgs = []
-                for hier, trav, grid, cgrid, split in ((0, 2, 1, 1, 0), (0, 2, 1, 0, 0), (0, 1, 1, 0, 0), (1, 2, 1, 0, 1), (1, 1, 0, 0, 0), (0, 2, 0, 1, 1)):
+                for hier, trav, grid, cgrid, split, defer in ((0, 2, 1, 1, 0, 2), (0, 2, 1, 0, 0, 1), (0, 1, 1, 0, 0, 0), (1, 2, 1, 0, 1, 2), (1, 1, 0, 0, 0, 1),
+                                                              (0, 2, 0, 1, 1, 0)):
                     ctx.set_option("hierarchy", hier); ctx.set_option("trav", trav); ctx.set_option("light_grid", grid)
-                    ctx.set_option("camera_grid", cgrid); ctx.set_option("post_split", split)
+                    ctx.set_option("camera_grid", cgrid); ctx.set_option("post_split", split); ctx.set_option("post_defer", defer)
                     setup(ctx, ob, scene, cam)
                     img, st = ctx.render(vr.Context.params(integ, W, H, spp))
                     imgs.append(img)
-                    assert np.array_equal(img, imgs[0]), (hier, trav, grid, cgrid, split)
+                    assert np.array_equal(img, imgs[0]), (hier, trav, grid, cgrid, split, defer)
         # the camera inside the mixture: the pinhole sits in a component's box -> no camera grid, same image
         scene = file_scene(scenegen, "rand300")
         oc = ob.make_camera("pinhole", (0.1, 1.0, 2.6), look=(0, 1, 0), fov=0.9)
@@ -516,3 +521,4 @@ def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scen
     finally:
         ctx.set_option("hierarchy", 0); ctx.set_option("trav", 2); ctx.set_option("light_grid", 1); ctx.set_option("light_grid_min_samples", 16e6)
         ctx.set_option("camera_grid", 1); ctx.set_option("camera_grid_min_samples", 2e6); ctx.set_option("post_split", 0)
+        ctx.set_option("post_defer", 2)
