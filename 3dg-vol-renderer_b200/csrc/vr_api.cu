@@ -137,6 +137,7 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "blocks_per_sm")) { ctx->blocks_per_sm_main = std::max(1, (int)value); return VR_OK; }
     if (!strcmp(name, "engine")) { ctx->engine = (int)value; return VR_OK; }
     if (!strcmp(name, "post_split")) { ctx->post_split = (int)value != 0; return VR_OK; }
+    if (!strcmp(name, "post_pair")) { ctx->post_pair = (int)value != 0; return VR_OK; }
     if (!strcmp(name, "post_defer")) { ctx->post_defer = std::max(0, std::min(2, (int)value)); return VR_OK; }
     if (!strcmp(name, "trav")) { const int v = (int)value; ctx->trav_version = (v == 1 || v == 3) ? v : 2; return VR_OK; }   // 3: trav2 except the light-grid walk
     if (!strcmp(name, "hierarchy")) { ctx->hierarchy_builder = (int)value != 0; return VR_OK; }   // 0 device LBVH, 1 host binned SAH; next vr_set_gmm*

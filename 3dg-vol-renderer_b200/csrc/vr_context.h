@@ -105,6 +105,7 @@ struct vr_context {
     int blocks_per_sm_main = 0, blocks_per_sm_arena = 0;
     int engine = 0;                                // 0 wavefront (vr_wave.cu), 1 warp-scheduled single kernel (vr_warp.cuh)
     int wave_slots = 0;                            // 0 = 32768 per SM (sweeps in profiles/r01_tuning.md, r01_v11/)
+    int post_pair = 1;                             // slots with exactly two overlaps walked by the register-only wave_post_a_kernel<5> (needs post_defer 2, post_split 0)
     int post_defer = 2;                            // iterative free-flight solves: 0 in place, 1 deferred (walk redone), 2 deferred and resumed from saved state
     int post_split = 0;                            // wave_post_a_kernel per overlap-count class (vr_wave.cu)
     int trav_version = 2;                          // traversal kernels of the wavefront engine (vr_wave.cu): 2 wave_trav2_kernel, 1 wave_trav_kernel

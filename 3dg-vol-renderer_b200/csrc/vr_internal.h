@@ -17,6 +17,7 @@ struct RenderArgs {
     SceneDev scene;
     CameraPod cam;
     int W, H, spp, nsq;
+    int post_pair;         // wave_post_a: 1 = slots with two overlaps go through the register-only kernel <5>, the rest through <6>
     int post_defer;        // wave_post_a: iterative solves 0 in place, 1 deferred + walk redone (adaptive), 2 deferred + resumed (wave_post_a_kernel<4>)
     int post_split;        // wave_post_a: 1 = one launch per overlap-count class with a store of its size, 0 = one launch for classes 1..4
     int trav_version;      // wavefront traversal kernels: 2 = wave_trav2_kernel (private candidate slots), 1 = wave_trav_kernel

@@ -90,6 +90,7 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     A.trav_version = ctx->trav_version;
     A.post_split = ctx->post_split;
     A.post_defer = ctx->post_defer;
+    A.post_pair = ctx->post_pair;
     A.solver = p->solver;
     A.min_bounces = p->min_bounces;
     A.x0 = p->x0; A.y0 = p->y0; A.win_w = p->x1 - p->x0;

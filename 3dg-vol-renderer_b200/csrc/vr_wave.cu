@@ -991,17 +991,18 @@ template <int MODE, int CLS = -1>
 __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ RenderArgs A, const __grid_constant__ WavePool Q) {
     const SceneDev& S = A.scene;
     constexpr bool FAST = MODE == 1;
+    constexpr bool PAIR = MODE == 5;
     constexpr bool kOneClass = (MODE == 0 || MODE == 3) && CLS > 0;
     constexpr bool kDeferred = MODE == 2 || MODE == 4;
-    constexpr int kFirst = MODE == 1 ? 0 : (kDeferred ? kPostClasses : (kOneClass ? CLS : 1));              // classes [kFirst, kLast)
-    constexpr int kLast = MODE == 1 ? 1 : (kDeferred ? kPostClasses + 1 : (kOneClass ? CLS + 1 : kPostClasses));
+    constexpr int kFirst = MODE == 1 ? 0 : (kDeferred ? kPostClasses : (kOneClass ? CLS : (MODE == 6 ? 2 : 1)));              // classes [kFirst, kLast)
+    constexpr int kLast = MODE == 1 ? 1 : (PAIR ? 2 : (kDeferred ? kPostClasses + 1 : (kOneClass ? CLS + 1 : kPostClasses)));
     constexpr int kStoreCap = !kOneClass ? kWaveCap : (CLS == 1 ? 2 : (CLS == 2 ? 4 : (CLS == 3 ? 8 : kWaveCap)));
     unsigned int nA[kPostClasses + 1], base[kPostClasses + 2];
     base[kFirst] = 0;
 #pragma unroll
     for (int c = kFirst; c < kLast; ++c) { nA[c] = Q.cnt[WC_NA + c]; base[c + 1] = base[c] + ((nA[c] + 31u) & ~31u); }
     const unsigned int total = base[kLast];
-    if ((MODE == 0 || MODE == 3) && (!kOneClass || CLS == 1) && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;
+    if ((MODE == 0 || MODE == 3 || MODE == 6) && (!kOneClass || CLS == 1) && blockIdx.x == 0 && threadIdx.x == 0) Q.cnt[WC_NTS] = 0;
     if (MODE != 1 && blockIdx.x == 0 && threadIdx.x == 0) {   // the host decides from these whether deferring pays (run_wavefront_pass)
         unsigned int sum = 0;
 #pragma unroll
@@ -1018,7 +1019,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
         unsigned int p = 0;
         int cls = kFirst;
 #pragma unroll
-        for (int c = kFirst + 1; c < kLast; ++c) cls += (i >= base[c]) ? 1 : 0;
+        for (int c = kFirst + 1; c < kLast; ++c) cls += (i >= base[c]) ? 1 : 0;   // (no iterations for the one-class kernels)
         unsigned int j = i, nc = nA[kFirst];
 #pragma unroll
         for (int c = kFirst + 1; c < kLast; ++c) if (cls == c) { j = i - base[c]; nc = nA[c]; }
@@ -1078,6 +1079,142 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 } else {
                     hand_over = true;   // untouched: the general kernel redoes it
                 }
+            } else if (PAIR) {
+                // ---- two overlaps, register only: the general walk (free_flight, integrator.h:422-498 / :333-361) written out
+                //      for K = 2.  X = the component entered first, Y = the other; the active list is {X}, {X, Y} (in the
+                //      reference's list order), {the one left}, or, when they do not overlap each other, {X}, {}, {Y}.  The
+                //      same operations in the same order as the general walk; a target that falls where both are active needs
+                //      an iterative solve and is deferred with its state like there; anything unusual goes to the general kernel.
+                if (K == 2 && A.solver <= 1 && target_tau >= 0.0f) {
+                    const uint4 h1 = Q.hit01[kSlotF4 * (size_t)p + 1];
+                    const bool ss = A.integrator == 0;
+                    uint32_t x_gi = h0.w, y_gi = h1.z;
+                    float x_t0 = __uint_as_float(h0.y), x_t1 = __uint_as_float(h0.z), y_t0 = __uint_as_float(h1.x), y_t1 = __uint_as_float(h1.y);
+                    uint32_t x_or = __ldg(S.orig + x_gi), y_or = __ldg(S.orig + y_gi);
+                    unsigned int x_pool = 0u, y_pool = 1u;
+                    if (!((x_t0 != y_t0) ? (x_t0 < y_t0) : (x_or < y_or))) {   // entry order (sort_entries)
+                        uint32_t tu; float tf;
+                        tu = x_gi; x_gi = y_gi; y_gi = tu;  tu = x_or; x_or = y_or; y_or = tu;
+                        tf = x_t0; x_t0 = y_t0; y_t0 = tf;  tf = x_t1; x_t1 = y_t1; y_t1 = tf;
+                        x_pool = 1u; y_pool = 0u;
+                    }
+                    const GaussRec gx = load_gauss(S.gauss, x_gi);
+                    const DepthConst cx = depth_const(gx, ray_quad(gx, o, d));
+                    const GaussRec gy = load_gauss(S.gauss, y_gi);
+                    const DepthConst cy = depth_const(gy, ray_quad(gy, o, d));
+                    VR_COUNT(unsigned int n_erf = 0u;)
+                    double acc = 0.0; float accf = 0.0f;
+                    // what the walk ends with: 0 left the mixture, 1 analytic solve on `sel` in [ta, tb], 2 both active -> deferred
+                    int outcome = 0; int sel = 0; float ta = 0.0f, tb = 0.0f, remaining = 0.0f;
+                    // one segment [t_prev, t_evt] with one active component (constants c, erf at t_prev in *F): true = target inside
+                    auto segment1 = [&](const DepthConst& c, float* F, float t_evt) -> bool {
+                        const float Fn = erff_ni(erf_arg(c, t_evt));
+                        VR_COUNT(++n_erf;)
+                        const float term = __fmul_rn(c.K, __fsub_rn(Fn, *F));
+                        *F = Fn;
+                        if (ss) {
+                            const float seg = __fadd_rn(0.0f, term);
+                            remaining = __fsub_rn(target_tau, accf);
+                            if (__fadd_rn(accf, seg) > target_tau) return true;
+                            accf = __fadd_rn(accf, seg);
+                        } else {
+                            const double seg = __dadd_rn(0.0, (double)term);
+                            remaining = (float)__dsub_rn((double)target_tau, acc);
+                            if (__dadd_rn(acc, seg) > (double)target_tau) return true;
+                            acc = __dadd_rn(acc, seg);
+                        }
+                        return false;
+                    };
+                    // (the empty segment before X enters cannot hold the target: 0 > target_tau is false for target_tau >= 0)
+                    float xF = erff_ni(erf_arg(cx, x_t0)), yF = 0.0f;
+                    VR_COUNT(++n_erf;)
+                    bool take_enter = true;   // next_event: Y's entry against X's exit
+                    if (x_t1 < y_t0) take_enter = false;
+                    else if (x_t1 == y_t0) take_enter = y_or <= x_or;
+                    if (take_enter) {
+                        if (segment1(cx, &xF, y_t0)) { outcome = 1; sel = 0; ta = x_t0; tb = y_t0; }
+                        else {
+                            yF = erff_ni(erf_arg(cy, y_t0));
+                            VR_COUNT(++n_erf;)
+                            // active list: multi scatter appends (X, Y); single scatter keeps ascending original index
+                            const bool x_first = !ss || x_or < y_or;
+                            // earliest exit among the two, scanned in list order (ties: the lower original index)
+                            const float f_t1 = x_first ? x_t1 : y_t1, s_t1 = x_first ? y_t1 : x_t1;
+                            const uint32_t f_or = x_first ? x_or : y_or, s_or = x_first ? y_or : x_or;
+                            const bool second_exits = s_t1 < f_t1 || (s_t1 == f_t1 && s_or < f_or);
+                            const bool x_exits = x_first ? !second_exits : second_exits;
+                            const float t_evt = x_exits ? x_t1 : y_t1;
+                            const float Fxn = erff_ni(erf_arg(cx, t_evt)), Fyn = erff_ni(erf_arg(cy, t_evt));
+                            VR_COUNT(n_erf += 2u;)
+                            const float term_x = __fmul_rn(cx.K, __fsub_rn(Fxn, xF)), term_y = __fmul_rn(cy.K, __fsub_rn(Fyn, yF));
+                            const float term_f = x_first ? term_x : term_y, term_s = x_first ? term_y : term_x;
+                            bool hit;
+                            if (ss) {
+                                const float seg = __fadd_rn(__fadd_rn(0.0f, term_f), term_s);
+                                remaining = __fsub_rn(target_tau, accf);
+                                hit = __fadd_rn(accf, seg) > target_tau;
+                                if (!hit) accf = __fadd_rn(accf, seg);
+                            } else {
+                                const double seg = __dadd_rn(__dadd_rn(0.0, (double)term_f), (double)term_s);
+                                remaining = (float)__dsub_rn((double)target_tau, acc);
+                                hit = __dadd_rn(acc, seg) > (double)target_tau;
+                                if (!hit) acc = __dadd_rn(acc, seg);
+                            }
+                            if (hit) { outcome = 2; sel = x_first ? 0 : 1; ta = y_t0; tb = t_evt; }
+                            else {
+                                xF = Fxn; yF = Fyn;
+                                if (x_exits) { if (segment1(cy, &yF, y_t1)) { outcome = 1; sel = 1; ta = t_evt; tb = y_t1; } }
+                                else         { if (segment1(cx, &xF, x_t1)) { outcome = 1; sel = 0; ta = t_evt; tb = x_t1; } }
+                            }
+                        }
+                    } else {
+                        if (segment1(cx, &xF, x_t1)) { outcome = 1; sel = 0; ta = x_t0; tb = x_t1; }
+                        else {
+                            // (the empty segment [x_t1, y_t0]: acc > target_tau is false, acc + seg was not above it)
+                            yF = erff_ni(erf_arg(cy, y_t0));
+                            VR_COUNT(++n_erf;)
+                            if (segment1(cy, &yF, y_t1)) { outcome = 1; sel = 1; ta = y_t0; tb = y_t1; }
+                        }
+                    }
+                    float t = -1.0f;
+                    bool solved = outcome == 0;
+                    if (outcome == 1) {   // solve_distance with one active component: the analytic inverse (distance_solvers.h:163-171)
+                        const GaussRec& g = sel == 0 ? gx : gy;
+                        float t_an;
+                        VR_COUNT(++cn.sa;)
+                        if (solve_t_given_tau(g, ray_quad(g, o, d), ta, tb, remaining, &t_an)) { t = clampf(t_an, ta, tb); solved = true; }
+                    }
+                    VR_COUNT(cn.erf += n_erf;)
+                    if (solved) {
+                        cn.hits += 2u;
+                        float albedo = 0.0f;
+                        if (t >= 0.0f) {       // evaluate_albedo over the one active component (gmm.h:128-143)
+                            const GaussRec& g = sel == 0 ? gx : gy;
+                            const float mu = gauss_mu_t(g, add3(o, scale3(t, d)));
+                            VR_COUNT(++cn.mu;)
+                            const float a = __fdiv_rn(__fadd_rn(0.0f, __fmul_rn(mu, g.albedo)), __fadd_rn(0.0f, mu));
+                            albedo = a < 0.0f ? 0.0f : (1.0f < a ? 1.0f : a);
+                        }
+                        if (A.record_bits) {  // integrator.h:616-644
+                            int x, y, si;
+                            lane_xy(A, s1.z, &x, &y, &si);
+                            uint32_t* row = A.record_bits + ((size_t)y * A.W + x) * (size_t)A.record_words;
+                            const float tlim = __fadd_rn(t, 1e-6f);
+                            if (t < 0.0f || x_t0 <= tlim) { const uint32_t bit = 1u << (x_or & 31u); if (!(row[x_or >> 5] & bit)) atomicOr(row + (x_or >> 5), bit); }
+                            if (t < 0.0f || y_t0 <= tlim) { const uint32_t bit = 1u << (y_or & 31u); if (!(row[y_or >> 5] & bit)) atomicOr(row + (y_or >> 5), bit); }
+                        }
+                        dest = post_a_finish(A, Q, p, s0, s1, o, d, target_tau, t, albedo, rng, cn);
+                    } else {   // an iterative solve: the state wave_post_a_kernel<4> resumes from (see MODE 0 below)
+                        deferred = true;
+                        unsigned int order, na;
+                        if (outcome == 2) { na = 2u; order = sel == 0 ? (x_pool | (y_pool << 4)) : (y_pool | (x_pool << 4)); }
+                        else { na = 1u; order = sel == 0 ? x_pool : y_pool; }
+                        Q.ps2[kSlotF4 * (size_t)p] = make_float4(__uint_as_float(order), __uint_as_float(0u), 0.f, 0.f);
+                        Q.ps2[kSlotF4 * (size_t)p + 1] = make_float4(ta, tb, remaining, __int_as_float((int)na));
+                    }
+                } else {
+                    hand_over = true;   // untouched: the general kernel does it
+                }
             } else if (MODE == 4) {
                 // ---- resume an iterative solve (distance_solvers.h:25-127) from the saved state: only the active components
                 //      are loaded, in list order; constants and erf(arg(ta)) are recomputed from the same inputs, bit for bit
@@ -1136,7 +1273,7 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
                 }
                 int na = 0;
                 DeferState ds;
-                const float t = free_flight<MODE == 0>(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state, &deferred, &ds);
+                const float t = free_flight<MODE == 0 || MODE == 6>(S, st, K, o, d, target_tau, A.solver, A.integrator == 0, &na, rng.state, &deferred, &ds);
                 if (deferred) {
                     cn.hits -= (unsigned int)K;   // counted when the slot is finished
                     uint64_t order = 0;            // the active list in the reference's order, four bits per entry
@@ -1163,7 +1300,8 @@ __global__ void VR_POSTA_BOUNDS wave_post_a_kernel(const __grid_constant__ Rende
             }
         }
         if (FAST) wave_append(Q.listA + (size_t)1 * Q.P, &Q.cnt[WC_NA + 1], hand_over, p);
-        if (MODE == 0) wave_append(Q.listA + (size_t)kPostClasses * Q.P, &Q.cnt[WC_NA + kPostClasses], deferred, p);
+        if (PAIR) wave_append(Q.listA + (size_t)2 * Q.P, &Q.cnt[WC_NA + 2], hand_over, p);
+        if (MODE == 0 || MODE == 6 || PAIR) wave_append(Q.listA + (size_t)kPostClasses * Q.P, &Q.cnt[WC_NA + kPostClasses], deferred, p);
         wave_append(Q.listTh, &Q.cnt[WC_NTH], dest == DEST_TRAV, p);
         wave_append(Q.listTl, &Q.cnt[WC_NTL], dest == DEST_TRAV_LIGHT, p);
         wave_append(Q.listC, &Q.cnt[WC_NC], dest == DEST_REGEN, p);
@@ -1338,6 +1476,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
     });
     const bool t2 = a_all.trav_version != 1;
     const bool post_split = a_all.post_split != 0;
+    const bool pair = a_all.post_defer == 2 && a_all.post_pair != 0 && a_all.post_split == 0;
     const bool resume = a_all.post_defer == 2;   // deferred solves resumed from the state in the slot (no second walk)
     const int bps_s = occ[t2 ? 1 : 0][0], bps_h = occ[t2 ? 1 : 0][1], bps_l = occ[t2 ? 1 : 0][2];
     const char* prof_env = getenv("VR_WAVE_PROFILE");
@@ -1426,6 +1565,10 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
                 wave_post_a_kernel<3, 1><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<3, 2><<<pt.grid_post, 128, 0, st>>>(a, q);
                 wave_post_a_kernel<3, 3><<<pt.grid_post, 128, 0, st>>>(a, q); wave_post_a_kernel<3, 4><<<pt.grid_post, 128, 0, st>>>(a, q);
             }
+        } else if (pt.defer && pair) {
+            wave_post_a_kernel<5><<<pt.grid_post, 128, 0, st>>>(a, q);   // two overlaps, register only
+            wave_post_a_kernel<6><<<pt.grid_post, 128, 0, st>>>(a, q);   // three and more, and what the first two kernels handed over
+            wave_post_a_kernel<4><<<pt.grid_post, 128, 0, st>>>(a, q);
         } else if (pt.defer) {
             wave_post_a_kernel<0><<<pt.grid_post, 128, 0, st>>>(a, q);
             if (resume) wave_post_a_kernel<4><<<pt.grid_post, 128, 0, st>>>(a, q);
@@ -1466,7 +1609,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             Part& pt = part[i];
             if (pt.done) continue;
             any = true;
-            const unsigned int per_iter = 6u + (pt.defer ? 1u : 0u) + (pt.a.scene.lg_mask ? 1u : 0u) + (post_split ? 3u : 0u);
+            const unsigned int per_iter = 6u + (pt.defer ? 1u : 0u) + (pt.defer && pair ? 1u : 0u) + (pt.a.scene.lg_mask ? 1u : 0u) + (post_split ? 3u : 0u);
             if (use_graph) {
                 WaveGraphCache::Entry& en = graphs->e[i][pt.defer ? 1 : 0];
                 WaveGraphKey key;

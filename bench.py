@@ -300,6 +300,7 @@ def main():
     ap.add_argument("--trav", type=int, default=0, help="traversal kernels of the wavefront engine: 2 (default) wave_trav2_kernel, 1 wave_trav_kernel")
     ap.add_argument("--camera-grid", type=int, default=-1, help="camera rays gathered from the pinhole's direction grid (default 1)")
     ap.add_argument("--post-split", type=int, default=-1, help="wave_post_a: 1 one launch per overlap-count class, 0 one launch for all")
+    ap.add_argument("--post-pair", type=int, default=-1, help="slots with exactly two overlaps: 1 register-only kernel (default), 0 the general walk")
     ap.add_argument("--post-defer", type=int, default=-1, help="iterative free-flight solves: 0 in place, 1 deferred with the walk redone, 2 deferred and resumed from saved state (default)")
     ap.add_argument("--hierarchy", type=int, default=-1, help="0: hierarchy and light grids built on the device (default), 1: host binned-SAH builder")
     ap.add_argument("--box-kappa", type=float, default=-1.0, help="slack of the culling boxes (vr_bvh.h inflate_boxes), default = the library's")
@@ -366,6 +367,8 @@ def main():
         ctx.set_option("post_split", a.post_split)
     if a.post_defer >= 0:
         ctx.set_option("post_defer", a.post_defer)
+    if a.post_pair >= 0:
+        ctx.set_option("post_pair", a.post_pair)
     if a.camera_grid >= 0:
         ctx.set_option("camera_grid", a.camera_grid)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)
