@@ -28,7 +28,7 @@ STATUS = {0: "VR_OK", 1: "VR_ERR_INVALID_ARGUMENT", 2: "VR_ERR_CUDA", 3: "VR_ERR
 # every symbol include/volrender.h declares (tests/test_cabi.py checks the header against this and the .so)
 SYMBOLS = ["vr_create", "vr_destroy", "vr_last_error", "vr_version", "vr_device_count", "vr_stream", "vr_set_gmm",
            "vr_set_gmm_params", "vr_set_smm", "vr_set_lights", "vr_set_camera", "vr_render", "vr_render_device",
-           "vr_image_dev", "vr_get_recorded", "vr_get_samples", "vr_transmittance", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
+           "vr_image_dev", "vr_get_recorded", "vr_get_samples", "vr_transmittance", "vr_transmittance_noalloc", "vr_transmittance_noalloc_max_rays", "vr_sfd_begin", "vr_sfd_set_target", "vr_sfd_fdiff",
            "vr_sfd_set_target_view", "vr_sfd_select_view", "vr_sfd_apply", "vr_sfd_reset_fdiff", "vr_sfd_accumulate", "vr_sfd_read", "vr_sfd_fdiff_dev", "vr_comm_available", "vr_comm_version",
            "vr_comm_unique_id", "vr_comm_init_rank", "vr_comm_init_all", "vr_comm_destroy", "vr_comm_size", "vr_sfd_allreduce", "vr_sfd_allreduce_all",
            "vr_sfd_get_params", "vr_sfd_get_state", "vr_sfd_set_state", "vr_adam_step", "vr_unpack_params", "vr_set_option", "vr_kat_pcg", "vr_kat_gaussian",
@@ -99,6 +99,8 @@ def lib(path: str | None = None):
     L.vr_get_recorded.argtypes = [vp, fp, fp, ci]
     L.vr_get_samples.argtypes = [vp, fp, C.c_uint64]
     L.vr_transmittance.argtypes = [vp, ci, fp, fp, fp, fp]
+    L.vr_transmittance_noalloc.argtypes = [vp, ci, fp, fp, fp, fp]
+    L.vr_transmittance_noalloc_max_rays.argtypes = []
     L.vr_sfd_begin.argtypes = [vp, ci, fp, fp, C.c_float, C.c_float, C.c_float, C.c_float]
     L.vr_sfd_set_target.argtypes = [vp, ci, ci, fp]
     L.vr_sfd_set_target_view.argtypes = [vp, ci, ci, ci, fp]
@@ -268,6 +270,17 @@ class Context:
         out = np.empty(tmax.shape[0], np.float32)
         self._ck(self.L.vr_transmittance(self.h, tmax.shape[0], _ptr(o), _ptr(d), _ptr(tmax), _ptr(out)))
         return out
+
+    def transmittance_noalloc(self, o, d, tmax):
+        """vr_transmittance_noalloc: the same kernel with the rays staged in the library's fixed device array (at most
+        noalloc_max_rays() rays, no cudaMalloc inside the call; calls that overlap on one GPU race)"""
+        o, d, tmax = _f32(o), _f32(d), _f32(tmax)
+        out = np.empty(tmax.shape[0], np.float32)
+        self._ck(self.L.vr_transmittance_noalloc(self.h, tmax.shape[0], _ptr(o), _ptr(d), _ptr(tmax), _ptr(out)))
+        return out
+
+    def noalloc_max_rays(self) -> int:
+        return int(self.L.vr_transmittance_noalloc_max_rays())
 
     # ---- inverse
     def sfd_begin(self, params, eps, lr=1e-2, beta1=0.9, beta2=0.999, adam_eps=1e-8):

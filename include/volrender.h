@@ -139,6 +139,22 @@ int vr_get_samples(vr_context* ctx, float* out4, uint64_t count);
  * directions must be unit length (the Ray ctor normalises, ray.h:11-12) */
 int vr_transmittance(vr_context* ctx, int nrays, const float* o3, const float* d3, const float* tmax, float* out);
 
+/* ---- vr_transmittance for callers that cannot call cudaMalloc --------------------------------
+ * No counterpart in the reference: added (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid allocation).  Same arguments, same kernel and same
+ * results as vr_transmittance, but the rays and results are staged in a fixed file-scope device array
+ * (32 bytes per ray, VR_NOALLOC_MAX_RAYS rays = 2 MiB held by every GPU that loads the library) instead
+ * of the context's growing scratch buffer: the call performs no cudaMalloc / cudaFree and no allocating
+ * library routine.  nrays > VR_NOALLOC_MAX_RAYS -> VR_ERR_INVALID_ARGUMENT; a batch whose origins lie
+ * farther out than the culling hierarchy was built for -> VR_ERR_UNSUPPORTED (vr_transmittance would
+ * rebuild, which allocates).  All calls on one GPU share the array: calls that overlap on the GPU race;
+ * nothing in it needs clearing between calls (every byte read was written by the same call).
+ * The first call on a device resolves the array's address (and, under lazy module loading, is when the
+ * driver materialises the array there): make one warm-up call at set-up.  csrc/vr_noalloc.cu. */
+#define VR_NOALLOC_MAX_RAYS 65536
+int vr_transmittance_noalloc(vr_context* ctx, int nrays, const float* o3, const float* d3, const float* tmax, float* out);
+int vr_transmittance_noalloc_max_rays(void);
+
 /* ---- inverse path: inverse_integrator.h:67-241, optimizer.h:30-41 ---------------------------
  * vr_sfd_begin: uploads the target image (3*W*H floats) and the packed parameters, resets Adam.
  * vr_sfd_fdiff: for the CURRENT parameters renders the base image and S perturbed images
