@@ -25,6 +25,9 @@ vr::SceneDev vr_context::scene_dev() const {
     S.lg_res = lg_res; S.lg_mask = lg_valid ? lg_mask : 0u;
     S.cg_start = cg_start.as<uint32_t>(); S.cg_gi = cg_gi.as<uint32_t>(); S.cg_dmin = cg_dmin.as<float>();
     S.cg_res = 0;   // switched on per render (vr_render.cu) when the grid is valid for this camera
+    S.g3_start = g3_start.as<uint32_t>(); S.g3_gi = g3_gi.as<uint32_t>();
+    for (int k = 0; k < 3; ++k) { S.g3_org[k] = g3_org[k]; S.g3_inv[k] = g3_inv[k]; S.g3_cell[k] = g3_cell[k]; }
+    S.g3_res = 0;   // switched on per render
     S.orig = perm.as<uint32_t>();
     S.n = n;
     S.nl = nl;
@@ -111,7 +114,7 @@ void vr_destroy(vr_context* ctx) {
     ctx->comm_scratch.release();
     for (DevBuf* b : {&ctx->mean3, &ctx->cov6, &ctx->density, &ctx->albedo, &ctx->gauss_orig, &ctx->gauss_leaf, &ctx->nodes,
                       &ctx->perm, &ctx->leaf_of_orig, &ctx->box_lo, &ctx->box_hi, &ctx->lam, &ctx->qnodes, &ctx->lg_start, &ctx->lg_gi,
-                      &ctx->lg_dmin, &ctx->lg_scratch, &ctx->cg_start, &ctx->cg_gi, &ctx->cg_dmin, &ctx->spheres, &ctx->lpos, &ctx->lint,
+                      &ctx->lg_dmin, &ctx->lg_scratch, &ctx->cg_start, &ctx->cg_gi, &ctx->cg_dmin, &ctx->g3_start, &ctx->g3_gi, &ctx->g3_cursor, &ctx->spheres, &ctx->lpos, &ctx->lint,
                       &ctx->image, &ctx->sampleL, &ctx->counters, &ctx->stats, &ctx->overflow_list, &ctx->arena,
                       &ctx->record_bits, &ctx->scratch, &ctx->wavepool})
         b->release();
@@ -144,6 +147,9 @@ int vr_set_option(vr_context* ctx, const char* name, double value) {
     if (!strcmp(name, "box_kappa")) { ctx->box_kappa = std::max(0.0, value); return VR_OK; }   // takes effect at the next vr_set_gmm*
     if (!strcmp(name, "light_grid")) { vr::cancel_light_grid_job(ctx); ctx->use_light_grid = (int)value != 0; ctx->lg_valid = false; return VR_OK; }
     if (!strcmp(name, "light_grid_min_samples")) { ctx->light_grid_min_samples = value; return VR_OK; }
+    if (!strcmp(name, "grid3d")) { ctx->use_grid3d = (int)value != 0; return VR_OK; }
+    if (!strcmp(name, "grid3d_min_samples")) { ctx->grid3d_min_samples = value; return VR_OK; }
+    if (!strcmp(name, "grid3d_res")) { ctx->g3_res_option = std::max(0, (int)value); ctx->g3_valid = false; return VR_OK; }
     if (!strcmp(name, "camera_grid")) { ctx->use_camera_grid = (int)value != 0; return VR_OK; }
     if (!strcmp(name, "camera_grid_min_samples")) { ctx->camera_grid_min_samples = value; return VR_OK; }
     if (!strcmp(name, "light_grid_res")) { ctx->cg_valid = false; vr::cancel_light_grid_job(ctx); ctx->lg_res = std::min(1024, std::max(8, (int)value)); ctx->lg_valid = false; return VR_OK; }
@@ -262,6 +268,7 @@ int set_gmm_from_device(vr_context* ctx, int n, const float* reach_RX) {
     ctx->rec_valid = false;
     ctx->lg_valid = false;
     ctx->cg_valid = false;
+    ctx->g3_valid = false;
     ctx->h_box_lo.clear(); ctx->h_box_hi.clear(); ctx->h_leaf_of_orig.clear();
     const size_t m = (size_t)std::max(n, 1);
     VR_CUDA(ctx->gauss_orig.ensure(m * 48)); VR_CUDA(ctx->gauss_leaf.ensure(m * 48));
@@ -360,6 +367,17 @@ int ensure_camera_grid(vr_context* ctx) {
     if (rc) return rc;
     memcpy(ctx->cg_pinhole, ctx->cam.pinhole, sizeof(float) * 3);
     ctx->cg_valid = true;
+    return VR_OK;
+}
+
+// uniform grid over the mixture for the bounce rays' first stretch: (re)built when the mixture changed; device builder only
+int ensure_grid3d(vr_context* ctx) {
+    if (ctx->hierarchy_builder != 0 || ctx->n <= 0) { ctx->g3_ok = false; return VR_OK; }
+    if (ctx->g3_valid) return VR_OK;
+    NvtxRange range("vr.grid3d");
+    int rc = build_grid3d_device(ctx);
+    if (rc) return rc;
+    ctx->g3_valid = true;
     return VR_OK;
 }
 

@@ -66,6 +66,13 @@ struct vr_context {
     vr::DevBuf lg_start, lg_gi, lg_dmin, lg_scratch;
     // direction grid around the pinhole of the camera: candidate lists of the camera rays (vr_lightgrid_dev.cu, wave_regen_kernel)
     vr::DevBuf cg_start, cg_gi, cg_dmin;
+    vr::DevBuf g3_start, g3_gi, g3_cursor;         // uniform grid over the mixture (vr_grid3d.cu)
+    bool g3_valid = false, g3_ok = false;          // built for the current mixture / usable
+    int g3_res = 0, g3_res_option = 0;             // cells per axis (option "grid3d_res": 0 = from the component count)
+    unsigned long long g3_entries = 0;
+    float g3_org[3] = {0.f, 0.f, 0.f}, g3_inv[3] = {0.f, 0.f, 0.f}, g3_cell[3] = {0.f, 0.f, 0.f};
+    bool use_grid3d = true;                        // option "grid3d"
+    double grid3d_min_samples = 2e6;
     bool cg_valid = false, cg_ok = false;          // built for the current mixture + camera / usable (pinhole not inside a component)
     float cg_pinhole[3] = {0.f, 0.f, 0.f};
     int use_camera_grid = 1;
@@ -131,6 +138,8 @@ int set_gmm_from_device(vr_context* c, int n, const float* reach_RX = nullptr); 
 int build_hierarchy_device(vr_context* c, int n, const float* reach_RX);          // vr_lbvh.cu
 int build_light_grids_device(vr_context* c);      // vr_lightgrid_dev.cu
 int build_camera_grid_device(vr_context* c);      // vr_lightgrid_dev.cu
+int build_grid3d_device(vr_context* c);           // vr_grid3d.cu
+int ensure_grid3d(vr_context* c);
 int ensure_camera_grid(vr_context* c);            // vr_api.cu
 int fetch_host_boxes(vr_context* c);               // vr_api.cu: inflated boxes + leaf order on the host (light-grid builder)
 int ensure_reach(vr_context* c, float R, float X);   // rebuilds the hierarchy when it was inflated for a smaller reach

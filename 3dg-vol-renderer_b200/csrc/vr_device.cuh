@@ -21,6 +21,11 @@ struct SceneDev {
     const uint32_t* cg_gi;
     const float* cg_dmin;
     int cg_res;
+    // uniform grid over the mixture (vr_grid3d.cu): candidates of the first stretch of a bounce ray; g3_res = 0: none
+    const uint32_t* g3_start;
+    const uint32_t* g3_gi;
+    float g3_org[3], g3_inv[3], g3_cell[3];
+    int g3_res;
     const uint32_t* orig;   // leaf order -> original index
     int n;
     int nl;
@@ -320,6 +325,7 @@ struct DeferState { float ta, tb, remaining; };
 template <bool DEFER, class St>
 __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, float ta, float tb, float remaining,
                                 int solver, uint64_t key, bool* deferred, DeferState* ds = nullptr) {  // :150-187
+    if (ds) { ds->ta = ta; ds->tb = tb; ds->remaining = remaining; }   // the segment the walk ended in (also read by post_a_certified)
     if (solver == 4) {  // UNIFORM (:131-137): t = ta + u (tb - ta); the reference's u comes from a random_device-seeded
                         // generator (parity unpinned), ours is hashed from the path's PCG state after the target draw,
                         // like the oracle's solve_uniform
@@ -334,11 +340,7 @@ __device__ float solve_distance(const SceneDev& S, St& st, int na, f3 o, f3 d, f
         VR_COUNT(++st.n_sa;)
         if (solve_t_given_tau(g, q, ta, tb, remaining, &t_an)) return clampf(t_an, ta, tb);
     }
-    if (DEFER) {
-        *deferred = true;
-        if (ds) { ds->ta = ta; ds->tb = tb; ds->remaining = remaining; }
-        return ta;
-    }
+    if (DEFER) { *deferred = true; return ta; }
     if (solver == 0 || solver == 2) return solve_newton(st, na, ta, tb, remaining);
     return solve_bisection(st, na, ta, tb, remaining);
 }

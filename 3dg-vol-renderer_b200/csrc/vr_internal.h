@@ -60,9 +60,9 @@ constexpr int kWaveCap = 16;         // free-flight overlaps kept per path slot 
 constexpr int kPostClasses = 5;
 enum { WC_NTS = 0, WC_NTH, WC_NB, WC_NC, WC_NEXT_SAMPLE, WC_CURSOR_S, WC_CURSOR_H, WC_TICKET, WC_NTL, WC_CURSOR_L,
        WC_NA /* kPostClasses + 1 counters */,
-       WC_SUM_GENERAL = WC_NA + kPostClasses + 1, WC_SUM_DEFERRED,   // running totals of the pass (general-kernel slots, deferred slots)
+       WC_SUM_GENERAL = WC_NA + kPostClasses + 1, WC_SUM_DEFERRED, WC_TICKET_S,   // running totals of the pass (general-kernel slots, deferred slots)
        kWaveCounters = 24 };
-static_assert(WC_SUM_DEFERRED < kWaveCounters, "wave counters overflow");
+static_assert(WC_TICKET_S < kWaveCounters, "wave counters overflow");
 constexpr int kSlotF4 = 8;           // float4s per slot record
 struct WavePool {
     int P;

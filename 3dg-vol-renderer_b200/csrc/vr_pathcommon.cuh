@@ -6,6 +6,7 @@ namespace vr {
 
 constexpr int kMaxLeafDev = 1;                 // == vr::kMaxLeaf of the host builder (vr_bvh.h)
 enum { RAY_SCATTER = 0, RAY_SHADOW = 1, RAY_LIGHT = 2 };   // RAY_LIGHT: shadow ray to a point light with a direction grid
+constexpr int kRayNoGrid = 0x100;   // flag on a RAY_SCATTER kind: gather through the hierarchy, not the uniform grid (wave_post_a sent the slot back)
 
 __device__ __forceinline__ void lane_xy(const RenderArgs& A, unsigned int work, int* x, int* y, int* si) {
     const unsigned int p = A.pixel_base + work / (unsigned int)A.spp;

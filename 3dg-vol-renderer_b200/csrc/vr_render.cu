@@ -78,9 +78,14 @@ int render_device_impl(vr_context* ctx, const vr_render_params* p, vr_render_sta
     const bool want_cam_grid = ctx->engine == 0 && ctx->use_camera_grid && ctx->trav_version != 1 && ctx->cam.kind == VR_CAMERA_PINHOLE &&
                                (double)render_samples >= ctx->camera_grid_min_samples;
     if (want_cam_grid) { rc = ensure_camera_grid(ctx); if (rc) return rc; }
+    // bounce rays take the candidates of their first stretch from a uniform grid over the mixture (vr_grid3d.cu)
+    const bool want_grid3d = ctx->engine == 0 && ctx->use_grid3d && ctx->trav_version == 2 && p->integrator == VR_INTEGRATOR_MULTI_SCATTER &&
+                             (double)render_samples >= ctx->grid3d_min_samples;
+    if (want_grid3d) { rc = ensure_grid3d(ctx); if (rc) return rc; }
     RenderArgs A{};
     A.scene = ctx->scene_dev();
     if (!use_grids) A.scene.lg_mask = 0;
+    if (want_grid3d && ctx->g3_valid && ctx->g3_ok) A.scene.g3_res = ctx->g3_res;
     if (want_cam_grid && ctx->cg_valid && ctx->cg_ok) A.scene.cg_res = ctx->lg_res;
     A.cam = ctx->cam;
     A.W = W; A.H = H; A.spp = p->spp;

@@ -300,6 +300,9 @@ def main():
     ap.add_argument("--trav", type=int, default=0, help="traversal kernels of the wavefront engine: 2 (default) wave_trav2_kernel, 1 wave_trav_kernel")
     ap.add_argument("--camera-grid", type=int, default=-1, help="camera rays gathered from the pinhole's direction grid (default 1)")
     ap.add_argument("--post-split", type=int, default=-1, help="wave_post_a: 1 one launch per overlap-count class, 0 one launch for all")
+    ap.add_argument("--light-grid", type=int, default=-1, help="per-light direction grids for the shadow rays (default 1)")
+    ap.add_argument("--grid3d", type=int, default=-1, help="1 (default): bounce rays take the candidates of their first stretch from a uniform grid over the mixture")
+    ap.add_argument("--grid3d-res", type=int, default=0, help="cells per axis of that grid (default: from the component count, 32..128)")
     ap.add_argument("--post-pair", type=int, default=-1, help="slots with exactly two overlaps: 1 register-only kernel (default), 0 the general walk")
     ap.add_argument("--post-defer", type=int, default=-1, help="iterative free-flight solves: 0 in place, 1 deferred with the walk redone, 2 deferred and resumed from saved state (default)")
     ap.add_argument("--hierarchy", type=int, default=-1, help="0: hierarchy and light grids built on the device (default), 1: host binned-SAH builder")
@@ -369,6 +372,12 @@ def main():
         ctx.set_option("post_defer", a.post_defer)
     if a.post_pair >= 0:
         ctx.set_option("post_pair", a.post_pair)
+    if a.light_grid >= 0:
+        ctx.set_option("light_grid", a.light_grid)
+    if a.grid3d >= 0:
+        ctx.set_option("grid3d", a.grid3d)
+    if a.grid3d_res > 0:
+        ctx.set_option("grid3d_res", a.grid3d_res)
     if a.camera_grid >= 0:
         ctx.set_option("camera_grid", a.camera_grid)
     cam = vr.camera_basis("pinhole", (0, 1, 6), look=(0, 1, 0), fov=0.78539816339)

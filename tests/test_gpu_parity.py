@@ -31,7 +31,7 @@ def vr():
 @pytest.fixture(scope="module")
 def ctx(vr):
     c = vr.Context(0)   # raises without a GPU: no fallback
-    for name in ("post_defer", "post_pair", "trav", "camera_grid"):   # VR_TEST_OPT_<name>=v runs the whole file with that option (bisecting a regression)
+    for name in ("post_defer", "post_pair", "trav", "camera_grid", "grid3d", "grid3d_res", "grid3d_min_samples"):   # VR_TEST_OPT_<name>=v runs the whole file with that option (bisecting a regression)
         if os.environ.get("VR_TEST_OPT_" + name):
             c.set_option(name, float(os.environ["VR_TEST_OPT_" + name]))
     yield c

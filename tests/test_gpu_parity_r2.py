@@ -32,7 +32,7 @@ def vr():
 @pytest.fixture(scope="module")
 def ctx(vr):
     c = vr.Context(0)   # raises without a GPU: no fallback
-    for name in ("post_defer", "post_pair", "trav", "camera_grid"):   # VR_TEST_OPT_<name>=v runs the whole file with that option (bisecting a regression)
+    for name in ("post_defer", "post_pair", "trav", "camera_grid", "grid3d", "grid3d_res", "grid3d_min_samples"):   # VR_TEST_OPT_<name>=v runs the whole file with that option (bisecting a regression)
         if os.environ.get("VR_TEST_OPT_" + name):
             c.set_option(name, float(os.environ["VR_TEST_OPT_" + name]))
     yield c
@@ -497,25 +497,28 @@ def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scen
     light grids against the host binned-SAH tree and host grids, camera rays gathered from the pinhole's direction grid
     (wave_regen_cam_kernel) against camera rays sent through the hierarchy, iterative free-flight solves in place / deferred
     with the walk redone / deferred and resumed from the state saved in the slot, slots with two overlaps walked by the
-    register-only kernel or by the general one: candidates come in another order and from
+    register-only kernel or by the general one, bounce rays that start in the uniform grid over the mixture (coarse, default and
+    fine cells) or at the hierarchy's root: candidates come in another order and from
     another structure, the quadric test decides and the sums are order independent -> images identical bit for bit, with
     and without grids, both integrators, also on the heavy-overlap scene whose rays overflow the per-slot overlap records."""
     cases = [(file_scene(scenegen, "rand2k"), "pin", 96, 64, 16), (file_scene(scenegen, "rand300"), "pin2", 64, 64, 9),
              (scenegen.generate(3000, 11, nonuniform=True, diameter_range=(0.02, 0.09)), "pin", 128, 96, 16)]
-    ctx.set_option("light_grid_min_samples", 0); ctx.set_option("camera_grid_min_samples", 0)
+    ctx.set_option("light_grid_min_samples", 0); ctx.set_option("camera_grid_min_samples", 0); ctx.set_option("grid3d_min_samples", 0)
     try:
         for scene, cam, W, H, spp in cases:
             for integ in (vr.INTEGRATOR_MS, vr.INTEGRATOR_SS):
                 imgs = []
-                for hier, trav, grid, cgrid, split, defer, pair in ((0, 2, 1, 1, 0, 2, 1), (0, 2, 1, 1, 0, 2, 0), (0, 2, 1, 0, 0, 1, 0), (0, 1, 1, 0, 0, 0, 0),
-                                                                    (1, 2, 1, 0, 1, 2, 0), (1, 1, 0, 0, 0, 1, 0), (0, 2, 0, 1, 1, 0, 0), (1, 1, 0, 0, 0, 2, 1)):
+                # hierarchy builder, traversal kernels, light grids, camera grid, post_split, post_defer, post_pair, grid3d (+ its resolution)
+                for hier, trav, grid, cgrid, split, defer, pair, g3, g3res in (
+                        (0, 2, 1, 1, 0, 2, 1, 0, 0), (0, 2, 1, 1, 0, 2, 1, 1, 0), (0, 2, 1, 1, 0, 2, 0, 1, 16), (0, 2, 1, 0, 0, 1, 0, 1, 200), (0, 1, 1, 0, 0, 0, 0, 0, 0),
+                        (1, 2, 1, 0, 1, 2, 0, 1, 0), (1, 1, 0, 0, 0, 1, 0, 0, 0), (0, 2, 0, 1, 1, 0, 0, 1, 64), (1, 1, 0, 0, 0, 2, 1, 0, 0), (0, 2, 0, 0, 0, 0, 1, 1, 8)):
                     ctx.set_option("hierarchy", hier); ctx.set_option("trav", trav); ctx.set_option("light_grid", grid)
                     ctx.set_option("camera_grid", cgrid); ctx.set_option("post_split", split); ctx.set_option("post_defer", defer)
-                    ctx.set_option("post_pair", pair)
+                    ctx.set_option("post_pair", pair); ctx.set_option("grid3d", g3); ctx.set_option("grid3d_res", g3res)
                     setup(ctx, ob, scene, cam)
                     img, st = ctx.render(vr.Context.params(integ, W, H, spp))
                     imgs.append(img)
-                    assert np.array_equal(img, imgs[0]), (hier, trav, grid, cgrid, split, defer, pair)
+                    assert np.array_equal(img, imgs[0]), (hier, trav, grid, cgrid, split, defer, pair, g3, g3res)
         # the camera inside the mixture: the pinhole sits in a component's box -> no camera grid, same image
         scene = file_scene(scenegen, "rand300")
         oc = ob.make_camera("pinhole", (0.1, 1.0, 2.6), look=(0, 1, 0), fov=0.9)
@@ -533,3 +536,23 @@ def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scen
         ctx.set_option("hierarchy", 0); ctx.set_option("trav", 2); ctx.set_option("light_grid", 1); ctx.set_option("light_grid_min_samples", 16e6)
         ctx.set_option("camera_grid", 1); ctx.set_option("camera_grid_min_samples", 2e6); ctx.set_option("post_split", 0)
         ctx.set_option("post_defer", 2); ctx.set_option("post_pair", 1)
+        ctx.set_option("grid3d", 1); ctx.set_option("grid3d_res", 0); ctx.set_option("grid3d_min_samples", 2e6)
+
+
+def test_uniform_grid_changes_no_bit_at_full_size(ctx, ob, vr, scenegen):
+    """The uniform grid over the mixture (vr_grid3d.cu) gives a bounce ray the overlaps that enter before it leaves its origin's
+    cell, with a certificate; wave_post_a accepts a result only if the reference's walk could not have looked beyond the
+    certificate, and sends the slot back to the hierarchy otherwise.  If that reasoning had a hole, some of the ~10^9 bounce rays
+    of a full-size image would show it: config C2 at its full 1024^2 x 256 spp and config C3 (200 000 components) at 2048^2 x 16
+    spp, with and without the grid -- every pixel bit for bit."""
+    for name, W, H, spp in (("c2", 1024, 1024, 256), ("c3", 2048, 2048, 16)):
+        scene = big_scene(scenegen, name)
+        setup(ctx, ob, scene, "pin")
+        imgs = []
+        for g3 in (1, 0):
+            ctx.set_option("grid3d", g3)
+            img, st = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, W, H, spp))
+            imgs.append(img)
+            print(f"{name} grid3d {g3}: {st['samples']} samples, {st['scatter_rays']} free-flight rays, {st['hits']} overlaps kept, {st['kernel_ms']:.1f} ms")
+        ctx.set_option("grid3d", 1)
+        assert np.array_equal(imgs[0], imgs[1]), name
