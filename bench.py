@@ -38,11 +38,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ENV = (0.53, 0.81, 0.92)
-# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, wave_trav2_kernel<0> (free-flight
-# traversal, 27 % of a step): 285.7 + 73.5 MB for one part's wave -- half of the 4.85 M-slot pool -- with the pool full,
-# profiles/r02/ncu_final_c2_wave_kernels.md (ncu --set full of this command at 64 spp, caches flushed between replays;
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, wave_trav2_kernel<0, true> (free-flight
+# traversal, 24.5 % of a step): 286.9 + 78.0 MB for one part's wave -- half of the 4.85 M-slot pool -- with the pool full,
+# profiles/r02/ncu_head_c2_wave_kernels.md (ncu --set full of this command at 64 spp, caches flushed between replays;
 # only meaningful for the C2 workload it was captured on; round 1's wave_trav_kernel<0>: 424.5 MB)
-DOMINANT_KERNEL_DRAM_BYTES = 359.2e6
+DOMINANT_KERNEL_DRAM_BYTES = 364.9e6
 CONFIGS = {
     # name: (n_gaussians, seed, nonuniform, W, H, spp, integrator)
     "c1": dict(n=1000, seed=1, nonuniform=False, W=512, H=512, spp=64, integrator="ss",
