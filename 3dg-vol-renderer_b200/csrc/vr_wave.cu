@@ -494,9 +494,10 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
 // Candidates, tests and sums are the same as wave_trav_kernel's (test_trav2_equals_trav: bit-identical images).
 // ------------------------------------------------------------------------------------------
 // leave the node loop when this many lanes do not traverse; sweep at C2 (profiles/r02/trav2_threshold_sweep.md):
-// 4 -> 229, 8 -> 268, 12 -> 279, 16 -> 289, 24 -> 288 Msamples/s
+// 4 -> 229, 8 -> 268, 12 -> 279, 16 -> 289, 24 -> 288 Msamples/s; with the uniform grid (lanes in a grid cell stop after a
+// round or two): 12 -> 373.4, 16 -> 378.5, 20 -> 379.2, 24 -> 378.7, and 20 with a fetch threshold of 16 -> 382.5
 #ifndef VR_T2_IDLE_S
-#define VR_T2_IDLE_S 16
+#define VR_T2_IDLE_S 20
 #endif
 #ifndef VR_T2_IDLE_H
 #define VR_T2_IDLE_H 16
@@ -507,7 +508,7 @@ __global__ void VR_TRAV_BOUNDS wave_trav_kernel(const __grid_constant__ RenderAr
 // finished rays are flushed (result to the slot, slot to a work list: up to six warp-aggregated appends) and their lanes
 // refilled once this many wait -- or nothing traverses any more
 #ifndef VR_T2_FETCH_S
-#define VR_T2_FETCH_S 12
+#define VR_T2_FETCH_S 16   // (with the uniform grid: 8 -> 371.8, 12 -> 378.5, 16 -> 379.9)
 #endif
 #ifndef VR_T2_FETCH_H
 #define VR_T2_FETCH_H 12
