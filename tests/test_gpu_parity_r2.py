@@ -519,6 +519,19 @@ def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scen
                     img, st = ctx.render(vr.Context.params(integ, W, H, spp))
                     imgs.append(img)
                     assert np.array_equal(img, imgs[0]), (hier, trav, grid, cgrid, split, defer, pair, g3, g3res)
+        # recorded renders (the inverse path: integrator.h:616-644) with and without the uniform grid, all four solvers that look at the
+        # solver's segment: same image, same recorded sets
+        scene = file_scene(scenegen, "rand2k")
+        setup(ctx, ob, scene, "pin")
+        for solver in (0, 1, 2, 3, 4):
+            rec = []
+            for g3 in (0, 1):
+                ctx.set_option("grid3d", g3); ctx.set_option("grid3d_res", 0)
+                img, _ = ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 96, 64, 16, record=True, solver=solver))
+                cnt, idx = ctx.recorded(96, 64, 256)
+                rec.append((img, cnt, idx))
+            assert np.array_equal(rec[0][0], rec[1][0]), solver
+            assert np.array_equal(rec[0][1], rec[1][1]) and np.array_equal(rec[0][2], rec[1][2]), solver
         # the camera inside the mixture: the pinhole sits in a component's box -> no camera grid, same image
         scene = file_scene(scenegen, "rand300")
         oc = ob.make_camera("pinhole", (0.1, 1.0, 2.6), look=(0, 1, 0), fov=0.9)
