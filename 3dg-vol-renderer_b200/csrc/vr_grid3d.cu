@@ -6,13 +6,16 @@
 // grid that contains the origin lists the 2-5 components it can meet before it leaves that cell.
 //
 // The table: R^3 cells over the mixture's box; per cell the components whose culling box (the inflated 3-sigma box of the
-// hierarchy build, vr_lbvh.cu inflate_kernel) touches the cell, padded by 1e-3 of a cell, as leaf-order indices sorted
-// ascending (deterministic lists).  wave_trav2_kernel<SCATTER, GRID> (vr_wave.cu) tests the origin cell's list with the
-// reference's quadric and keeps the overlaps that ENTER before the ray leaves the cell; if their optical depth up to that
-// point already exceeds the sampled target the ray is complete, otherwise the hierarchy is walked for the overlaps that
-// enter at or beyond the cell's exit.  Every overlap is found by exactly one of the two stages, the quadric decides, and what
-// lies beyond the scatter point never reaches a result: images are bit-identical with and without the grid
-// (test_traversal_versions_and_builders_give_identical_images).
+// hierarchy build, vr_lbvh.cu inflate_kernel) touches the cell, padded by 1e-3 of a cell plus the FP32 rounding of coordinates
+// of the mixture's magnitude, as leaf-order indices sorted ascending (deterministic lists).
+// wave_trav2_kernel<SCATTER, GRID> (vr_wave.cu) tests the origin cell's list with the reference's quadric and keeps the overlaps
+// that ENTER before the ray leaves the cell.  If they hold more than the sampled optical depth inside the cell the ray is
+// finished and carries the cell's exit as a certificate; otherwise the hierarchy is walked for the overlaps that enter at or
+// beyond that point, so every overlap is kept by exactly one of the two stages.  wave_post_a accepts a result computed from a
+// certified list only where the reference's walk cannot have looked beyond the certificate and sends the slot back to the
+// hierarchy otherwise (vr_wave.cu, "Certificates of the uniform grid").  Images and recorded sets are bit-identical with and
+// without the grid: test_traversal_versions_and_builders_give_identical_images (incl. the far and x50 scenes, recorded renders,
+// all solver modes), test_uniform_grid_changes_no_bit_at_full_size (C2 at full size, C3).
 //   g3_count_kernel   entries per cell;  cub exclusive scan -> cell_start
 //   g3_fill_kernel    leaf-order indices into their cells
 //   g3_sort_kernel    every cell's list ascending
@@ -25,7 +28,7 @@
 
 namespace vr {
 
-struct G3Dims { float org[3], inv[3]; int res; };
+struct G3Dims { float org[3], inv[3], pad[3]; int res; };   // pad: slack of a box's cell range, in cells
 
 __device__ __forceinline__ void g3_range(const G3Dims& G, const float* __restrict__ lo, const float* __restrict__ hi, int g, int r0[3], int r1[3], bool* finite) {
     *finite = true;
@@ -33,8 +36,8 @@ __device__ __forceinline__ void g3_range(const G3Dims& G, const float* __restric
     for (int k = 0; k < 3; ++k) {
         const float a = lo[3 * (size_t)g + k], b = hi[3 * (size_t)g + k];
         if (!(fabsf(a) < 1e30f) || !(fabsf(b) < 1e30f)) *finite = false;
-        // conservative: a box that comes within 1e-3 of a cell of a cell is listed there
-        const float fa = floorf((a - G.org[k]) * G.inv[k] - 1e-3f), fb = floorf((b - G.org[k]) * G.inv[k] + 1e-3f);
+        // conservative: a box that comes within G.pad of a cell (1e-3 of a cell + the rounding of coordinates this far out) is listed there
+        const float fa = floorf((a - G.org[k]) * G.inv[k] - G.pad[k]), fb = floorf((b - G.org[k]) * G.inv[k] + G.pad[k]);
         r0[k] = (int)fminf(fmaxf(fa, 0.0f), (float)(G.res - 1));
         r1[k] = (int)fminf(fmaxf(fb, 0.0f), (float)(G.res - 1));
     }
@@ -99,6 +102,10 @@ int build_grid3d_device(vr_context* ctx) {
         const double ext = std::max(hi - lo, 1e-6) * (1.0 + 1e-5) + 1e-6;   // the mixture's box, a hair larger
         const double org = lo - 0.5 * (ext - (hi - lo));
         G.org[k] = (float)org; G.inv[k] = (float)((double)res / ext);
+        // a ray's cell and the parameter at which it leaves it are computed in FP32 from coordinates of magnitude maxabs: 32 ulp of
+        // those, in cells, on top of the 1e-3 (at C2: 1e-3 + 1.2e-4; for a mixture 230 units from the origin: 1e-3 + 1.4e-2)
+        const double maxabs = std::max(std::fabs(lo), std::fabs(hi)) + ext;
+        G.pad[k] = (float)(1e-3 + 32.0 * 5.9604644775390625e-08 * maxabs * (double)res / ext);
         ctx->g3_org[k] = G.org[k]; ctx->g3_inv[k] = G.inv[k]; ctx->g3_cell[k] = (float)(ext / (double)res);
     }
     const size_t cells = (size_t)res * res * res;

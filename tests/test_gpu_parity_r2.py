@@ -502,6 +502,7 @@ def test_traversal_versions_and_builders_give_identical_images(ctx, ob, vr, scen
     another structure, the quadric test decides and the sums are order independent -> images identical bit for bit, with
     and without grids, both integrators, also on the heavy-overlap scene whose rays overflow the per-slot overlap records."""
     cases = [(file_scene(scenegen, "rand2k"), "pin", 96, 64, 16), (file_scene(scenegen, "rand300"), "pin2", 64, 64, 9),
+             (file_scene(scenegen, "rand300_far"), "pin_far", 64, 64, 16), (file_scene(scenegen, "rand300_x50"), "pin_x50", 64, 64, 16),
              (scenegen.generate(3000, 11, nonuniform=True, diameter_range=(0.02, 0.09)), "pin", 128, 96, 16)]
     ctx.set_option("light_grid_min_samples", 0); ctx.set_option("camera_grid_min_samples", 0); ctx.set_option("grid3d_min_samples", 0)
     try:
