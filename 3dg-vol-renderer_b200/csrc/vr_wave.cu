@@ -1784,7 +1784,7 @@ int run_wavefront_pass(const RenderArgs& a_all, void* pool_mem, int P_total, int
             { float ms = 0.f; cudaEventElapsedTime(&ms, pe[6], pe[4]); pt_light += ms; }
         }
     };
-    // The batch of kBatch iterations is a fixed chain of 6-8 kernels with fixed grids and arguments: it is captured
+    // The batch of kBatch iterations is a fixed chain of 7-9 kernels per iteration with fixed grids and arguments: it is captured
     // once per part (and per deferral mode) into a CUDA graph and replayed, so a batch costs one launch on the host and
     // the kernels of short waves (small renders, the drain of a pass) follow each other without launch gaps.
     while (!failed) {
