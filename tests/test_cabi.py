@@ -74,3 +74,22 @@ def test_product_does_not_touch_the_oracle():
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "liboracle" not in text and "oracle_binding" not in text and "ref_driver" not in text, f
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+
+
+def test_documented_options_exist_in_the_library():
+    """every option of INTEGRATION.md section 4 is a name vr_set_option accepts (csrc/vr_api.cu), and every name it accepts is
+    documented there or named as a tuning / debug option below"""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    sec = doc[doc.index("## 4. Options"):]
+    sec = sec[:sec.index("\n## ", 5)] if "\n## " in sec[5:] else sec
+    documented = set(re.findall(r"^\| `([a-z0-9_]+)` \|", sec, flags=re.M)) | set(re.findall(r"`([a-z0-9_]+_min_samples|grid3d_res)`", sec))
+    src = open(os.path.join(root, "3dg-vol-renderer_b200", "csrc", "vr_api.cu")).read()
+    accepted = set(re.findall(r'strcmp\(name, "([a-z0-9_]+)"\)', src))
+    assert documented, "no options found in INTEGRATION.md"
+    missing = documented - accepted
+    assert not missing, f"documented but not accepted by vr_set_option: {sorted(missing)}"
+    tuning = {"max_pass_samples", "blocks_per_sm"}   # include/volrender.h documents these beside vr_set_option
+    undocumented = accepted - documented - tuning
+    assert not undocumented, f"accepted by vr_set_option but not in INTEGRATION.md section 4: {sorted(undocumented)}"
