@@ -91,6 +91,26 @@ def test_samples_vs_reference(ctx, ob, vr, golden_r2, scenegen, sc, cam, spp):
     assert np.array_equal(acc / np.float32(spp), img)
 
 
+@pytest.mark.parametrize("mode", [1, 2, 3])
+@pytest.mark.parametrize("sc,cam,spp", [("rand50", "pin", 16), ("rand300", "pin", 16)])
+def test_solver_modes_vs_reference(ctx, ob, vr, scenegen, mode, sc, cam, spp):
+    """the other distance solvers (1 analytic + bisection, 2 Newton, 3 bisection; distance_solvers.h:25-129) against the per-sample
+    radiance of the reference COMPILED WITH THAT SOLVER (tests/golden/golden_solvers.npz, oracle/make_golden_solvers.py)"""
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_solvers.npz"))
+    scene = file_scene(scenegen, sc)
+    oc = setup(ctx, ob, scene, cam)
+    ref = gold[f"samples/{mode}/{sc}/{cam}/ms/{spp}"]
+    ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 24, 24, spp, solver=mode))
+    g = ctx.samples(24 * 24, spp).reshape(24, 24, spp, 4)
+    _, sens, _ = ob.sample_sensitivity(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 24, 24, spp, solver=mode)
+    ok = within(g[..., :3], ref[..., :3], 1e-4)
+    print(f"solver {mode} {sc}/{cam}: samples within 1e-4 {ok.mean():.5f}, outside {int((~ok).sum())}, identical bits "
+          f"{(g.view(np.uint32) == ref.view(np.uint32)).all(-1).mean():.4f}, sensitive {sens.mean():.4f}")
+    assert (g[..., 3] == ref[..., 3]).mean() >= 0.9995          # path lengths
+    assert ok.mean() >= 0.995
+    assert not (~ok & ~sens).any()                               # every outlier is a sensitive sample
+
+
 ATTRIBUTION = [
     # label, scene, camera, integrator, W, H, spp, window
     ("rand50 ms", "rand50", "pin", "ms", 32, 32, 16, None), ("rand50 pin2 ms", "rand50", "pin2", "ms", 32, 32, 9, None),
