@@ -20,7 +20,7 @@
 //   spheres  scene=F w= h= step= env= [envcolor=r,g,b] cam... out=img.f32   (RayMarchingSpheres; the env part is
 //            random_device-seeded in the reference -> statistical use only, SURVEY.md F9 -- unless envcolor=0,0,0,
 //            which makes that term vanish: the image is then deterministic and pins the sphere path)
-//   samples  scene=F w= h= spp= [min_bounces=] [win=x0,y0,x1,y1] cam... out=samples.f32
+//   samples  scene=F w= h= spp= [min_bounces=] [win=x0,y0,x1,y1] [check=0] cam... out=samples.f32
 //            per-SAMPLE radiance of MultiScatterGaussians (float4 per (y, x, si): rgb + bounce index at the end of the
 //            path) for single-sample attribution of pixel differences, SURVEY.md 7.3
 // Every standard / Eigen header the reference pulls in is included FIRST, then `private` is made public for the
@@ -457,6 +457,68 @@ static int cmd_march(const Args& a) {
     return 0;
 }
 
+// trace scene=F w= h= spp= x= y= si= cam...: one sample's path, bounce by bounce -- the ray, the events the reference's BVH gather
+// returns and the events of its own naive gather (gmm.h:190-203) on the same ray.  Debugging aid for sample-level differences.
+static int cmd_trace(const Args& a) {
+    Scene scene = Scene::load_GMM(get(a, "scene"));
+    const int W = std::stoi(get(a, "w", "32")), H = std::stoi(get(a, "h", "32"));
+    const int spp = std::stoi(get(a, "spp", "16"));
+    const int x = std::stoi(get(a, "x", "0")), y = std::stoi(get(a, "y", "0")), si = std::stoi(get(a, "si", "0"));
+    const int min_scatter = std::stoi(get(a, "min_bounces", "5"));
+    auto cam = make_camera(a);
+    MultiScatterGaussians ms(cam, spp, min_scatter);
+    const size_t Nprims = scene.get_num_primitives();
+    std::vector<PrimitiveHitEvent> events, naive;
+    std::vector<size_t> active;
+    std::vector<int> idx_pos(Nprims, 0), idx_epoch(Nprims, 0);
+    int epoch_counter = 0;
+    uint64_t seed = derive_path_seed(x, y, si);
+    PCG32 rng(seed, 1);
+    int n = int(std::sqrt(spp));
+    int sx = si % n, sy = si / n;
+    float u = (x + (sx + rng.uniform()) / n) / W;
+    float v = (y + (sy + rng.uniform()) / n) / H;
+    Ray ray = cam->sample_ray({u, v});
+    Eigen::Vector3f throughput = Eigen::Vector3f::Ones();
+    for (int bounce = 0;; ++bounce) {
+        events.clear(); naive.clear();
+        scene.intersect_events(ray, events);
+        scene.gmm->at(0).intersect_events_naive(ray, naive);
+        printf("bounce %d o %.9g %.9g %.9g d %.9g %.9g %.9g bvh_events %zu naive_events %zu", bounce, ray.origin.x(), ray.origin.y(), ray.origin.z(),
+               ray.direction.x(), ray.direction.y(), ray.direction.z(), events.size(), naive.size());
+        if (events.size() != naive.size()) {
+            printf("  MISSING:");
+            for (const auto& e : naive) {
+                bool found = false;
+                for (const auto& f : events) if (f.index == e.index && f.entering == e.entering) found = true;
+                if (!found) printf(" %zu%c@%.9g", (size_t)e.index, e.entering ? '+' : '-', e.t);
+            }
+        }
+        printf("\n");
+        if (get(a, "events", "0") == "1")
+            for (const auto& e : events) printf("      ev %.9g %c %zu\n", e.t, e.entering ? '+' : '-', (size_t)e.index);
+        if (events.empty()) break;
+        float target_tau = -std::log(1.0f - rng.uniform());
+        active.clear();
+        float t_scatter = ms.get_free_flight_distance(ray, events, target_tau, scene.gmm->at(0), active, idx_pos, idx_epoch, epoch_counter);
+        printf("   target %.9g t %.9g active %zu\n", target_tau, t_scatter, active.size());
+        if (t_scatter < 0.f) break;
+        Eigen::Vector3f pos = ray.origin + t_scatter * ray.direction;
+        float albedo = scene.gmm->at(0).evaluate_albedo(active, pos);
+        bool is_env = (rng.uniform() < 1.f / (scene.lights.size() + 1));
+        if (!is_env) { (void)rng.uniform(); } else { (void)sample_uniform_direction(rng); }
+        throughput *= albedo;
+        if (bounce >= min_scatter) {
+            float rr = std::min(throughput.maxCoeff(), 0.9f);
+            if (rng.uniform() > rr) break;
+            throughput /= rr;
+        }
+        Eigen::Vector3f new_dir = sample_uniform_direction(rng);
+        ray = Ray(pos, new_dir);
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------------
 // Per-sample radiance of MultiScatterGaussians.  The reference only ever returns the pixel mean
 // (integrator.h:702-706), so the sample loop integrator.h:557-702 is walked here, statement by statement, around
@@ -548,11 +610,14 @@ static int cmd_samples(const Args& a) {
             }
         }
     }
-    // check against the reference's own render(): si-ordered sums reproduce its pixels bit for bit
+    // check against the reference's own render(): si-ordered sums reproduce its pixels bit for bit.  check=0 skips it: render()
+    // has no window, and at a benchmark configuration's full size (2.7e8 - 4.3e9 samples) it takes hours on host cores -- the dump
+    // above is the same code that the check validates on every small image (oracle/make_golden_r2.py)
+    const bool check = get(a, "check", "1") != "0";
     Image image(W, H);
-    ms.render(scene, image);
+    if (check) ms.render(scene, image);
     long mismatch = 0;
-    for (int y = y0; y < y1; ++y)
+    for (int y = y0; check && y < y1; ++y)
         for (int x = x0; x < x1; ++x) {
             Eigen::Vector3f pixel_L = Eigen::Vector3f::Zero();
             for (int si = 0; si < spp; ++si) {
@@ -584,6 +649,7 @@ int main(int argc, char** argv) {
         if (c == "spheres") return cmd_spheres(a);
         if (c == "march") return cmd_march(a);
         if (c == "samples") return cmd_samples(a);
+        if (c == "trace") return cmd_trace(a);
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());
         return 2;

@@ -419,6 +419,12 @@ static void gmm_intersect_events(const vo_gmm* m, const vo_ray* ray, vo_events* 
                 if (gauss_intersect(&m->g[gi], ray, &t0, &t1)) {
                     if (t0 >= 0.0f) events_push(ev, t0, 1, gi);
                     if (t1 >= 0.0f) events_push(ev, t1, 0, gi);
+                    /* a grazed component: the FP32 discriminant is exactly 0 and t_enter == t_exit.  The reference sorts its events
+                     * with std::sort on t alone (gmm.h:511-513), which is not stable: it may put this component's EXIT before its
+                     * ENTER, and the walk (integrator.h:466-486) then never removes the component from the active list again.
+                     * Which way the tie falls depends on the order of the whole event array in the reference's own traversal;
+                     * this restatement (enter before exit) and the device cannot know it, so the sample is marked: margin 0. */
+                    if (t0 >= 0.0f && t0 == t1) vo_min_margin = 0.0f;
                 }
             }
         } else {
