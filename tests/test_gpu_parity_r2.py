@@ -135,6 +135,27 @@ def test_config2_windows_vs_reference(ctx, ob, vr, scenegen, win):
     assert not (~ok & ~sens & ~tie).any() and not (~same_len & ~sens & ~tie).any()
 
 
+def test_config3_window_vs_reference(ctx, ob, vr, scenegen):
+    """config C3 (200 000 components, 2048^2, 64 of its 1024 spp): every sample of an 8 x 8 window against the REFERENCE's own
+    per-sample radiance; attribution as in test_config2_windows_vs_reference (half of the C3 paths graze a component)"""
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_windows.npz"))
+    win = (1000, 1100, 1008, 1108)
+    ref = gold["samples/c3/1000_1100_1008_1108/ms/64"]
+    scene = big_scene(scenegen, "c3")
+    oc = setup(ctx, ob, scene, "pin")
+    ctx.render(vr.Context.params(vr.INTEGRATOR_MS, 2048, 2048, 64, window=win))
+    g = ctx.samples(64, 64).reshape(8, 8, 64, 4)
+    _, sens, mg = ob.sample_sensitivity(ob.Gmm(scene), scene["lights"], ENV, oc, ob.INTEGRATOR_MS, 2048, 2048, 64, window=win)
+    tie = mg <= 0
+    ok = within(g[..., :3], ref[..., :3], 1e-4)
+    same_len = g[..., 3] == ref[..., 3]
+    print(f"C3 window {win} vs the reference: samples within 1e-4 {ok.mean():.5f}, outside {int((~ok).sum())} (sensitive {int((~ok & sens).sum())}, "
+          f"grazing tie {int((~ok & tie & ~sens).sum())}, unexplained {int((~ok & ~sens & ~tie).sum())}), identical bits "
+          f"{(g.view(np.uint32) == ref.view(np.uint32)).all(-1).mean():.4f}, same path length {same_len.mean():.5f}")
+    assert ok.mean() >= 0.99 and same_len.mean() >= 0.995
+    assert not (~ok & ~sens & ~tie).any() and not (~same_len & ~sens & ~tie).any()
+
+
 def test_config1_image_vs_reference(ctx, ob, vr, scenegen):
     """config C1 (1k components, 512^2, 64 spp, FreeFlightGaussians) at full size against every 8th pixel of every 8th row of the
     reference's own image"""
